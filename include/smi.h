@@ -1,0 +1,188 @@
+/* libsmi -- C ABI of the B200-native Stein Mixture Inference / SVGD update step.
+ *
+ * The reference (aleatory-science/smi_experiments) has no native boundary: its hot path
+ * is the Python call `engine.update(state, *args, **kwargs)` (reference
+ * src/engine_run.py:25,30; src/model_select/early_stopping.py:42) that runs NumPyro's
+ * `SteinVI.update` as one XLA computation.  This header is the boundary a replacement
+ * exports instead; every entry point cites the stage of that computation it replaces
+ * (SURVEY.md section 8a rows a1-a10).  INTEGRATION.md shows the jax.ffi / ctypes
+ * binding a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - return 0 on success, a negative SMI_E* code otherwise; never throws; the message
+ *     of the last failure on the calling thread is smi_last_error().
+ *   - the caller owns every buffer.  All pointers are DEVICE pointers (row-major fp32 /
+ *     int32, 16-byte aligned) unless a parameter is documented as host.  Workspaces are
+ *     sized by the *_workspace_bytes query and passed in; nothing is allocated inside.
+ *   - no host synchronisation and no default-stream use: work is enqueued on `stream`
+ *     (a cudaStream_t passed as void*), so every call is CUDA-graph capturable.
+ *   - scalar results (loss, bandwidth, step counter, PRNG key) stay on the device.
+ *   - sm_100a only.  There is no CPU fallback.
+ */
+#ifndef SMI_H_
+#define SMI_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SMI_VERSION 100
+
+#define SMI_OK 0
+#define SMI_EINVAL (-1)   /* bad argument                                  */
+#define SMI_ENOSPC (-2)   /* workspace too small                           */
+#define SMI_ECUDA (-3)    /* CUDA runtime / driver error                   */
+#define SMI_EARCH (-4)    /* device is not sm_100                          */
+#define SMI_ELIMIT (-5)   /* shape outside what the kernels support        */
+
+/* jnp.median index arithmetic */
+#define SMI_MEDIAN_EXACT_MIDPOINT 0
+#define SMI_MEDIAN_JAX_FP32_INDEX 1
+
+/* which Stein-force implementation ran / is requested */
+#define SMI_PATH_AUTO 0
+#define SMI_PATH_SMALL 1   /* m <= 64: difference-form kernel, shared-memory sort      */
+#define SMI_PATH_TC 2      /* any m: tcgen05 3xTF32 Gram + radix select + tcgen05 force */
+
+#define SMI_OPT_NONE 0
+#define SMI_OPT_ADAM 1     /* numpyro.optim.Adam    (reference experiments/uci_benchmark.py:191)   */
+#define SMI_OPT_ADAGRAD 2  /* numpyro.optim.Adagrad (reference experiments/img_classifier.py:173)  */
+
+#define SMI_MODEL_GAUSS 0    /* reference experiments/variance_collapse.py:70-74 */
+#define SMI_MODEL_BNN_REG 1  /* reference src/models/uci_bnn.py:21-68, src/models/reg_1d_bnn.py:22-67 */
+#define SMI_MODEL_BNN_CLS 2  /* reference src/models/mlp.py:14-65 */
+
+#define SMI_ACT_RELU 0
+#define SMI_ACT_TANH 1
+
+#define SMI_NOISE_GAMMA_PREC 0 /* prec ~ Gamma(1, 0.1), y ~ N(f, prec^-1/2) */
+#define SMI_NOISE_FIXED 1      /* y ~ N(f, sigma)                            */
+
+#define SMI_GUIDE_NORMAL 0 /* AutoNormal: psi = sorted(loc, rho) leaves, u = loc + softplus(rho) eps */
+#define SMI_GUIDE_DELTA 1  /* AutoDelta : psi = loc leaves, S = 1                                    */
+
+#define SMI_T_IDENTITY 0
+#define SMI_T_EXP 1
+
+#define SMI_MAX_SITES 16
+
+/* One latent site of the model (numpyro.sample statement), in model order. */
+typedef struct SmiSite {
+  int32_t size;      /* number of scalars                                         */
+  int32_t transform; /* SMI_T_*: unconstrained -> constrained                     */
+  int32_t lat;       /* offset in the latent vector (model order)                 */
+  int32_t loc;       /* offset of <site>_auto_loc   inside the raveled particle   */
+  int32_t rho;       /* offset of <site>_auto_scale inside the raveled particle; -1 for AutoDelta */
+} SmiSite;
+
+/* Model + guide descriptor (host struct, passed by pointer, copied at call time). */
+typedef struct SmiModelDesc {
+  int32_t kind;    /* SMI_MODEL_*                                                 */
+  int32_t guide;   /* SMI_GUIDE_*                                                 */
+  int32_t in_dim;  /* features (Gaussian target: dimension)                       */
+  int32_t hidden;  /* hidden width (two hidden layers)                            */
+  int32_t out_dim; /* 1 for regression, classes for classification               */
+  int32_t act;     /* SMI_ACT_*                                                   */
+  int32_t noise;   /* SMI_NOISE_* (regression)                                    */
+  float sigma;     /* fixed observation noise (SMI_NOISE_FIXED)                   */
+  int32_t n_sites;
+  int32_t latent_dim;   /* L = sum of site sizes                                  */
+  int32_t particle_dim; /* d = 2L (AutoNormal) or L (AutoDelta)                   */
+  SmiSite sites[SMI_MAX_SITES];
+} SmiModelDesc;
+
+int smi_version(void);
+const char* smi_last_error(void);
+/* 0 when the current device is compute capability 10.x, SMI_EARCH otherwise. */
+int smi_device_check(void);
+
+/* ---- Stein force: replaces RBFKernel.compute + _apply_kernel + _kernel_grad + force sum
+ *      + ||F|| (NumPyro steinvi.py::_svgd_loss_and_grads).
+ *   X, G : (m, d) particles and per-particle ELBO gradients.
+ *   F    : (m, d) out (may be NULL when an optimizer is fused and F is not wanted).
+ *   loss : out, ||F||_F.   h : out, the bandwidth used.
+ *   h_fixed > 0 skips the median heuristic and uses that bandwidth.
+ *   F = c_att * K G + (2 alpha / (h m)) (rowsum(K) * X - K X),  K_ij = exp(-|x_i-x_j|^2 / h),
+ *   h = median(D)^2 / ln m + 1.1920929e-7 (m == 1: h = 1).                               */
+size_t smi_stein_force_workspace_bytes(int m, int d, int path);
+int smi_stein_force_f32(const float* X, const float* G, int m, int d, float c_att, float alpha,
+                        int median_mode, float h_fixed, int path, float* F, float* loss, float* h,
+                        void* ws, size_t ws_bytes, void* stream);
+
+/* Stages of the above, separately testable.
+ *   smi_sqdist_f32          : D2 (m, m) = max(|x_i|^2 + |x_j|^2 - 2 x_i.x_j, 0)  (Gram form, row a4)
+ *   smi_median_bandwidth_f32: h from D2 (exact order statistics of sqrt(D2), row a4)
+ *   rank_out (optional, 2 x uint32 device): the two selected D2 bit patterns (lo, hi).   */
+size_t smi_sqdist_workspace_bytes(int m, int d, int path);
+int smi_sqdist_f32(const float* X, int m, int d, int path, float* D2, void* ws, size_t ws_bytes,
+                   void* stream);
+size_t smi_median_bandwidth_workspace_bytes(int m);
+int smi_median_bandwidth_f32(const float* D2, int m, int median_mode, float* h, uint32_t* rank_out,
+                             void* ws, size_t ws_bytes, void* stream);
+
+/* ---- Row-sharded Stein force (no counterpart in the single-device reference).
+ *   One process per GPU owns particle rows [row0, row0 + rows).  X and G hold ALL m particles
+ *   (the caller all-gathers them over NCCL).  Stages, with the caller's collectives between:
+ *     smi_stein_rows_dist
+ *     for pass in 0..2: smi_stein_rows_hist -> all-reduce SUM hist[2048] -> smi_stein_rows_scan
+ *     smi_stein_rows_tail -> all-reduce SUM cnt_min[0], MIN cnt_min[1]
+ *     smi_stein_rows_bandwidth -> smi_stein_rows_force -> all-reduce SUM sumsq; loss = sqrt(sumsq)
+ *   `hist` is a caller-owned 2048 x uint32 buffer, zero before pass 0.  Integer reductions are
+ *   exact, so h is bit-identical for every world size.  ws is private to the rank and must be
+ *   the same buffer for every stage of one step.                                           */
+size_t smi_stein_rows_workspace_bytes(int rows, int m, int d);
+int smi_stein_rows_dist(const float* X, int m, int d, int row0, int rows, void* ws, size_t ws_bytes,
+                        void* stream);
+int smi_stein_rows_hist(int m, int d, int row0, int rows, int pass, uint32_t* hist, void* ws,
+                        size_t ws_bytes, void* stream);
+int smi_stein_rows_scan(int m, int d, int row0, int rows, int pass, int median_mode, uint32_t* hist,
+                        void* ws, size_t ws_bytes, void* stream);
+int smi_stein_rows_tail(int m, int d, int row0, int rows, uint32_t* cnt_min, void* ws, size_t ws_bytes,
+                        void* stream);
+int smi_stein_rows_bandwidth(int m, int d, int row0, int rows, int median_mode, float alpha,
+                             float h_fixed, const uint32_t* cnt_le, const uint32_t* min_gt, float* h,
+                             void* ws, size_t ws_bytes, void* stream);
+int smi_stein_rows_force(const float* X, const float* G, int m, int d, int row0, int rows, float c_att,
+                         float* F_rows, double* sumsq, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- Optimizers (row a8).  `grad_sign` multiplies F before use: the Stein step hands the
+ *      optimizer -F, so pass -1.  `step` is a device int32 holding the number of updates
+ *      applied so far; it is read, and incremented by one when `bump_step` is non-zero.  */
+int smi_adam_f32(float* x, float* mom, float* vel, const float* F, float grad_sign, int32_t* step,
+                 int bump_step, float lr, float b1, float b2, float eps, size_t n, void* stream);
+int smi_adagrad_f32(float* x, float* acc, float* mom, const float* F, float grad_sign,
+                    int32_t* step, int bump_step, float lr, float momentum, size_t n, void* stream);
+
+/* ---- Per-particle mixture-ELBO gradients (row a3; NumPyro stein_loss.py).
+ *   psi  : (m, d) all particles.   eps : (nrows, S, L) N(0,1) noise of the owned rows (NULL for
+ *   AutoDelta).  idx : (nrows, S, B) int32 subsample rows into x / y, or NULL = every draw uses
+ *   rows 0..B-1 of x / y.
+ *   x    : (N, in_dim) fp32.  y : (N) fp32 targets, or int32 labels for SMI_MODEL_BNN_CLS.
+ *   lik_scale : plate scaling N/B.   tau : loss_temperature.
+ *   rows : particles [row0, row0 + nrows) are differentiated (particle-row sharding, row a3/e).
+ *   G    : (nrows, d) out = d/d psi_i mean_s ELBO_is.   elbo : (nrows) out.                */
+size_t smi_elbo_grad_workspace_bytes(const SmiModelDesc* md, int m, int S, int B, int nrows);
+int smi_elbo_grad_f32(const SmiModelDesc* md, const float* psi, const float* eps,
+                      const int32_t* idx, const float* x, const void* y, int m, int S, int B,
+                      float lik_scale, float tau, int row0, int nrows, float* G, float* elbo,
+                      void* ws, size_t ws_bytes, void* stream);
+
+/* ---- Counter PRNG (row a9): threefry2x32 key chain of one update on the device.
+ *   key_in  : device uint32[2] state key.  key_out : device uint32[2] next state key (must not
+ *   alias key_in; may be NULL).  n_total > 0 declares a data plate (it consumes one subkey even
+ *   when idx is NULL).
+ *   eps     : (nrows, S, L) out (NULL for AutoDelta).  idx : (nrows, S, B) out or NULL.
+ *   Chain (partitionable threefry layout): split(key,3) ->
+ *   step key -> attractive key -> per particle -> per draw -> guide key -> one subkey per
+ *   RNG-consuming statement (data plate first, then latent sites in model order).          */
+int smi_prng_step_f32(const SmiModelDesc* md, const uint32_t* key_in, uint32_t* key_out, int m,
+                      int S, int n_total, int B, int row0, int nrows, float* eps, int32_t* idx,
+                      void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SMI_H_ */

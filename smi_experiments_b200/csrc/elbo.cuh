@@ -1,0 +1,50 @@
+// Internal interface between the ELBO-gradient kernels (elbo_guide.cu, elbo_mlp.cu, elbo_api.cu).
+//
+// Pipeline for one smi_elbo_grad_f32 call (NumPyro SteinLoss.particle_loss):
+//   guide_prep    : gather mu / sigma / 1/sigma of every particle into latent order, log-dets
+//   guide_sample  : z = mu_i + sigma_i eps ; partial quadratic forms sum_k ((z-mu_j)/sigma_j)^2
+//   guide_weights : log q_j -> mixture responsibilities w_j, log q
+//   model kernel  : d log p / d u and log p per draw (elbo_mlp.cu)
+//   guide_grad    : assemble d/d(loc, rho) of mean_s ELBO, fixed summation order
+#pragma once
+#include <cuda_runtime.h>
+
+#include "common.cuh"
+
+constexpr int kGuideKT = 64;      // latent indices per CTA tile
+constexpr int kGuideMaxM = 64;    // mixture components supported by the AutoNormal path
+
+struct ElboWs {
+  int* loc_of;     // [L] latent index -> offset of loc in psi
+  int* rho_of;     // [L]
+  int* tr_of;      // [L] transform code
+  float* MU;       // [m x L]
+  float* SIG;      // [m x L]
+  float* ISIG;     // [m x L]
+  double* logdet_part;  // [m x nkt]
+  float* Z;        // [nrows x S x L] unconstrained draws
+  float* DZ;       // [nrows x S x L] d log p / d u
+  float* QP;       // [nrows x nkt x S x m] partial quadratic forms
+  float* W;        // [nrows x S x m]
+  float* LOGQ;     // [nrows x S]
+  float* LOGP;     // [nrows x S]
+  int nkt;
+};
+
+size_t smi_elbo_carve(SmiArena& ar, ElboWs& w, const SmiModelDesc& md, int m, int S, int nrows);
+
+int smi_guide_prep(const SmiModelDesc& md, const float* psi, int m, ElboWs& w, cudaStream_t st);
+int smi_guide_sample(const SmiModelDesc& md, const float* eps, int m, int S, int row0, int nrows, ElboWs& w,
+                     cudaStream_t st);
+int smi_guide_weights(const SmiModelDesc& md, int m, int S, int nrows, ElboWs& w, cudaStream_t st);
+int smi_guide_grad(const SmiModelDesc& md, const float* psi, const float* eps, int m, int S, float tau,
+                   int row0, int nrows, ElboWs& w, float* G, float* elbo, cudaStream_t st);
+int smi_delta_gather(const SmiModelDesc& md, const float* psi, int row0, int nrows, ElboWs& w, cudaStream_t st);
+int smi_delta_scatter(const SmiModelDesc& md, float tau, int nrows, ElboWs& w, float* G, float* elbo,
+                      cudaStream_t st);
+
+// Model kernels: Z (ndraws x L, unconstrained) -> DZ = d log p / d u, LOGP.
+size_t smi_model_smem_bytes(const SmiModelDesc& md, int B);
+int smi_model_logp_grad(const SmiModelDesc& md, const float* Z, const int32_t* idx, const float* x,
+                        const void* y, int ndraws, int B, float lik_scale, float* DZ, float* LOGP,
+                        cudaStream_t st);

@@ -1,0 +1,55 @@
+// C-ABI entry point of the per-particle mixture-ELBO gradient.
+#include "elbo.cuh"
+
+static int check_desc(const SmiModelDesc* md) {
+  if (!md) SMI_FAIL(SMI_EINVAL, "null model descriptor");
+  if (md->n_sites < 1 || md->n_sites > SMI_MAX_SITES) SMI_FAIL(SMI_EINVAL, "n_sites=%d", md->n_sites);
+  int L = 0;
+  for (int s = 0; s < md->n_sites; ++s) {
+    if (md->sites[s].lat != L) SMI_FAIL(SMI_EINVAL, "site %d: latent offsets must be contiguous in model order", s);
+    L += md->sites[s].size;
+  }
+  if (L != md->latent_dim) SMI_FAIL(SMI_EINVAL, "latent_dim=%d but sites sum to %d", md->latent_dim, L);
+  const int want = md->guide == SMI_GUIDE_NORMAL ? 2 * L : L;
+  if (md->particle_dim != want) SMI_FAIL(SMI_EINVAL, "particle_dim=%d, expected %d", md->particle_dim, want);
+  return SMI_OK;
+}
+
+SMI_API size_t smi_elbo_grad_workspace_bytes(const SmiModelDesc* md, int m, int S, int B, int nrows) {
+  (void)B;
+  if (!md || m < 1 || S < 1 || nrows < 1) return 0;
+  SmiArena ar(nullptr, 0);
+  ElboWs w;
+  return smi_elbo_carve(ar, w, *md, m, S, nrows) + 512;
+}
+
+SMI_API int smi_elbo_grad_f32(const SmiModelDesc* md, const float* psi, const float* eps, const int32_t* idx,
+                              const float* x, const void* y, int m, int S, int B, float lik_scale, float tau,
+                              int row0, int nrows, float* G, float* elbo, void* ws, size_t ws_bytes,
+                              void* stream) {
+  int rc = check_desc(md);
+  if (rc) return rc;
+  if (!psi || !G || !ws) SMI_FAIL(SMI_EINVAL, "smi_elbo_grad_f32: null pointer");
+  if (m < 1 || S < 1 || row0 < 0 || nrows < 1 || row0 + nrows > m)
+    SMI_FAIL(SMI_EINVAL, "smi_elbo_grad_f32: m=%d S=%d rows [%d, %d)", m, S, row0, row0 + nrows);
+  if (md->kind != SMI_MODEL_GAUSS && (!x || !y || B < 1)) SMI_FAIL(SMI_EINVAL, "smi_elbo_grad_f32: model needs x, y, B");
+  if (ws_bytes < smi_elbo_grad_workspace_bytes(md, m, S, B, nrows)) SMI_FAIL(SMI_ENOSPC, "elbo workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  SmiArena ar(ws, ws_bytes);
+  ElboWs w;
+  smi_elbo_carve(ar, w, *md, m, S, nrows);
+  if (md->guide == SMI_GUIDE_DELTA) {
+    if (S != 1) SMI_FAIL(SMI_EINVAL, "AutoDelta guides take S = 1 (got %d)", S);
+    if ((rc = smi_delta_gather(*md, psi, row0, nrows, w, st))) return rc;
+    if ((rc = smi_model_logp_grad(*md, w.Z, idx, x, y, nrows, B, lik_scale, w.DZ, w.LOGP, st))) return rc;
+    return smi_delta_scatter(*md, tau, nrows, w, G, elbo, st);
+  }
+  if (md->guide != SMI_GUIDE_NORMAL) SMI_FAIL(SMI_EINVAL, "guide=%d", md->guide);
+  if (!eps) SMI_FAIL(SMI_EINVAL, "AutoNormal guides need eps");
+  if (m > kGuideMaxM) SMI_FAIL(SMI_ELIMIT, "AutoNormal mixture path supports m <= %d particles (m=%d)", kGuideMaxM, m);
+  if ((rc = smi_guide_prep(*md, psi, m, w, st))) return rc;
+  if ((rc = smi_guide_sample(*md, eps, m, S, row0, nrows, w, st))) return rc;
+  if ((rc = smi_guide_weights(*md, m, S, nrows, w, st))) return rc;
+  if ((rc = smi_model_logp_grad(*md, w.Z, idx, x, y, nrows * S, B, lik_scale, w.DZ, w.LOGP, st))) return rc;
+  return smi_guide_grad(*md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
+}

@@ -1,0 +1,370 @@
+// AutoNormal / AutoDelta guide side of the per-particle mixture-ELBO gradient (row a3).
+//
+// Restates the guide half of NumPyro's SteinLoss.single_particle_loss (stein_loss.py) for
+// mean-field Normal guides (autoguide.AutoNormal, scale = softplus(rho)) and Delta guides:
+//   u = loc_i + softplus(rho_i) eps,   log q = logsumexp_j log N(u; loc_j, sigma_j) - log|dT/du| - log m
+// and the reverse pass through it, written out by hand:
+//   T_k      = sum_j w_j (u_k - mu_jk) / sigma_jk^2,   w = softmax_j(log q_j)
+//   dU_k     = tau dlogp/du_k + T_k + [k in an exp site]
+//   dloc_ik  = mean_s ( dU_k - w_i eps_k / sigma_ik )
+//   drho_ik  = mean_s ( dU_k eps_k - w_i (eps_k^2 - 1) / sigma_ik ) * sigmoid(rho_ik)
+// Everything is summed in a fixed order (no floating-point atomics).
+#include <math.h>
+
+#include "elbo.cuh"
+
+namespace {
+
+constexpr float kLog2Pi = 1.8378770664093453f;
+
+__device__ __forceinline__ float softplus_f(float x) {
+  // jax.nn.softplus = logaddexp(x, 0)
+  return fmaxf(x, 0.f) + log1pf(expf(-fabsf(x)));
+}
+__device__ __forceinline__ float sigmoid_f(float x) { return 1.f / (1.f + expf(-x)); }
+
+__device__ __forceinline__ int find_site(const SmiModelDesc& md, int k) {
+  int s = 0;
+  while (s + 1 < md.n_sites && k >= md.sites[s + 1].lat) ++s;
+  return s;
+}
+
+// ---------------------------------------------------------------------------------------
+// grid (nkt, m), block kGuideKT*4 = 256: 4 tiles of 64 latents per block.
+__global__ void __launch_bounds__(256)
+guide_prep_kernel(const SmiModelDesc md, const float* __restrict__ psi, int m, int* __restrict__ loc_of,
+                  int* __restrict__ rho_of, int* __restrict__ tr_of, float* __restrict__ MU,
+                  float* __restrict__ SIG, float* __restrict__ ISIG, double* __restrict__ logdet_part) {
+  __shared__ double red[32];
+  const int L = md.latent_dim, d = md.particle_dim;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y;
+  double ls = 0.0;
+  if (k < L) {
+    const int s = find_site(md, k);
+    const int off = k - md.sites[s].lat;
+    const int lo = md.sites[s].loc + off;
+    const int ro = md.sites[s].rho + off;
+    if (j == 0) {
+      loc_of[k] = lo;
+      rho_of[k] = ro;
+      tr_of[k] = md.sites[s].transform;
+    }
+    const float mu = psi[(size_t)j * d + lo];
+    const float sg = softplus_f(psi[(size_t)j * d + ro]);
+    MU[(size_t)j * L + k] = mu;
+    SIG[(size_t)j * L + k] = sg;
+    ISIG[(size_t)j * L + k] = 1.f / sg;
+    ls = (double)logf(sg);
+  }
+  ls = block_sum(ls, red);
+  if (threadIdx.x == 0) logdet_part[(size_t)j * gridDim.x + blockIdx.x] = ls;
+}
+
+// ---------------------------------------------------------------------------------------
+// Quadratic forms a[s][j] = sum_k ((z_sk - mu_jk) / sigma_jk)^2 over one tile of 64 latents.
+// grid (nkt, nrows); 256 threads = 32 s-groups (4 draws each) x 8 j-groups (4 components each).
+// smem: zt[64][128], mt[64][32], it[64][32], columns XOR-swizzled by ((k & 7) << 2).
+__global__ void __launch_bounds__(256)
+guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU, const float* __restrict__ SIG,
+                    const float* __restrict__ ISIG, int m, int S, int L, int row0, float* __restrict__ Z,
+                    float* __restrict__ QP, int nkt) {
+  extern __shared__ float sm[];
+  float* zt = sm;                       // [64][128]
+  float* mt = zt + kGuideKT * 128;      // [64][32]
+  float* it = mt + kGuideKT * 32;       // [64][32]
+  const int kt = blockIdx.x, r = blockIdx.y, i = row0 + r;
+  const int k0 = kt * kGuideKT;
+  const int ts = threadIdx.x & 31, tj = threadIdx.x >> 5;
+  for (int sb = 0; sb < S; sb += 128) {
+    __syncthreads();
+    // stage z tile (and write Z): coalesced along k
+    for (int t = threadIdx.x; t < 128 * kGuideKT; t += blockDim.x) {
+      const int sl = t / kGuideKT, kk = t - sl * kGuideKT;
+      const int s = sb + sl, k = k0 + kk;
+      float z = 0.f;
+      if (s < S && k < L) {
+        const size_t e = ((size_t)r * S + s) * L + k;
+        z = fmaf(SIG[(size_t)i * L + k], eps[e], MU[(size_t)i * L + k]);
+        Z[e] = z;
+      }
+      zt[kk * 128 + (sl ^ ((kk & 7) << 2))] = z;
+    }
+    for (int jb = 0; jb < m; jb += 32) {
+      __syncthreads();
+      for (int t = threadIdx.x; t < 32 * kGuideKT; t += blockDim.x) {
+        const int jl = t / kGuideKT, kk = t - jl * kGuideKT;
+        const int j = jb + jl, k = k0 + kk;
+        float mu = 0.f, is = 0.f;  // is = 0 masks padded latents and components
+        if (j < m && k < L) {
+          mu = MU[(size_t)j * L + k];
+          is = ISIG[(size_t)j * L + k];
+        }
+        const int c = jl ^ ((kk & 7) << 2);
+        mt[kk * 32 + c] = mu;
+        it[kk * 32 + c] = is;
+      }
+      __syncthreads();
+      float acc[4][4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+#pragma unroll 4
+      for (int kk = 0; kk < kGuideKT; ++kk) {
+        const int sw = (kk & 7) << 2;
+        const float4 z4 = *reinterpret_cast<const float4*>(zt + kk * 128 + ((ts * 4) ^ sw));
+        const float4 m4 = *reinterpret_cast<const float4*>(mt + kk * 32 + ((tj * 4) ^ sw));
+        const float4 i4 = *reinterpret_cast<const float4*>(it + kk * 32 + ((tj * 4) ^ sw));
+        const float zz[4] = {z4.x, z4.y, z4.z, z4.w};
+        const float mm[4] = {m4.x, m4.y, m4.z, m4.w};
+        const float ii[4] = {i4.x, i4.y, i4.z, i4.w};
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) {
+            const float df = (zz[a] - mm[b]) * ii[b];
+            acc[a][b] = fmaf(df, df, acc[a][b]);
+          }
+      }
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+        const int s = sb + ts * 4 + a;
+        if (s >= S) continue;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const int j = jb + tj * 4 + b;
+          if (j < m) QP[(((size_t)r * nkt + kt) * S + s) * m + j] = acc[a][b];
+        }
+      }
+    }
+  }
+}
+
+
+// ---------------------------------------------------------------------------------------
+// One warp per (row, draw): reduce the tile partials, softmax over components.
+__global__ void __launch_bounds__(256)
+guide_weights_kernel(const SmiModelDesc md, const float* __restrict__ QP, const double* __restrict__ logdet_part,
+                     int nlb, const float* __restrict__ Z, int m, int S, int nrows, int nkt,
+                     float* __restrict__ W, float* __restrict__ LOGQ) {
+  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (wid >= nrows * S) return;
+  const int r = wid / S, s = wid - r * S;
+  const int L = md.latent_dim;
+  double lq[2] = {-INFINITY, -INFINITY};  // components lane, lane + 32; kept in double: |lq| ~ L
+  for (int c = 0; c < 2; ++c) {
+    const int j = lane + 32 * c;
+    if (j >= m) continue;
+    double a = 0.0;
+    for (int kt = 0; kt < nkt; ++kt) a += (double)QP[(((size_t)r * nkt + kt) * S + s) * m + j];
+    double ld = 0.0;
+    for (int b = 0; b < nlb; ++b) ld += logdet_part[(size_t)j * nlb + b];
+    lq[c] = -0.5 * a - ld - 0.5 * (double)L * (double)kLog2Pi;
+  }
+  double mx = fmax(lq[0], lq[1]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  const float e0 = lq[0] > -INFINITY ? expf((float)(lq[0] - mx)) : 0.f;
+  const float e1 = lq[1] > -INFINITY ? expf((float)(lq[1] - mx)) : 0.f;
+  const float sum = warp_sum(e0 + e1);
+  if (lane < m) W[((size_t)r * S + s) * m + lane] = e0 / sum;
+  if (lane + 32 < m) W[((size_t)r * S + s) * m + lane + 32] = e1 / sum;
+  if (lane == 0) {
+    float logjac = 0.f;  // log |d theta / d u| = u on exp sites
+    for (int t = 0; t < md.n_sites; ++t)
+      if (md.sites[t].transform == SMI_T_EXP)
+        for (int q = 0; q < md.sites[t].size; ++q) logjac += Z[((size_t)r * S + s) * L + md.sites[t].lat + q];
+    LOGQ[(size_t)r * S + s] = (float)(mx + (double)logf(sum) - (double)logjac - log((double)m));
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// grid (nkt, nrows), 256 threads = 64 latents x 4 draw groups.  MP = padded component count.
+template <int MP>
+__global__ void __launch_bounds__(256)
+guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, const float* __restrict__ MU,
+                  const float* __restrict__ SIG, const float* __restrict__ ISIG, const float* __restrict__ W,
+                  const float* __restrict__ DZ, const float* __restrict__ LOGP, const float* __restrict__ LOGQ,
+                  const int* __restrict__ loc_of, const int* __restrict__ rho_of, const int* __restrict__ tr_of,
+                  int m, int S, int L, int d, float tau, int row0, float* __restrict__ G,
+                  float* __restrict__ elbo) {
+  extern __shared__ float sm[];
+  float* wt = sm;                        // [S][MP]
+  float* part = wt + (size_t)S * MP;     // [4][64][2]
+  const int kt = blockIdx.x, r = blockIdx.y, i = row0 + r;
+  const int kk = threadIdx.x & 63, sg = threadIdx.x >> 6;
+  const int k = kt * kGuideKT + kk;
+  for (int t = threadIdx.x; t < S * MP; t += blockDim.x) {
+    const int s = t / MP, j = t - s * MP;
+    wt[t] = j < m ? W[((size_t)r * S + s) * m + j] : 0.f;
+  }
+  __syncthreads();
+  float gl = 0.f, gs = 0.f;
+  if (k < L) {
+    float mu[MP], q[MP];
+#pragma unroll
+    for (int j = 0; j < MP; ++j) {
+      mu[j] = 0.f;
+      q[j] = 0.f;
+      if (j < m) {
+        mu[j] = MU[(size_t)j * L + k];
+        const float is = ISIG[(size_t)j * L + k];
+        q[j] = is * is;
+      }
+    }
+    const float mu_i = MU[(size_t)i * L + k], sg_i = SIG[(size_t)i * L + k], is_i = ISIG[(size_t)i * L + k];
+    const float jac = tr_of[k] == SMI_T_EXP ? 1.f : 0.f;
+    for (int s = sg; s < S; s += 4) {
+      const size_t e = ((size_t)r * S + s) * L + k;
+      const float ep = eps[e];
+      const float z = fmaf(sg_i, ep, mu_i);
+      float T = 0.f;
+#pragma unroll
+      for (int j = 0; j < MP; ++j) T = fmaf(wt[s * MP + j] * (z - mu[j]), q[j], T);
+      const float du = fmaf(tau, DZ[e], T) + jac;
+      const float wi = wt[s * MP + i];
+      gl += du - wi * ep * is_i;
+      gs += du * ep - wi * (ep * ep - 1.f) * is_i;
+    }
+  }
+  part[(sg * 64 + kk) * 2] = gl;
+  part[(sg * 64 + kk) * 2 + 1] = gs;
+  __syncthreads();
+  if (sg == 0 && k < L) {
+    float a = 0.f, b = 0.f;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      a += part[(g * 64 + kk) * 2];
+      b += part[(g * 64 + kk) * 2 + 1];
+    }
+    const float inv = 1.f / (float)S;
+    G[(size_t)r * d + loc_of[k]] = a * inv;
+    G[(size_t)r * d + rho_of[k]] = b * inv * sigmoid_f(psi[(size_t)i * d + rho_of[k]]);
+  }
+  if (kt == 0 && elbo && threadIdx.x < 32) {  // mean_s (tau log p - log q), fixed order
+    double v = 0.0;
+    for (int s = threadIdx.x; s < S; s += 32)
+      v += (double)tau * (double)LOGP[(size_t)r * S + s] - (double)LOGQ[(size_t)r * S + s];
+    v = warp_sum(v);
+    if (threadIdx.x == 0) elbo[r] = (float)(v / (double)S);
+  }
+}
+
+// ---- AutoDelta --------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+delta_gather_kernel(const SmiModelDesc md, const float* __restrict__ psi, int row0, float* __restrict__ Z,
+                    int* __restrict__ loc_of, int* __restrict__ tr_of) {
+  const int L = md.latent_dim, d = md.particle_dim;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+  if (k >= L) return;
+  const int s = find_site(md, k);
+  const int lo = md.sites[s].loc + (k - md.sites[s].lat);
+  if (r == 0) {
+    loc_of[k] = lo;
+    tr_of[k] = md.sites[s].transform;
+  }
+  Z[(size_t)r * L + k] = psi[(size_t)(row0 + r) * d + lo];
+}
+
+__global__ void __launch_bounds__(256)
+delta_scatter_kernel(const float* __restrict__ DZ, const float* __restrict__ LOGP, const int* __restrict__ loc_of,
+                     int L, int d, float tau, float* __restrict__ G, float* __restrict__ elbo) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+  if (k < L) G[(size_t)r * d + loc_of[k]] = tau * DZ[(size_t)r * L + k];
+  if (k == 0 && elbo) elbo[r] = tau * LOGP[r];
+}
+
+}  // namespace
+
+// ---- host side ---------------------------------------------------------------------------
+static int nlb_of(int L) { return (L + 255) / 256; }
+
+size_t smi_elbo_carve(SmiArena& ar, ElboWs& w, const SmiModelDesc& md, int m, int S, int nrows) {
+  const int L = md.latent_dim;
+  w.nkt = (L + kGuideKT - 1) / kGuideKT;
+  w.loc_of = ar.take<int>(L);
+  w.rho_of = ar.take<int>(L);
+  w.tr_of = ar.take<int>(L);
+  const bool normal = md.guide == SMI_GUIDE_NORMAL;
+  w.MU = ar.take<float>(normal ? (size_t)m * L : 0);
+  w.SIG = ar.take<float>(normal ? (size_t)m * L : 0);
+  w.ISIG = ar.take<float>(normal ? (size_t)m * L : 0);
+  w.logdet_part = ar.take<double>(normal ? (size_t)m * nlb_of(L) : 0);
+  w.Z = ar.take<float>((size_t)nrows * S * L);
+  w.DZ = ar.take<float>((size_t)nrows * S * L);
+  w.QP = ar.take<float>(normal ? (size_t)nrows * w.nkt * S * m : 0);
+  w.W = ar.take<float>(normal ? (size_t)nrows * S * m : 0);
+  w.LOGQ = ar.take<float>((size_t)nrows * S);
+  w.LOGP = ar.take<float>((size_t)nrows * S);
+  return ar.off;
+}
+
+int smi_guide_prep(const SmiModelDesc& md, const float* psi, int m, ElboWs& w, cudaStream_t st) {
+  dim3 grid(nlb_of(md.latent_dim), m);
+  guide_prep_kernel<<<grid, 256, 0, st>>>(md, psi, m, w.loc_of, w.rho_of, w.tr_of, w.MU, w.SIG, w.ISIG,
+                                          w.logdet_part);
+  SMI_LAUNCH_OK();
+  return SMI_OK;
+}
+
+int smi_guide_sample(const SmiModelDesc& md, const float* eps, int m, int S, int row0, int nrows, ElboWs& w,
+                     cudaStream_t st) {
+  const size_t smem = (size_t)kGuideKT * (128 + 64) * sizeof(float);
+  static bool set = false;
+  if (!set) {
+    SMI_CUDA_OK(cudaFuncSetAttribute(guide_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    set = true;
+  }
+  dim3 grid(w.nkt, nrows);
+  guide_sample_kernel<<<grid, 256, smem, st>>>(eps, w.MU, w.SIG, w.ISIG, m, S, md.latent_dim, row0, w.Z, w.QP,
+                                               w.nkt);
+  SMI_LAUNCH_OK();
+  return SMI_OK;
+}
+
+int smi_guide_weights(const SmiModelDesc& md, int m, int S, int nrows, ElboWs& w, cudaStream_t st) {
+  const int warps = nrows * S;
+  guide_weights_kernel<<<(warps + 7) / 8, 256, 0, st>>>(md, w.QP, w.logdet_part, nlb_of(md.latent_dim), w.Z, m, S,
+                                                        nrows, w.nkt, w.W, w.LOGQ);
+  SMI_LAUNCH_OK();
+  return SMI_OK;
+}
+
+template <int MP>
+static int launch_grad(const SmiModelDesc& md, const float* psi, const float* eps, int m, int S, float tau,
+                       int row0, int nrows, ElboWs& w, float* G, float* elbo, cudaStream_t st) {
+  const size_t smem = ((size_t)S * MP + 4 * 64 * 2) * sizeof(float);
+  if (smem > 200 * 1024) SMI_FAIL(SMI_ELIMIT, "guide_grad: S * m too large for shared memory");
+  if (smem > 48 * 1024)
+    SMI_CUDA_OK(cudaFuncSetAttribute(guide_grad_kernel<MP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid(w.nkt, nrows);
+  guide_grad_kernel<MP><<<grid, 256, smem, st>>>(psi, eps, w.MU, w.SIG, w.ISIG, w.W, w.DZ, w.LOGP, w.LOGQ,
+                                                 w.loc_of, w.rho_of, w.tr_of, m, S, md.latent_dim,
+                                                 md.particle_dim, tau, row0, G, elbo);
+  SMI_LAUNCH_OK();
+  return SMI_OK;
+}
+
+int smi_guide_grad(const SmiModelDesc& md, const float* psi, const float* eps, int m, int S, float tau,
+                   int row0, int nrows, ElboWs& w, float* G, float* elbo, cudaStream_t st) {
+  if (m <= 8) return launch_grad<8>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
+  if (m <= 16) return launch_grad<16>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
+  if (m <= 32) return launch_grad<32>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
+  return launch_grad<64>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
+}
+
+int smi_delta_gather(const SmiModelDesc& md, const float* psi, int row0, int nrows, ElboWs& w, cudaStream_t st) {
+  dim3 grid(nlb_of(md.latent_dim), nrows);
+  delta_gather_kernel<<<grid, 256, 0, st>>>(md, psi, row0, w.Z, w.loc_of, w.tr_of);
+  SMI_LAUNCH_OK();
+  return SMI_OK;
+}
+
+int smi_delta_scatter(const SmiModelDesc& md, float tau, int nrows, ElboWs& w, float* G, float* elbo,
+                      cudaStream_t st) {
+  dim3 grid(nlb_of(md.latent_dim), nrows);
+  delta_scatter_kernel<<<grid, 256, 0, st>>>(w.DZ, w.LOGP, w.loc_of, md.latent_dim, md.particle_dim, tau, G, elbo);
+  SMI_LAUNCH_OK();
+  return SMI_OK;
+}

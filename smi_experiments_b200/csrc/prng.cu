@@ -1,0 +1,184 @@
+// Counter-based PRNG of one update on the device.
+//
+// Restates jax.random's threefry2x32 primitives (split / random_bits / normal, in the
+// "partitionable" stream layout) and the key chain NumPyro's seed handler walks inside
+// SteinVI.update: state key -> split(3) -> step key -> split(2)[0] -> per particle -> per ELBO
+// draw -> split(2)[0] = guide key -> one (key, subkey) split per RNG-consuming statement: the
+// data plate first (partial Fisher-Yates subsample, numpyro/primitives.py::_subsample_fn CPU
+// branch, with a one-word multiply-shift randint), then every latent site in model order.
+// Keys enter the reference at src/engine_run.py:42 and experiments/uci_benchmark.py:390.
+// One CTA per (particle row, draw).
+#include <math.h>
+
+#include "common.cuh"
+
+namespace {
+
+__device__ __forceinline__ uint32_t rotl32(uint32_t x, int r) { return __funnelshift_l(x, x, r); }
+
+__device__ __forceinline__ void threefry2x32(uint32_t k0, uint32_t k1, uint32_t x0, uint32_t x1, uint32_t& o0,
+                                             uint32_t& o1) {
+  const uint32_t ks0 = k0, ks1 = k1, ks2 = k0 ^ k1 ^ 0x1BD11BDAu;
+  x0 += ks0;
+  x1 += ks1;
+#define TF_ROUND(r)   \
+  x0 += x1;           \
+  x1 = rotl32(x1, r); \
+  x1 ^= x0;
+  TF_ROUND(13) TF_ROUND(15) TF_ROUND(26) TF_ROUND(6)
+  x0 += ks1;
+  x1 += ks2 + 1u;
+  TF_ROUND(17) TF_ROUND(29) TF_ROUND(16) TF_ROUND(24)
+  x0 += ks2;
+  x1 += ks0 + 2u;
+  TF_ROUND(13) TF_ROUND(15) TF_ROUND(26) TF_ROUND(6)
+  x0 += ks0;
+  x1 += ks1 + 3u;
+  TF_ROUND(17) TF_ROUND(29) TF_ROUND(16) TF_ROUND(24)
+  x0 += ks1;
+  x1 += ks2 + 4u;
+  TF_ROUND(13) TF_ROUND(15) TF_ROUND(26) TF_ROUND(6)
+  x0 += ks2;
+  x1 += ks0 + 5u;
+#undef TF_ROUND
+  o0 = x0;
+  o1 = x1;
+}
+
+struct Key {
+  uint32_t a, b;
+};
+
+// jax.random.split(key, n)[j], partitionable layout: threefry(key, (0, j)).
+__device__ __forceinline__ Key split_at(Key k, uint32_t j) {
+  Key r;
+  threefry2x32(k.a, k.b, 0u, j, r.a, r.b);
+  return r;
+}
+// random_bits(key, 32, shape)[j] for a flat shape with fewer than 2^32 elements.
+__device__ __forceinline__ uint32_t bits_at(Key k, uint32_t j) {
+  uint32_t o0, o1;
+  threefry2x32(k.a, k.b, 0u, j, o0, o1);
+  return o0 ^ o1;
+}
+
+// Giles' single-precision erfinv (the polynomial XLA lowers erf_inv(f32) to).
+__device__ __forceinline__ float erfinv_giles(float x) {
+  float w = -log1pf(-(x * x));
+  float p;
+  if (w < 5.0f) {
+    w -= 2.5f;
+    p = 2.81022636e-08f;
+    p = fmaf(p, w, 3.43273939e-07f);
+    p = fmaf(p, w, -3.5233877e-06f);
+    p = fmaf(p, w, -4.39150654e-06f);
+    p = fmaf(p, w, 0.00021858087f);
+    p = fmaf(p, w, -0.00125372503f);
+    p = fmaf(p, w, -0.00417768164f);
+    p = fmaf(p, w, 0.246640727f);
+    p = fmaf(p, w, 1.50140941f);
+  } else {
+    w = sqrtf(w) - 3.0f;
+    p = -0.000200214257f;
+    p = fmaf(p, w, 0.000100950558f);
+    p = fmaf(p, w, 0.00134934322f);
+    p = fmaf(p, w, -0.00367342844f);
+    p = fmaf(p, w, 0.00573950773f);
+    p = fmaf(p, w, -0.0076224613f);
+    p = fmaf(p, w, 0.00943887047f);
+    p = fmaf(p, w, 1.00167406f);
+    p = fmaf(p, w, 2.83297682f);
+  }
+  return p * x;
+}
+
+// jax.random.normal: uniform on [nextafter(-1, 0), 1) from 23 mantissa bits, sqrt(2) erfinv(u).
+__device__ __forceinline__ float normal_from_bits(uint32_t bits) {
+  const float f = __uint_as_float((bits >> 9) | 0x3F800000u) - 1.0f;
+  const float lo = -0.99999994f;  // nextafter(-1, 0)
+  const float u = fmaxf(lo, __fadd_rn(__fmul_rn(f, 1.0f - lo), lo));
+  return 1.41421356237f * erfinv_giles(u);
+}
+
+__global__ void __launch_bounds__(256)
+prng_step_kernel(const SmiModelDesc md, const uint32_t* __restrict__ key_in, uint32_t* __restrict__ key_out,
+                 int m, int S, int n_total, int B, int row0, float* __restrict__ eps, int32_t* __restrict__ idx) {
+  extern __shared__ int perm[];  // [n_total] + [B] when idx is produced
+  __shared__ Key site_key[SMI_MAX_SITES];
+  __shared__ Key plate_key;
+  const int r = blockIdx.x / S, s = blockIdx.x - r * S;
+  const int L = md.latent_dim;
+  if (threadIdx.x == 0) {
+    const Key state = {key_in[0], key_in[1]};
+    if (blockIdx.x == 0 && key_out) {
+      const Key nk = split_at(state, 0);
+      key_out[0] = nk.a;
+      key_out[1] = nk.b;
+    }
+    const Key step = split_at(state, 2);
+    const Key attractive = split_at(step, 0);
+    const Key pk = split_at(attractive, (uint32_t)(row0 + r));
+    const Key dk = split_at(pk, (uint32_t)s);
+    Key key = split_at(dk, 0);  // guide key
+    if (n_total > 0) {          // the data plate consumes the first subkey
+      plate_key = split_at(key, 1);
+      key = split_at(key, 0);
+    }
+    for (int t = 0; t < md.n_sites; ++t) {
+      site_key[t] = split_at(key, 1);
+      key = split_at(key, 0);
+    }
+  }
+  __syncthreads();
+  if (eps) {
+    float* out = eps + ((size_t)r * S + s) * L;
+    for (int t = 0; t < md.n_sites; ++t) {
+      const Key k = site_key[t];
+      const int n = md.sites[t].size, off = md.sites[t].lat;
+      for (int q = threadIdx.x; q < n; q += blockDim.x) out[off + q] = normal_from_bits(bits_at(k, (uint32_t)q));
+    }
+  }
+  if (idx) {
+    int* jt = perm + n_total;
+    for (int t = threadIdx.x; t < n_total; t += blockDim.x) perm[t] = t;
+    for (int t = threadIdx.x; t < B; t += blockDim.x) {
+      const Key kt = split_at(plate_key, (uint32_t)t);
+      const uint32_t bits = bits_at(kt, 0u);
+      jt[t] = (int)(((unsigned long long)bits * (unsigned long long)(n_total - t)) >> 32);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      for (int t = 0; t < B; ++t) {
+        const int i = n_total - 1 - t, j = jt[t];
+        const int a = perm[i];
+        perm[i] = perm[j];
+        perm[j] = a;
+      }
+    }
+    __syncthreads();
+    int32_t* out = idx + ((size_t)r * S + s) * B;
+    for (int b = threadIdx.x; b < B; b += blockDim.x) out[b] = perm[n_total - B + b];
+  }
+}
+
+}  // namespace
+
+SMI_API int smi_prng_step_f32(const SmiModelDesc* md, const uint32_t* key_in, uint32_t* key_out, int m, int S,
+                              int n_total, int B, int row0, int nrows, float* eps, int32_t* idx, void* stream) {
+  if (!md || !key_in) SMI_FAIL(SMI_EINVAL, "smi_prng_step_f32: null pointer");
+  if (key_out == key_in) SMI_FAIL(SMI_EINVAL, "smi_prng_step_f32: key_out must not alias key_in");
+  if (m < 1 || S < 1 || nrows < 1 || row0 < 0 || row0 + nrows > m) SMI_FAIL(SMI_EINVAL, "smi_prng_step_f32: bad rows");
+  if (md->guide != SMI_GUIDE_NORMAL) eps = nullptr;
+  size_t smem = 0;
+  if (idx) {
+    if (n_total < 1 || B < 1 || B > n_total) SMI_FAIL(SMI_EINVAL, "smi_prng_step_f32: subsample %d of %d", B, n_total);
+    smem = ((size_t)n_total + B) * sizeof(int);
+    if (smem > 200 * 1024) SMI_FAIL(SMI_ELIMIT, "smi_prng_step_f32: plate of %d rows exceeds shared memory", n_total);
+    if (smem > 48 * 1024)
+      SMI_CUDA_OK(cudaFuncSetAttribute(prng_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  }
+  prng_step_kernel<<<nrows * S, 256, smem, (cudaStream_t)stream>>>(*md, key_in, key_out, m, S, n_total, B, row0, eps,
+                                                                   idx);
+  SMI_LAUNCH_OK();
+  return SMI_OK;
+}

@@ -1,0 +1,242 @@
+// Exact median bandwidth by radix select over the squared-distance matrix (row a4, K2).
+//
+// Replaces numpyro stein_util.median_bandwidth = jnp.median(D)**2 / ln m + eps, which XLA
+// evaluates with a full sort of m^2 floats.  D2 >= 0, so the uint32 bit patterns order like
+// the values and sqrt is monotone: the order statistics of D = sqrt(D2) are the sqrt of the
+// order statistics of D2.  Three histogram passes (11 + 11 + 10 bits) find the value at
+// rank `lo`; a fourth pass counts elements <= it and takes the minimum above it, which
+// gives rank `hi` (hi is lo or lo + 1).  All counters are integers: the result does not
+// depend on summation order, and in the sharded layout the per-rank histograms are summed
+// with an integer all-reduce between `hist` and `scan` (see smi_experiments_b200/dist.py).
+// HBM traffic: 4 reads of D2 = 16 bytes per matrix element.
+#include <math.h>
+
+#include "common.cuh"
+#include "select.cuh"
+
+namespace {
+
+constexpr int kBins = 2048;
+constexpr int kThreads = 256;
+
+__host__ __device__ inline int pass_shift(int p) { return p == 0 ? 21 : (p == 1 ? 10 : 0); }
+__host__ __device__ inline int pass_bits(int p) { return p == 2 ? 10 : 11; }
+
+// state: [0] prefix (high bits found so far, right-aligned), [1] remaining rank,
+//        [2] value a (rank lo), [3] count(<= a) , [4] min(> a)
+__device__ __forceinline__ void hist_add(unsigned* sh, unsigned key, bool valid, int shift, int bits) {
+  const unsigned digit = (key >> shift) & ((1u << bits) - 1u);
+  const unsigned act = __ballot_sync(0xffffffffu, valid);
+  if (valid) {
+    const unsigned peers = __match_any_sync(act, digit);
+    const int leader = __ffs(peers) - 1;
+    if ((int)(threadIdx.x & 31) == leader) atomicAdd(sh + digit, (unsigned)__popc(peers));
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+select_hist(const unsigned* __restrict__ keys, size_t n, int pass, const unsigned* __restrict__ state,
+            unsigned* __restrict__ hist) {
+  __shared__ unsigned sh[kBins];
+  for (int t = threadIdx.x; t < kBins; t += blockDim.x) sh[t] = 0u;
+  __syncthreads();
+  const int shift = pass_shift(pass), bits = pass_bits(pass);
+  const unsigned prefix = pass == 0 ? 0u : state[0];
+  const int hs = shift + bits;  // bits above this pass's digit
+  const size_t n4 = n / 4;
+  const uint4* k4 = reinterpret_cast<const uint4*>(keys);
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  // every lane of a warp runs the same trip count (ballot/match need the full warp)
+  const size_t base = (size_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31);
+  for (size_t i0 = base; i0 < n4; i0 += stride) {
+    const size_t i = i0 + (threadIdx.x & 31);
+    const bool in = i < n4;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (in) v = k4[i];
+    hist_add(sh, v.x, in && (pass == 0 || (v.x >> hs) == prefix), shift, bits);
+    hist_add(sh, v.y, in && (pass == 0 || (v.y >> hs) == prefix), shift, bits);
+    hist_add(sh, v.z, in && (pass == 0 || (v.z >> hs) == prefix), shift, bits);
+    hist_add(sh, v.w, in && (pass == 0 || (v.w >> hs) == prefix), shift, bits);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < 32) {  // tail (n % 4 elements)
+    const size_t i = n4 * 4 + threadIdx.x;
+    const bool in = i < n;
+    const unsigned key = in ? keys[i] : 0u;
+    hist_add(sh, key, in && (pass == 0 || (key >> hs) == prefix), shift, bits);
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < kBins; t += blockDim.x)
+    if (sh[t]) atomicAdd(hist + t, sh[t]);
+}
+
+// One warp: locate the bin holding the remaining rank, update the state, clear the histogram.
+__global__ void select_scan(unsigned* __restrict__ hist, int pass, unsigned rank0, unsigned* __restrict__ state) {
+  const int lane = threadIdx.x;
+  const int nb = 1 << pass_bits(pass);
+  const int per = nb / 32;
+  unsigned rank = pass == 0 ? rank0 : state[1];
+  unsigned mine = 0;
+  for (int b = 0; b < per; ++b) mine += hist[lane * per + b];
+  unsigned incl = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  const unsigned excl = incl - mine;
+  const bool owner = rank >= excl && rank < incl;
+  if (owner) {
+    unsigned r = rank - excl;
+    int b = 0;
+    for (; b < per; ++b) {
+      const unsigned c = hist[lane * per + b];
+      if (r < c) break;
+      r -= c;
+    }
+    const unsigned prefix = pass == 0 ? 0u : state[0];
+    state[0] = (prefix << pass_bits(pass)) | (unsigned)(lane * per + b);
+    state[1] = r;
+    if (pass == 2) {
+      state[2] = state[0];
+      state[3] = 0u;
+      state[4] = 0xffffffffu;
+    }
+  }
+  __syncwarp();
+  for (int b = lane; b < kBins; b += 32) hist[b] = 0u;
+}
+
+__global__ void __launch_bounds__(kThreads)
+select_tail(const unsigned* __restrict__ keys, size_t n, unsigned* __restrict__ state) {
+  const unsigned a = state[2];
+  unsigned cnt = 0, mn = 0xffffffffu;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  const size_t n4 = n / 4;
+  const uint4* k4 = reinterpret_cast<const uint4*>(keys);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    const uint4 v = k4[i];
+    cnt += (v.x <= a) + (v.y <= a) + (v.z <= a) + (v.w <= a);
+    if (v.x > a) mn = min(mn, v.x);
+    if (v.y > a) mn = min(mn, v.y);
+    if (v.z > a) mn = min(mn, v.z);
+    if (v.w > a) mn = min(mn, v.w);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    const unsigned k = keys[n4 * 4 + threadIdx.x];
+    cnt += k <= a;
+    if (k > a) mn = min(mn, k);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (cnt) atomicAdd(state + 3, cnt);
+    if (mn != 0xffffffffu) atomicMin(state + 4, mn);
+  }
+}
+
+__global__ void select_finish(const unsigned* __restrict__ state, const unsigned* __restrict__ cnt_le,
+                              const unsigned* __restrict__ min_gt, unsigned rank_hi, float factor,
+                              float alpha, int m, float* __restrict__ h_out, float* __restrict__ scal,
+                              unsigned* __restrict__ rank_out) {
+  const unsigned a = state[2];
+  const unsigned b = rank_hi < *cnt_le ? a : *min_gt;
+  const float med = (sqrtf(__uint_as_float(a)) + sqrtf(__uint_as_float(b))) * 0.5f;
+  const float h = __fadd_rn(__fmul_rn(__fmul_rn(med, med), factor), 1.1920929e-07f);
+  if (h_out) *h_out = h;
+  if (scal) {
+    scal[0] = h;
+    scal[1] = (2.0f * alpha) / (h * (float)m);
+  }
+  if (rank_out) {
+    rank_out[0] = a;
+    rank_out[1] = b;
+  }
+}
+
+__global__ void select_fixed_h(float h, float alpha, int m, float* __restrict__ h_out, float* __restrict__ scal) {
+  if (h_out) *h_out = h;
+  if (scal) {
+    scal[0] = h;
+    scal[1] = (2.0f * alpha) / (h * (float)m);
+  }
+}
+
+int hist_grid() { return smi_num_sms() * 4; }
+
+}  // namespace
+
+size_t smi_select_workspace_bytes() { return 256 + kBins * sizeof(unsigned) + 256; }
+
+int smi_select_hist(const float* D2, size_t n, int pass, unsigned* state, unsigned* hist, cudaStream_t st) {
+  select_hist<<<hist_grid(), kThreads, 0, st>>>((const unsigned*)D2, n, pass, state, hist);
+  SMI_LAUNCH_OK();
+  return SMI_OK;
+}
+
+int smi_select_scan(unsigned* hist, int pass, unsigned long long rank_lo, unsigned* state, cudaStream_t st) {
+  select_scan<<<1, 32, 0, st>>>(hist, pass, (unsigned)rank_lo, state);
+  SMI_LAUNCH_OK();
+  return SMI_OK;
+}
+
+int smi_select_tail(const float* D2, size_t n, unsigned* state, cudaStream_t st) {
+  select_tail<<<hist_grid(), kThreads, 0, st>>>((const unsigned*)D2, n, state);
+  SMI_LAUNCH_OK();
+  return SMI_OK;
+}
+
+int smi_select_finish(const unsigned* state, const unsigned* cnt_le, const unsigned* min_gt,
+                      unsigned long long rank_hi, int m, float alpha, float* h_out, float* scal,
+                      unsigned* rank_out, cudaStream_t st) {
+  const float factor = m > 1 ? (float)(1.0 / log((double)m)) : 1.0f;
+  select_finish<<<1, 1, 0, st>>>(state, cnt_le ? cnt_le : state + 3, min_gt ? min_gt : state + 4, (unsigned)rank_hi, factor, alpha, m, h_out, scal, rank_out);
+  SMI_LAUNCH_OK();
+  return SMI_OK;
+}
+
+int smi_select_fixed(float h, int m, float alpha, float* h_out, float* scal, cudaStream_t st) {
+  select_fixed_h<<<1, 1, 0, st>>>(h, alpha, m, h_out, scal);
+  SMI_LAUNCH_OK();
+  return SMI_OK;
+}
+
+// Whole single-GPU select: D2 is the full (m x m) matrix.
+int smi_select_bandwidth(const float* D2, int m, int median_mode, float alpha, float* h_out, float* scal,
+                         unsigned* rank_out, void* ws, size_t ws_bytes, cudaStream_t st) {
+  if (ws_bytes < smi_select_workspace_bytes()) SMI_FAIL(SMI_ENOSPC, "select workspace too small");
+  if (m == 1) return smi_select_fixed(1.0f, m, alpha, h_out, scal, st);
+  SmiArena ar(ws, ws_bytes);
+  unsigned* state = ar.take<unsigned>(8);
+  unsigned* hist = ar.take<unsigned>(kBins);
+  const size_t n = (size_t)m * m;
+  if (n > 0xffffffffull) SMI_FAIL(SMI_ELIMIT, "select: m*m exceeds 2^32");
+  long long lo, hi;
+  smi_median_ranks((long long)n, median_mode, &lo, &hi);
+  SMI_CUDA_OK(cudaMemsetAsync(hist, 0, kBins * sizeof(unsigned), st));
+  for (int p = 0; p < 3; ++p) {
+    int rc = smi_select_hist(D2, n, p, state, hist, st);
+    if (rc) return rc;
+    rc = smi_select_scan(hist, p, (unsigned long long)lo, state, st);
+    if (rc) return rc;
+  }
+  int rc = smi_select_tail(D2, n, state, st);
+  if (rc) return rc;
+  return smi_select_finish(state, nullptr, nullptr, (unsigned long long)hi, m, alpha, h_out, scal, rank_out, st);
+}
+
+SMI_API size_t smi_median_bandwidth_workspace_bytes(int m) {
+  (void)m;
+  return smi_select_workspace_bytes();
+}
+
+SMI_API int smi_median_bandwidth_f32(const float* D2, int m, int median_mode, float* h, uint32_t* rank_out,
+                                     void* ws, size_t ws_bytes, void* stream) {
+  if (!D2 || !h || !ws) SMI_FAIL(SMI_EINVAL, "smi_median_bandwidth_f32: null pointer");
+  if (m < 1) SMI_FAIL(SMI_EINVAL, "smi_median_bandwidth_f32: m=%d", m);
+  if (((uintptr_t)D2 & 15) != 0) SMI_FAIL(SMI_EINVAL, "smi_median_bandwidth_f32: D2 must be 16-byte aligned");
+  return smi_select_bandwidth(D2, m, median_mode, 1.0f, h, nullptr, rank_out, ws, ws_bytes,
+                              (cudaStream_t)stream);
+}

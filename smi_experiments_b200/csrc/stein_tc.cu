@@ -1,0 +1,353 @@
+// tcgen05 Stein-force path (any m; the path config C5 takes): split planes -> 3xTF32 Gram
+// GEMM with the distance epilogue -> exact radix-select bandwidth -> K = exp(-D2/h) planes and
+// row sums -> Y^T planes -> 3xTF32 force GEMM with the repulsive-term epilogue -> |F|_F.
+//
+// Replaces NumPyro's RBFKernel.compute + _apply_kernel + _kernel_grad + force sum (SURVEY.md
+// rows a4-a7) in the GEMM form of Appendix A.4:
+//     F = K (c_att G - c X) + c rowsum(K) * X,   c = 2 alpha / (h m),   K = exp(-D2 / h).
+// Unlike the small-m kernel, K is evaluated from the Gram-form D2 (the difference form is an
+// m x m x d broadcast); see DESIGN.md "numerics of the tensor path".
+// `rows` < m selects a block of particle rows (particle-row sharding): B operands
+// always span all m particles.
+#include <math.h>
+
+#include "common.cuh"
+#include "select.cuh"
+#include "stein_tc.cuh"
+#include "tc_gemm.cuh"
+
+namespace {
+
+// ---- elementwise preparation kernels ------------------------------------------------------
+__device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
+  hi = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);  // top 19 bits: exactly a tf32 value
+  lo = x - hi;                                            // exact in fp32
+}
+
+// One CTA per particle row: X row -> hi / lo planes (zero padded to ld) + squared norm.
+__global__ void __launch_bounds__(256)
+split_rows_kernel(const float* __restrict__ X, int d, int ld, float* __restrict__ Xh, float* __restrict__ Xl,
+                  float* __restrict__ norms) {
+  __shared__ double red[32];
+  const int row = blockIdx.x;
+  const float* x = X + (size_t)row * d;
+  float* h = Xh + (size_t)row * ld;
+  float* l = Xl + (size_t)row * ld;
+  double s = 0.0;
+  for (int k = threadIdx.x; k < ld; k += blockDim.x) {
+    float v = k < d ? __ldg(x + k) : 0.f, hi, lo;
+    split_tf32(v, hi, lo);
+    h[k] = hi;
+    l[k] = lo;
+    s += (double)v * (double)v;
+  }
+  s = block_sum(s, red);
+  if (threadIdx.x == 0) norms[row] = (float)s;
+}
+
+// One CTA per local row: K = exp(-D2/h) -> hi / lo planes (zero padded) + row sum.
+__global__ void __launch_bounds__(256)
+kmat_rows_kernel(const float* __restrict__ D2, int m, int ldm, const float* __restrict__ scal,
+                 float* __restrict__ Kh, float* __restrict__ Kl, float* __restrict__ rowsum) {
+  __shared__ double red[32];
+  const int row = blockIdx.x;
+  const float h = scal[0];
+  const float* drow = D2 + (size_t)row * m;
+  float* kh = Kh + (size_t)row * ldm;
+  float* kl = Kl + (size_t)row * ldm;
+  double s = 0.0;
+  for (int j = threadIdx.x; j < ldm; j += blockDim.x) {
+    float kv = 0.f, hi, lo;
+    if (j < m) kv = expf(-__ldg(drow + j) / h);
+    split_tf32(kv, hi, lo);
+    kh[j] = hi;
+    kl[j] = lo;
+    s += (double)kv;
+  }
+  s = block_sum(s, red);
+  if (threadIdx.x == 0) rowsum[row] = (float)s;
+}
+
+// Y = c_att G - c X, transposed into (d x ldm) hi / lo planes through a 32 x 32 smem tile.
+__global__ void __launch_bounds__(256)
+ysplit_t_kernel(const float* __restrict__ X, const float* __restrict__ G, int m, int d, int ldm, float c_att,
+                const float* __restrict__ scal, float* __restrict__ Yh, float* __restrict__ Yl) {
+  __shared__ float tile[32][33];
+  const float c = scal[1];
+  const int j0 = blockIdx.y * 32, k0 = blockIdx.x * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  for (int r = ty; r < 32; r += 8) {
+    const int j = j0 + r, k = k0 + tx;
+    float y = 0.f;
+    if (j < m && k < d) y = c_att * __ldg(G + (size_t)j * d + k) - c * __ldg(X + (size_t)j * d + k);
+    tile[r][tx] = y;
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    const int k = k0 + r, j = j0 + tx;
+    if (k < d && j < ldm) {
+      float hi, lo;
+      split_tf32(tile[tx][r], hi, lo);
+      Yh[(size_t)k * ldm + j] = hi;
+      Yl[(size_t)k * ldm + j] = lo;
+    }
+  }
+}
+
+__global__ void loss_finish_kernel(const double* __restrict__ lpart, int n, float* __restrict__ loss) {
+  __shared__ double red[32];
+  double t = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) t += lpart[i];
+  t = block_sum(t, red);
+  if (threadIdx.x == 0) *loss = (float)sqrt(t);
+}
+
+__global__ void sumsq_finish_kernel(const double* __restrict__ lpart, int n, double* __restrict__ out) {
+  __shared__ double red[32];
+  double t = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) t += lpart[i];
+  t = block_sum(t, red);
+  if (threadIdx.x == 0) *out = t;
+}
+
+// ---- TMA descriptors ----------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      return nullptr;
+    fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// Plane [rows x ld] fp32, K-major; box = 32 x box_rows, SWIZZLE_128B, OOB rows read as zero.
+int make_map(CUtensorMap* map, const float* base, long long rows, long long ld, int box_rows) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) SMI_FAIL(SMI_ECUDA, "cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t dims[2] = {(cuuint64_t)ld, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(float)};
+  cuuint32_t box[2] = {(cuuint32_t)tc::BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) SMI_FAIL(SMI_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return SMI_OK;
+}
+
+template <int EPI>
+int launch_gemm(const float* Ah, const float* Al, long long a_rows, const float* Bh, const float* Bl,
+                long long b_rows, long long ldk, tc::GemmArgs ga, cudaStream_t st) {
+  CUtensorMap ma_h, ma_l, mb_h, mb_l;
+  int rc;
+  if ((rc = make_map(&ma_h, Ah, a_rows, ldk, tc::BM))) return rc;
+  if ((rc = make_map(&ma_l, Al, a_rows, ldk, tc::BM))) return rc;
+  if ((rc = make_map(&mb_h, Bh, b_rows, ldk, tc::BN))) return rc;
+  if ((rc = make_map(&mb_l, Bl, b_rows, ldk, tc::BN))) return rc;
+  ga.K = (int)ldk;
+  ga.tiles_m = (ga.M + tc::BM - 1) / tc::BM;
+  ga.tiles_n = (ga.N + tc::BN - 1) / tc::BN;
+  const int ntiles = ga.tiles_m * ga.tiles_n;
+  const int grid = ntiles < smi_num_sms() ? ntiles : smi_num_sms();
+  static bool attr_set[2] = {false, false};
+  if (!attr_set[EPI]) {
+    SMI_CUDA_OK(cudaFuncSetAttribute(tc::gemm3xtf32_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)tc::kSmemBytes));
+    attr_set[EPI] = true;
+  }
+  tc::gemm3xtf32_kernel<EPI><<<grid, tc::kThreads, tc::kSmemBytes, st>>>(ma_h, ma_l, mb_h, mb_l, ga);
+  SMI_LAUNCH_OK();
+  return SMI_OK;
+}
+
+inline int pad32(int v) { return (v + 31) / 32 * 32; }
+
+struct TcWs {
+  float *Xh, *Xl, *norms, *D2, *Kh, *Kl, *rowsum, *Yh, *Yl, *scal;
+  double* lpart;
+  void* sel;
+};
+
+size_t carve(SmiArena& ar, TcWs& w, int rows, int m, int d) {
+  const int ldk = pad32(d), ldm = pad32(m);
+  w.Xh = ar.take<float>((size_t)m * ldk);
+  w.Xl = ar.take<float>((size_t)m * ldk);
+  w.norms = ar.take<float>(m);
+  w.D2 = ar.take<float>((size_t)rows * m);
+  w.Kh = ar.take<float>((size_t)rows * ldm);
+  w.Kl = ar.take<float>((size_t)rows * ldm);
+  w.rowsum = ar.take<float>(rows);
+  w.Yh = ar.take<float>((size_t)d * ldm);
+  w.Yl = ar.take<float>((size_t)d * ldm);
+  w.scal = ar.take<float>(4);
+  w.lpart = ar.take<double>(256);
+  w.sel = ar.take<char>(smi_select_workspace_bytes());
+  return ar.off;
+}
+
+}  // namespace
+
+// ---- orchestration ------------------------------------------------------------------------
+size_t smi_stein_tc_workspace_bytes(int rows, int m, int d) {
+  SmiArena ar(nullptr, 0);
+  TcWs w;
+  return carve(ar, w, rows, m, d) + 512;
+}
+
+// Stage 1: split planes, norms, Gram GEMM -> D2 rows [row0, row0+rows) x m (compact, ld = m).
+static int tc_dist_rows(const float* X, int m, int d, int row0, int rows, TcWs& w, float* D2, cudaStream_t st) {
+  const int ldk = pad32(d);
+  split_rows_kernel<<<m, 256, 0, st>>>(X, d, ldk, w.Xh, w.Xl, w.norms);
+  SMI_LAUNCH_OK();
+  tc::GemmArgs ga = {};
+  ga.M = rows;
+  ga.N = m;
+  ga.C = D2;
+  ga.ldc = m;
+  ga.na = w.norms + row0;
+  ga.nb = w.norms;
+  return launch_gemm<tc::EPI_GRAM>(w.Xh + (size_t)row0 * ldk, w.Xl + (size_t)row0 * ldk, rows, w.Xh, w.Xl, m,
+                                   ldk, ga, st);
+}
+
+// Stage 3: K planes, Y^T planes, force GEMM, loss partials.
+static int tc_force_rows(const float* X, const float* G, int m, int d, int row0, int rows, float c_att,
+                         TcWs& w, float* F, cudaStream_t st) {
+  const int ldm = pad32(m);
+  kmat_rows_kernel<<<rows, 256, 0, st>>>(w.D2, m, ldm, w.scal, w.Kh, w.Kl, w.rowsum);
+  SMI_LAUNCH_OK();
+  dim3 yg((d + 31) / 32, ldm / 32);
+  ysplit_t_kernel<<<yg, 256, 0, st>>>(X, G, m, d, ldm, c_att, w.scal, w.Yh, w.Yl);
+  SMI_LAUNCH_OK();
+  tc::GemmArgs ga = {};
+  ga.M = rows;
+  ga.N = d;
+  ga.C = F;
+  ga.ldc = d;
+  ga.X = X + (size_t)row0 * d;
+  ga.ldx = d;
+  ga.rowsum = w.rowsum;
+  ga.scal = w.scal;
+  ga.lpart = w.lpart;
+  SMI_CUDA_OK(cudaMemsetAsync(w.lpart, 0, 256 * sizeof(double), st));
+  return launch_gemm<tc::EPI_FORCE>(w.Kh, w.Kl, rows, w.Yh, w.Yl, d, ldm, ga, st);
+}
+
+int smi_stein_tc_run(const float* X, const float* G, int m, int d, int row0, int rows, float c_att,
+                     float alpha, int median_mode, float h_fixed, float* F, float* loss, float* h, void* ws,
+                     size_t ws_bytes, cudaStream_t st) {
+  if (!F) SMI_FAIL(SMI_EINVAL, "tensor-core Stein path needs an F output buffer");
+  if (rows != m || row0 != 0) SMI_FAIL(SMI_EINVAL, "smi_stein_tc_run handles the unsharded case; use the staged API");
+  if (ws_bytes < smi_stein_tc_workspace_bytes(rows, m, d)) SMI_FAIL(SMI_ENOSPC, "stein workspace too small");
+  if ((((uintptr_t)X | (uintptr_t)G | (uintptr_t)F) & 15) != 0)
+    SMI_FAIL(SMI_EINVAL, "X, G, F must be 16-byte aligned");
+  SmiArena ar(ws, ws_bytes);
+  TcWs w;
+  carve(ar, w, rows, m, d);
+  int rc;
+  if (h_fixed > 0.f || m == 1) {
+    if ((rc = smi_select_fixed(h_fixed > 0.f ? h_fixed : 1.0f, m, alpha, h, w.scal, st))) return rc;
+    if ((rc = tc_dist_rows(X, m, d, row0, rows, w, w.D2, st))) return rc;
+  } else {
+    if ((rc = tc_dist_rows(X, m, d, row0, rows, w, w.D2, st))) return rc;
+    if ((rc = smi_select_bandwidth(w.D2, m, median_mode, alpha, h, w.scal, nullptr, w.sel,
+                                   smi_select_workspace_bytes(), st)))
+      return rc;
+  }
+  if ((rc = tc_force_rows(X, G, m, d, row0, rows, c_att, w, F, st))) return rc;
+  loss_finish_kernel<<<1, 256, 0, st>>>(w.lpart, 256, loss);
+  SMI_LAUNCH_OK();
+  return SMI_OK;
+}
+
+int smi_stein_tc_sqdist(const float* X, int m, int d, float* D2, void* ws, size_t ws_bytes, cudaStream_t st) {
+  if (ws_bytes < smi_stein_tc_workspace_bytes(m, m, d)) SMI_FAIL(SMI_ENOSPC, "stein workspace too small");
+  SmiArena ar(ws, ws_bytes);
+  TcWs w;
+  carve(ar, w, m, m, d);
+  return tc_dist_rows(X, m, d, 0, m, w, D2, st);
+}
+
+// ---- staged, row-sharded API -------------------------------------------------
+// One process per GPU owns particle rows [row0, row0 + rows).  X and G hold ALL m particles
+// (the caller all-gathers them over NCCL).  Between the stages the caller reduces three small
+// integer / scalar buffers across ranks:
+//     stage_dist -> [hist(p) -> all-reduce SUM hist -> scan(p)] for p = 0, 1, 2
+//                -> tail -> all-reduce SUM cnt_le, MIN min_gt -> bandwidth
+//                -> force -> all-reduce SUM sumsq -> loss = sqrt(sumsq)
+// Integer reductions are exact, so h is bit-identical for every world size.
+SMI_API size_t smi_stein_rows_workspace_bytes(int rows, int m, int d) {
+  return smi_stein_tc_workspace_bytes(rows, m, d);
+}
+
+#define ROWS_PROLOGUE()                                                                           \
+  if (!ws || rows < 1 || row0 < 0 || row0 + rows > m) SMI_FAIL(SMI_EINVAL, "stein_rows: bad rows"); \
+  if (ws_bytes < smi_stein_tc_workspace_bytes(rows, m, d)) SMI_FAIL(SMI_ENOSPC, "stein workspace too small"); \
+  SmiArena ar(ws, ws_bytes);                                                                      \
+  TcWs w;                                                                                         \
+  carve(ar, w, rows, m, d);                                                                       \
+  cudaStream_t st = (cudaStream_t)stream;                                                         \
+  unsigned* state = (unsigned*)w.sel;                                                             \
+  (void)state;                                                                                    \
+  (void)st
+
+SMI_API int smi_stein_rows_dist(const float* X, int m, int d, int row0, int rows, void* ws, size_t ws_bytes,
+                                void* stream) {
+  ROWS_PROLOGUE();
+  return tc_dist_rows(X, m, d, row0, rows, w, w.D2, st);
+}
+
+// hist: caller-owned 2048 x uint32 device buffer, zero on entry for pass 0 (scan re-zeroes it).
+SMI_API int smi_stein_rows_hist(int m, int d, int row0, int rows, int pass, uint32_t* hist, void* ws,
+                                size_t ws_bytes, void* stream) {
+  ROWS_PROLOGUE();
+  return smi_select_hist(w.D2, (size_t)rows * m, pass, state, hist, st);
+}
+
+SMI_API int smi_stein_rows_scan(int m, int d, int row0, int rows, int pass, int median_mode, uint32_t* hist,
+                                void* ws, size_t ws_bytes, void* stream) {
+  ROWS_PROLOGUE();
+  long long lo, hi;
+  smi_median_ranks((long long)m * m, median_mode, &lo, &hi);
+  return smi_select_scan(hist, pass, (unsigned long long)lo, state, st);
+}
+
+// cnt_min: caller-owned uint32[2] = {count(<= a), min(> a)} of the local rows.
+SMI_API int smi_stein_rows_tail(int m, int d, int row0, int rows, uint32_t* cnt_min, void* ws, size_t ws_bytes,
+                                void* stream) {
+  ROWS_PROLOGUE();
+  int rc = smi_select_tail(w.D2, (size_t)rows * m, state, st);
+  if (rc) return rc;
+  SMI_CUDA_OK(cudaMemcpyAsync(cnt_min, state + 3, 2 * sizeof(unsigned), cudaMemcpyDeviceToDevice, st));
+  return SMI_OK;
+}
+
+SMI_API int smi_stein_rows_bandwidth(int m, int d, int row0, int rows, int median_mode, float alpha,
+                                     float h_fixed, const uint32_t* cnt_le, const uint32_t* min_gt, float* h,
+                                     void* ws, size_t ws_bytes, void* stream) {
+  ROWS_PROLOGUE();
+  if (h_fixed > 0.f || m == 1) return smi_select_fixed(h_fixed > 0.f ? h_fixed : 1.0f, m, alpha, h, w.scal, st);
+  long long lo, hi;
+  smi_median_ranks((long long)m * m, median_mode, &lo, &hi);
+  return smi_select_finish(state, cnt_le, min_gt, (unsigned long long)hi, m, alpha, h, w.scal, nullptr, st);
+}
+
+// F_rows: (rows, d) out.  sumsq: device double, sum of F^2 over the local rows.
+SMI_API int smi_stein_rows_force(const float* X, const float* G, int m, int d, int row0, int rows, float c_att,
+                                 float* F_rows, double* sumsq, void* ws, size_t ws_bytes, void* stream) {
+  ROWS_PROLOGUE();
+  int rc = tc_force_rows(X, G, m, d, row0, rows, c_att, w, F_rows, st);
+  if (rc) return rc;
+  sumsq_finish_kernel<<<1, 256, 0, st>>>(w.lpart, 256, sumsq);
+  SMI_LAUNCH_OK();
+  return SMI_OK;
+}
