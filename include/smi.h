@@ -98,6 +98,15 @@ int smi_version(void);
 const char* smi_last_error(void);
 /* 0 when the current device is compute capability 10.x, SMI_EARCH otherwise. */
 int smi_device_check(void);
+/* Number of kernels libsmi has launched from the calling thread since the last reset (launches
+ * replayed by a CUDA graph are not seen here: count one eager step).  reset != 0 zeroes it.   */
+long long smi_launch_count(int reset);
+/* Per-kernel timing for the roofline report: while enabled, CUDA events are recorded on the
+ * launching stream around the hot kernels.  smi_profile(1) clears and starts, smi_profile(0)
+ * stops; smi_profile_report synchronises the device and writes one "name count total_ms" line
+ * per kernel into buf (host).  Not for use during CUDA-graph capture.                        */
+int smi_profile(int on);
+int smi_profile_report(char* buf, size_t cap);
 
 /* ---- Stein force: replaces RBFKernel.compute + _apply_kernel + _kernel_grad + force sum
  *      + ||F|| (NumPyro steinvi.py::_svgd_loss_and_grads).
@@ -181,6 +190,23 @@ int smi_elbo_grad_f32(const SmiModelDesc* md, const float* psi, const float* eps
 int smi_prng_step_f32(const SmiModelDesc* md, const uint32_t* key_in, uint32_t* key_out, int m,
                       int S, int n_total, int B, int row0, int nrows, float* eps, int32_t* idx,
                       void* stream);
+
+/* jax.random primitives on the device (partitionable threefry layout), used by engine.init
+ * (numpyro init_to_uniform / guide initialisation) and exposed for known-answer tests.
+ *   smi_prng_split      : keys_out (num, 2) = jax.random.split(key, num)
+ *   smi_prng_uniform_f32: out (n) = jax.random.uniform(key, (n,), minval=lo, maxval=hi)
+ *   smi_prng_normal_f32 : out (n) = jax.random.normal(key, (n,))
+ *   smi_prng_bits_u32   : out (n) = jax.random.bits(key, (n,), uint32)                      */
+int smi_prng_split(const uint32_t* key, int num, uint32_t* keys_out, void* stream);
+int smi_prng_uniform_f32(const uint32_t* key, size_t n, float lo, float hi, float* out, void* stream);
+int smi_prng_normal_f32(const uint32_t* key, size_t n, float* out, void* stream);
+int smi_prng_bits_u32(const uint32_t* key, size_t n, uint32_t* out, void* stream);
+
+/* ---- Loss collection without a host sync (SteinVI.run's fori_collect of the per-step loss;
+ *      replaces the per-step device_get at reference src/engine_run.py:56).
+ *   ring[(step - 1) mod ring_len] = *loss, `step` being the device counter the optimizer
+ *   bumped for this update.                                                               */
+int smi_loss_record_f32(const float* loss, const int32_t* step, float* ring, int ring_len, void* stream);
 
 #ifdef __cplusplus
 }

@@ -13,6 +13,14 @@ void smi_set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+thread_local long long g_smi_launches = 0;
+
+SMI_API long long smi_launch_count(int reset) {
+  const long long v = g_smi_launches;
+  if (reset) g_smi_launches = 0;
+  return v;
+}
+
 SMI_API int smi_version(void) { return SMI_VERSION; }
 
 SMI_API const char* smi_last_error(void) { return g_err; }
@@ -37,4 +45,77 @@ int smi_num_sms() {
     cached_dev = dev;
   }
   return cached;
+}
+
+// ---- per-kernel timing ---------------------------------------------------------------------
+bool g_smi_prof_on = false;
+namespace {
+constexpr int kMaxRec = 8192;
+struct ProfRec {
+  const char* name;
+  cudaEvent_t e0, e1;
+};
+ProfRec g_rec[kMaxRec];
+int g_nrec = 0, g_nevents = 0;
+bool g_open = false;
+}  // namespace
+
+void smi_prof_begin_(cudaStream_t st) {
+  if (g_nrec >= kMaxRec) return;
+  ProfRec& r = g_rec[g_nrec];
+  if (g_nrec >= g_nevents) {
+    if (cudaEventCreate(&r.e0) != cudaSuccess || cudaEventCreate(&r.e1) != cudaSuccess) return;
+    g_nevents = g_nrec + 1;
+  }
+  cudaEventRecord(r.e0, st);
+  g_open = true;
+}
+
+void smi_prof_end_(const char* name, cudaStream_t st) {
+  if (!g_open || g_nrec >= kMaxRec) return;
+  ProfRec& r = g_rec[g_nrec];
+  r.name = name;
+  cudaEventRecord(r.e1, st);
+  ++g_nrec;
+  g_open = false;
+}
+
+SMI_API int smi_profile(int on) {
+  if (on) g_nrec = 0;
+  g_smi_prof_on = on != 0;
+  g_open = false;
+  return SMI_OK;
+}
+
+// Writes "name count total_ms\n" per marked kernel into buf; synchronises the device.
+SMI_API int smi_profile_report(char* buf, size_t cap) {
+  if (!buf || cap < 2) SMI_FAIL(SMI_EINVAL, "smi_profile_report: bad buffer");
+  SMI_CUDA_OK(cudaDeviceSynchronize());
+  struct Agg {
+    const char* name;
+    int count;
+    double ms;
+  } agg[64];
+  int na = 0;
+  for (int i = 0; i < g_nrec; ++i) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, g_rec[i].e0, g_rec[i].e1) != cudaSuccess) continue;
+    int k = 0;
+    for (; k < na; ++k)
+      if (strcmp(agg[k].name, g_rec[i].name) == 0) break;
+    if (k == na) {
+      if (na == 64) continue;
+      agg[na++] = {g_rec[i].name, 0, 0.0};
+    }
+    agg[k].count += 1;
+    agg[k].ms += ms;
+  }
+  size_t off = 0;
+  buf[0] = 0;
+  for (int k = 0; k < na; ++k) {
+    int w = snprintf(buf + off, cap - off, "%s %d %.6f\n", agg[k].name, agg[k].count, agg[k].ms);
+    if (w < 0 || (size_t)w >= cap - off) break;
+    off += (size_t)w;
+  }
+  return SMI_OK;
 }

@@ -24,7 +24,32 @@ void smi_set_error(const char* fmt, ...);
                cudaGetErrorString(e__));                                               \
   } while (0)
 
-#define SMI_LAUNCH_OK() SMI_CUDA_OK(cudaGetLastError())
+extern thread_local long long g_smi_launches;
+#define SMI_LAUNCH_OK()                 \
+  do {                                  \
+    ++g_smi_launches;                   \
+    SMI_CUDA_OK(cudaGetLastError());    \
+  } while (0)
+
+// Optional per-kernel timing (bench.py's roofline leg): CUDA events recorded on the launching
+// stream around the marked kernels.  Off by default: one predictable branch per launch.
+extern bool g_smi_prof_on;
+void smi_prof_begin_(cudaStream_t st);
+void smi_prof_end_(const char* name, cudaStream_t st);
+#define SMI_PROF_BEGIN(st)              \
+  do {                                  \
+    if (g_smi_prof_on) smi_prof_begin_(st); \
+  } while (0)
+#define SMI_PROF_END(name, st)                \
+  do {                                        \
+    if (g_smi_prof_on) smi_prof_end_(name, st); \
+  } while (0)
+
+#define SMI_LAUNCH_OK_N(name, st) \
+  do {                            \
+    SMI_PROF_END(name, st);       \
+    SMI_LAUNCH_OK();              \
+  } while (0)
 
 static inline size_t smi_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 

@@ -302,9 +302,10 @@ size_t smi_elbo_carve(SmiArena& ar, ElboWs& w, const SmiModelDesc& md, int m, in
 
 int smi_guide_prep(const SmiModelDesc& md, const float* psi, int m, ElboWs& w, cudaStream_t st) {
   dim3 grid(nlb_of(md.latent_dim), m);
+  SMI_PROF_BEGIN(st);
   guide_prep_kernel<<<grid, 256, 0, st>>>(md, psi, m, w.loc_of, w.rho_of, w.tr_of, w.MU, w.SIG, w.ISIG,
                                           w.logdet_part);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("guide_prep_kernel", st);
   return SMI_OK;
 }
 
@@ -317,17 +318,19 @@ int smi_guide_sample(const SmiModelDesc& md, const float* eps, int m, int S, int
     set = true;
   }
   dim3 grid(w.nkt, nrows);
+  SMI_PROF_BEGIN(st);
   guide_sample_kernel<<<grid, 256, smem, st>>>(eps, w.MU, w.SIG, w.ISIG, m, S, md.latent_dim, row0, w.Z, w.QP,
                                                w.nkt);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("guide_sample_kernel", st);
   return SMI_OK;
 }
 
 int smi_guide_weights(const SmiModelDesc& md, int m, int S, int nrows, ElboWs& w, cudaStream_t st) {
   const int warps = nrows * S;
+  SMI_PROF_BEGIN(st);
   guide_weights_kernel<<<(warps + 7) / 8, 256, 0, st>>>(md, w.QP, w.logdet_part, nlb_of(md.latent_dim), w.Z, m, S,
                                                         nrows, w.nkt, w.W, w.LOGQ);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("guide_weights_kernel", st);
   return SMI_OK;
 }
 
@@ -339,10 +342,11 @@ static int launch_grad(const SmiModelDesc& md, const float* psi, const float* ep
   if (smem > 48 * 1024)
     SMI_CUDA_OK(cudaFuncSetAttribute(guide_grad_kernel<MP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid(w.nkt, nrows);
+  SMI_PROF_BEGIN(st);
   guide_grad_kernel<MP><<<grid, 256, smem, st>>>(psi, eps, w.MU, w.SIG, w.ISIG, w.W, w.DZ, w.LOGP, w.LOGQ,
                                                  w.loc_of, w.rho_of, w.tr_of, m, S, md.latent_dim,
                                                  md.particle_dim, tau, row0, G, elbo);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("guide_grad_kernel", st);
   return SMI_OK;
 }
 
@@ -356,15 +360,17 @@ int smi_guide_grad(const SmiModelDesc& md, const float* psi, const float* eps, i
 
 int smi_delta_gather(const SmiModelDesc& md, const float* psi, int row0, int nrows, ElboWs& w, cudaStream_t st) {
   dim3 grid(nlb_of(md.latent_dim), nrows);
+  SMI_PROF_BEGIN(st);
   delta_gather_kernel<<<grid, 256, 0, st>>>(md, psi, row0, w.Z, w.loc_of, w.tr_of);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("delta_gather_kernel", st);
   return SMI_OK;
 }
 
 int smi_delta_scatter(const SmiModelDesc& md, float tau, int nrows, ElboWs& w, float* G, float* elbo,
                       cudaStream_t st) {
   dim3 grid(nlb_of(md.latent_dim), nrows);
+  SMI_PROF_BEGIN(st);
   delta_scatter_kernel<<<grid, 256, 0, st>>>(w.DZ, w.LOGP, w.loc_of, md.latent_dim, md.particle_dim, tau, G, elbo);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("delta_scatter_kernel", st);
   return SMI_OK;
 }

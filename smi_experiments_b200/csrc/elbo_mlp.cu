@@ -214,8 +214,9 @@ int smi_model_logp_grad(const SmiModelDesc& md, const float* Z, const int32_t* i
                         cudaStream_t st) {
   const int L = md.latent_dim;
   if (md.kind == SMI_MODEL_GAUSS) {
+    SMI_PROF_BEGIN(st);
     gauss_kernel<<<ndraws, kThreads, 0, st>>>(Z, L, DZ, LOGP);
-    SMI_LAUNCH_OK();
+    SMI_LAUNCH_OK_N("gauss_kernel", st);
     return SMI_OK;
   }
   if (md.kind == SMI_MODEL_BNN_CLS) {
@@ -240,16 +241,18 @@ int smi_model_logp_grad(const SmiModelDesc& md, const float* Z, const int32_t* i
     if (smem > 48 * 1024)
       SMI_CUDA_OK(cudaFuncSetAttribute(bnn_reg_kernel<SMI_ACT_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem));
+    SMI_PROF_BEGIN(st);
     bnn_reg_kernel<SMI_ACT_RELU><<<ndraws, kThreads, smem, st>>>(Z, idx, x, (const float*)y, L, I, H, B, md.noise,
                                                                  md.sigma, lik_scale, o, DZ, LOGP);
   } else {
     if (smem > 48 * 1024)
       SMI_CUDA_OK(cudaFuncSetAttribute(bnn_reg_kernel<SMI_ACT_TANH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem));
+    SMI_PROF_BEGIN(st);
     bnn_reg_kernel<SMI_ACT_TANH><<<ndraws, kThreads, smem, st>>>(Z, idx, x, (const float*)y, L, I, H, B, md.noise,
                                                                  md.sigma, lik_scale, o, DZ, LOGP);
   }
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("bnn_reg_kernel", st);
   return SMI_OK;
 }
 

@@ -1,7 +1,290 @@
-// Placeholder until the classifier kernel lands (next commit).
+// Model side of the ELBO gradient for the classifier BNN (row a3, config C4).
+//
+// Restates reference src/models/mlp.py:14-65: a Flax MLP in -> H -> H -> O with tanh, lifted
+// to a BNN by random_flax_module with N(0, 1) priors on every kernel / bias, Categorical
+// likelihood, plate scale n / batch_size (the minibatch arrives pre-sliced, mlp.py:28-30).
+// Latent order (model order = sorted Flax param names):
+//   Dense_0.bias [H], Dense_0.kernel [in][H], Dense_1.bias [H], Dense_1.kernel [H][H],
+//   Dense_2.bias [O], Dense_2.kernel [H][O]
+// One CTA per ELBO draw.  Activations (B x H) live in shared memory; the 784 x 100 first-layer
+// kernel does not fit and is streamed from HBM/L2 in K-chunks for the forward product and in
+// row-chunks for dW1 = x^T dh1.  fp32 FMA register tiles (4 x 4 per thread); every output is
+// written exactly once, in a fixed summation order.
+#include <math.h>
+
 #include "elbo.cuh"
+
+namespace {
+
+constexpr float kLog2Pi = 1.8378770664093453f;
+constexpr int kThreads = 256;
+constexpr int KC = 32;        // chunk of the streamed dimension
+constexpr int kSlots = 4;     // 4 x 4 register tiles per thread in the forward products
+
+struct ClsOffsets {
+  int b1, w1, b2, w2, b3, w3;
+};
+
+template <int ACT>
+__device__ __forceinline__ float act_f(float v) {
+  return ACT == SMI_ACT_RELU ? fmaxf(v, 0.f) : tanhf(v);
+}
+template <int ACT>
+__device__ __forceinline__ float dact_from_out(float h) {
+  return ACT == SMI_ACT_RELU ? (h > 0.f ? 1.f : 0.f) : 1.f - h * h;
+}
+
+// acc[slot] += P(i, kk) * W(kk, j) for kk < nk.  P(i, kk) = P[i*pi + kk*pr]; W = ws[kk*HP + j].
+__device__ __forceinline__ void fwd_chunk(float (&acc)[kSlots][16], const float* __restrict__ P, int pi, int pr,
+                                          int rows, const float* __restrict__ ws, int HP, int nk, int ntj,
+                                          int ntiles) {
+#pragma unroll
+  for (int q = 0; q < kSlots; ++q) {
+    const int tile = q * kThreads + threadIdx.x;
+    if (tile >= ntiles) continue;
+    const int i0 = (tile / ntj) << 2, j0 = (tile % ntj) << 2;
+    int io[4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a) io[a] = min(i0 + a, rows - 1) * pi;
+    for (int kk = 0; kk < nk; ++kk) {
+      const float4 w4 = *reinterpret_cast<const float4*>(ws + kk * HP + j0);
+      const float wv[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+        const float p = P[io[a] + kk * pr];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[q][a * 4 + b] = fmaf(p, wv[b], acc[q][a * 4 + b]);
+      }
+    }
+  }
+}
+
+// C(i, j) = sum_r P(i, r) Q(r, j); 4 x 4 per thread; emit(i, j, v).
+template <typename Emit>
+__device__ __forceinline__ void tile_gemm(int I, int J, int R, const float* __restrict__ P, int pi, int pr,
+                                          const float* __restrict__ Q, int qr, int qj, Emit emit) {
+  const int nti = (I + 3) >> 2, ntj = (J + 3) >> 2;
+  for (int t = threadIdx.x; t < nti * ntj; t += blockDim.x) {
+    const int i0 = (t / ntj) << 2, j0 = (t % ntj) << 2;
+    int io[4], jo[4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+      io[a] = min(i0 + a, I - 1) * pi;
+      jo[a] = min(j0 + a, J - 1) * qj;
+    }
+    float acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+    for (int r = 0; r < R; ++r) {
+      float p[4], q[4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a) p[a] = P[io[a] + r * pr];
+#pragma unroll
+      for (int b = 0; b < 4; ++b) q[b] = Q[r * qr + jo[b]];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(p[a], q[b], acc[a][b]);
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int b = 0; b < 4; ++b)
+        if (i0 + a < I && j0 + b < J) emit(i0 + a, j0 + b, acc[a][b]);
+  }
+}
+
+template <int ACT>
+__global__ void __launch_bounds__(kThreads)
+bnn_cls_kernel(const float* __restrict__ Z, const float* __restrict__ x, const int32_t* __restrict__ y, int L,
+               int I, int H, int O, int B, float lik_scale, ClsOffsets o, float* __restrict__ DZ,
+               float* __restrict__ LOGP) {
+  extern __shared__ __align__(16) float sm[];
+  const int H1 = H | 1, O1 = O | 1, KC1 = KC + 1, HP = (H + 3) & ~3;
+  float* ws = sm;                   // [KC][HP]   (16-byte aligned rows)
+  float* h1 = ws + KC * HP;         // [B][H1]
+  float* h2 = h1 + B * H1;          // [B][H1]   (later: dh1)
+  float* dh = h2 + B * H1;          // [B][H1]   dh2
+  float* lg = dh + B * H1;          // [B][O1]   logits, then d logits
+  float* xs = lg + B * O1;          // [B][KC1]
+  __shared__ double red[32];
+  const int n = blockIdx.x;
+  const float* __restrict__ z = Z + (size_t)n * L;
+  float* __restrict__ dz = DZ + (size_t)n * L;
+  const int ntj = HP >> 2, nti = (B + 3) >> 2, ntiles = nti * ntj;
+  double lprior = 0.0;  // -0.5 sum z^2 accumulated where each parameter's gradient is emitted
+
+  auto emit_param = [&](int k, float g) {
+    const float t = z[k];
+    dz[k] = g - t;
+    lprior += (double)(t * t);
+  };
+
+  float acc[kSlots][16];
+  auto zero_acc = [&]() {
+#pragma unroll
+    for (int q = 0; q < kSlots; ++q)
+#pragma unroll
+      for (int e = 0; e < 16; ++e) acc[q][e] = 0.f;
+  };
+  auto store_act = [&](float* dst, int boff) {
+#pragma unroll
+    for (int q = 0; q < kSlots; ++q) {
+      const int tile = q * kThreads + threadIdx.x;
+      if (tile >= ntiles) continue;
+      const int i0 = (tile / ntj) << 2, j0 = (tile % ntj) << 2;
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+          if (i0 + a < B && j0 + b < H) dst[(i0 + a) * H1 + j0 + b] = act_f<ACT>(acc[q][a * 4 + b] + z[boff + j0 + b]);
+    }
+  };
+
+  // ---- forward layer 1: h1 = act(x W1 + b1), W1 streamed in chunks of KC input rows ----
+  zero_acc();
+  for (int k0 = 0; k0 < I; k0 += KC) {
+    const int nk = min(KC, I - k0);
+    __syncthreads();
+    for (int t = threadIdx.x; t < B * KC; t += blockDim.x) {
+      const int b = t / KC, kk = t - b * KC;
+      xs[b * KC1 + kk] = kk < nk ? __ldg(x + (size_t)b * I + k0 + kk) : 0.f;
+    }
+    for (int t = threadIdx.x; t < KC * HP; t += blockDim.x) {
+      const int kk = t / HP, j = t - kk * HP;
+      ws[t] = (kk < nk && j < H) ? z[o.w1 + (size_t)(k0 + kk) * H + j] : 0.f;
+    }
+    __syncthreads();
+    fwd_chunk(acc, xs, KC1, 1, B, ws, HP, nk, ntj, ntiles);
+  }
+  store_act(h1, o.b1);
+  // ---- forward layer 2: h2 = act(h1 W2 + b2) ----
+  zero_acc();
+  for (int k0 = 0; k0 < H; k0 += KC) {
+    const int nk = min(KC, H - k0);
+    __syncthreads();  // also publishes h1 on the first trip
+    for (int t = threadIdx.x; t < KC * HP; t += blockDim.x) {
+      const int kk = t / HP, j = t - kk * HP;
+      ws[t] = (kk < nk && j < H) ? z[o.w2 + (size_t)(k0 + kk) * H + j] : 0.f;
+    }
+    __syncthreads();
+    fwd_chunk(acc, h1 + k0, H1, 1, B, ws, HP, nk, ntj, ntiles);
+  }
+  store_act(h2, o.b2);
+  __syncthreads();
+  // ---- output layer, log-softmax, d logits ----
+  for (int t = threadIdx.x; t < B * O; t += blockDim.x) {
+    const int b = t / O, c = t - b * O;
+    float v = z[o.b3 + c];
+    for (int j = 0; j < H; ++j) v = fmaf(h2[b * H1 + j], z[o.w3 + j * O + c], v);
+    lg[b * O1 + c] = v;
+  }
+  __syncthreads();
+  double ll = 0.0;
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    float mx = -INFINITY;
+    for (int c = 0; c < O; ++c) mx = fmaxf(mx, lg[b * O1 + c]);
+    float se = 0.f;
+    for (int c = 0; c < O; ++c) se += expf(lg[b * O1 + c] - mx);
+    const float lse = mx + logf(se);
+    const int yb = y[b];
+    ll += (double)(lg[b * O1 + yb] - lse);
+    for (int c = 0; c < O; ++c) {
+      const float p = expf(lg[b * O1 + c] - lse);
+      lg[b * O1 + c] = lik_scale * ((c == yb ? 1.f : 0.f) - p);
+    }
+  }
+  ll = block_sum(ll, red);  // barriers inside publish d logits
+  __syncthreads();
+  // ---- backward: output layer ----
+  for (int t = threadIdx.x; t < H * O; t += blockDim.x) {
+    const int j = t / O, c = t - j * O;
+    float g = 0.f;
+    for (int b = 0; b < B; ++b) g = fmaf(h2[b * H1 + j], lg[b * O1 + c], g);
+    emit_param(o.w3 + t, g);
+  }
+  for (int c = threadIdx.x; c < O; c += blockDim.x) {
+    float g = 0.f;
+    for (int b = 0; b < B; ++b) g += lg[b * O1 + c];
+    emit_param(o.b3 + c, g);
+  }
+  for (int t = threadIdx.x; t < B * H; t += blockDim.x) {
+    const int b = t / H, j = t - b * H;
+    float g = 0.f;
+    for (int c = 0; c < O; ++c) g = fmaf(lg[b * O1 + c], z[o.w3 + j * O + c], g);
+    dh[b * H1 + j] = g * dact_from_out<ACT>(h2[b * H1 + j]);
+  }
+  __syncthreads();
+  // ---- backward: layer 2.  dW2[k][j] = sum_b h1[b][k] dh2[b][j]; db2; dh1 -> h2 buffer ----
+  tile_gemm(H, H, B, h1, 1, H1, dh, H1, 1, [&](int k, int j, float v) { emit_param(o.w2 + k * H + j, v); });
+  for (int j = threadIdx.x; j < H; j += blockDim.x) {
+    float g = 0.f;
+    for (int b = 0; b < B; ++b) g += dh[b * H1 + j];
+    emit_param(o.b2 + j, g);
+  }
+  // dh1[b][k] = act'(h1[b][k]) * sum_j dh2[b][j] W2[k][j]   (W2 read from L2: 4 H^2 bytes)
+  tile_gemm(B, H, H, dh, H1, 1, z + o.w2, 1, H,
+            [&](int b, int k, float v) { h2[b * H1 + k] = v * dact_from_out<ACT>(h1[b * H1 + k]); });
+  __syncthreads();
+  // ---- backward: layer 1.  dW1[k][j] = sum_b x[b][k] dh1[b][j], x streamed in row chunks; db1 ----
+  for (int j = threadIdx.x; j < H; j += blockDim.x) {
+    float g = 0.f;
+    for (int b = 0; b < B; ++b) g += h2[b * H1 + j];
+    emit_param(o.b1 + j, g);
+  }
+  for (int k0 = 0; k0 < I; k0 += KC) {
+    const int nk = min(KC, I - k0);
+    __syncthreads();
+    for (int t = threadIdx.x; t < B * KC; t += blockDim.x) {
+      const int b = t / KC, kk = t - b * KC;
+      xs[b * KC1 + kk] = kk < nk ? __ldg(x + (size_t)b * I + k0 + kk) : 0.f;
+    }
+    __syncthreads();
+    tile_gemm(nk, H, B, xs, 1, KC1, h2, H1, 1,
+              [&](int kk, int j, float v) { emit_param(o.w1 + (k0 + kk) * H + j, v); });
+  }
+  lprior = block_sum(lprior, red);
+  if (threadIdx.x == 0)
+    LOGP[n] = (float)(-0.5 * lprior - 0.5 * (double)L * (double)kLog2Pi + (double)lik_scale * ll);
+}
+
+size_t cls_smem_bytes(int H, int O, int B) {
+  const int H1 = H | 1, O1 = O | 1, HP = (H + 3) & ~3;
+  return ((size_t)KC * HP + (size_t)3 * B * H1 + (size_t)B * O1 + (size_t)B * (KC + 1)) * sizeof(float);
+}
+
+}  // namespace
+
 int smi_model_cls_logp_grad(const SmiModelDesc& md, const float* Z, const float* x, const int32_t* y, int ndraws,
                             int B, float lik_scale, float* DZ, float* LOGP, cudaStream_t st) {
-  (void)md; (void)Z; (void)x; (void)y; (void)ndraws; (void)B; (void)lik_scale; (void)DZ; (void)LOGP; (void)st;
-  SMI_FAIL(SMI_ELIMIT, "bnn_cls kernel not built");
+  const int I = md.in_dim, H = md.hidden, O = md.out_dim, L = md.latent_dim;
+  if (md.n_sites != 6) SMI_FAIL(SMI_EINVAL, "bnn_cls expects 6 sites");
+  const SmiSite* s = md.sites;
+  if (s[0].size != H || s[1].size != I * H || s[2].size != H || s[3].size != H * H || s[4].size != O ||
+      s[5].size != H * O)
+    SMI_FAIL(SMI_EINVAL, "bnn_cls site sizes do not match in=%d hidden=%d out=%d", I, H, O);
+  for (int t = 0; t < 6; ++t)
+    if (s[t].transform != SMI_T_IDENTITY) SMI_FAIL(SMI_EINVAL, "bnn_cls sites are unconstrained");
+  ClsOffsets o;
+  o.b1 = s[0].lat, o.w1 = s[1].lat, o.b2 = s[2].lat, o.w2 = s[3].lat, o.b3 = s[4].lat, o.w3 = s[5].lat;
+  const int HP = (H + 3) & ~3;
+  if (((B + 3) / 4) * (HP / 4) > kSlots * kThreads)
+    SMI_FAIL(SMI_ELIMIT, "bnn_cls: batch %d x hidden %d exceeds the register tiling", B, H);
+  const size_t smem = cls_smem_bytes(H, O, B);
+  if (smem > 220 * 1024) SMI_FAIL(SMI_ELIMIT, "bnn_cls: activations need %zu B of shared memory", smem);
+  if (md.act == SMI_ACT_RELU) {
+    SMI_CUDA_OK(cudaFuncSetAttribute(bnn_cls_kernel<SMI_ACT_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)smem));
+    SMI_PROF_BEGIN(st);
+    bnn_cls_kernel<SMI_ACT_RELU><<<ndraws, kThreads, smem, st>>>(Z, x, y, L, I, H, O, B, lik_scale, o, DZ, LOGP);
+  } else {
+    SMI_CUDA_OK(cudaFuncSetAttribute(bnn_cls_kernel<SMI_ACT_TANH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)smem));
+    SMI_PROF_BEGIN(st);
+    bnn_cls_kernel<SMI_ACT_TANH><<<ndraws, kThreads, smem, st>>>(Z, x, y, L, I, H, O, B, lik_scale, o, DZ, LOGP);
+  }
+  SMI_LAUNCH_OK_N("bnn_cls_kernel", st);
+  return SMI_OK;
 }

@@ -87,6 +87,12 @@ adagrad_kernel(float* __restrict__ x, float* __restrict__ acc, float* __restrict
 
 __global__ void bump_step_kernel(int32_t* step) { *step += 1; }
 
+__global__ void loss_record_kernel(const float* __restrict__ loss, const int32_t* __restrict__ step,
+                                   float* __restrict__ ring, int ring_len) {
+  const int t = *step - 1;
+  if (t >= 0) ring[t % ring_len] = *loss;
+}
+
 int grid_for(size_t n) {
   const size_t want = (n / 4 + kThreads - 1) / kThreads;
   const size_t cap = (size_t)smi_num_sms() * 8;
@@ -104,11 +110,13 @@ SMI_API int smi_adam_f32(float* x, float* mom, float* vel, const float* F, float
   if (!aligned16(x) || !aligned16(mom) || !aligned16(vel) || !aligned16(F))
     SMI_FAIL(SMI_EINVAL, "smi_adam_f32: buffers must be 16-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
+  SMI_PROF_BEGIN(st);
   adam_kernel<<<grid_for(n), kThreads, 0, st>>>(x, mom, vel, F, grad_sign, step, lr, b1, b2, eps, n);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("adam_kernel", st);
   if (bump_step) {
+    SMI_PROF_BEGIN(st);
     bump_step_kernel<<<1, 1, 0, st>>>(step);
-    SMI_LAUNCH_OK();
+    SMI_LAUNCH_OK_N("bump_step_kernel", st);
   }
   return SMI_OK;
 }
@@ -120,11 +128,21 @@ SMI_API int smi_adagrad_f32(float* x, float* acc, float* mom, const float* F, fl
   if (!aligned16(x) || !aligned16(acc) || !aligned16(mom) || !aligned16(F))
     SMI_FAIL(SMI_EINVAL, "smi_adagrad_f32: buffers must be 16-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
+  SMI_PROF_BEGIN(st);
   adagrad_kernel<<<grid_for(n), kThreads, 0, st>>>(x, acc, mom, F, grad_sign, lr, momentum, n);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("adagrad_kernel", st);
   if (bump_step && step) {
+    SMI_PROF_BEGIN(st);
     bump_step_kernel<<<1, 1, 0, st>>>(step);
-    SMI_LAUNCH_OK();
+    SMI_LAUNCH_OK_N("bump_step_kernel", st);
   }
+  return SMI_OK;
+}
+
+SMI_API int smi_loss_record_f32(const float* loss, const int32_t* step, float* ring, int ring_len, void* stream) {
+  if (!loss || !step || !ring || ring_len < 1) SMI_FAIL(SMI_EINVAL, "smi_loss_record_f32: bad argument");
+  SMI_PROF_BEGIN((cudaStream_t)stream);
+  loss_record_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(loss, step, ring, ring_len);
+  SMI_LAUNCH_OK_N("loss_record_kernel", (cudaStream_t)stream);
   return SMI_OK;
 }

@@ -161,7 +161,78 @@ prng_step_kernel(const SmiModelDesc md, const uint32_t* __restrict__ key_in, uin
   }
 }
 
+__global__ void prng_split_kernel(const uint32_t* __restrict__ key, int num, uint32_t* __restrict__ out) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= num) return;
+  const Key k = {key[0], key[1]};
+  const Key r = split_at(k, (uint32_t)j);
+  out[2 * j] = r.a;
+  out[2 * j + 1] = r.b;
+}
+
+// MODE 0: raw bits, 1: uniform [lo, hi), 2: normal
+template <int MODE>
+__global__ void __launch_bounds__(256)
+prng_fill_kernel(const uint32_t* __restrict__ key, size_t n, float lo, float hi, void* __restrict__ out) {
+  const Key k = {key[0], key[1]};
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint32_t o0, o1;
+    threefry2x32(k.a, k.b, (uint32_t)(i >> 32), (uint32_t)i, o0, o1);
+    const uint32_t bits = o0 ^ o1;
+    if (MODE == 0) {
+      ((uint32_t*)out)[i] = bits;
+    } else if (MODE == 1) {
+      const float f = __uint_as_float((bits >> 9) | 0x3F800000u) - 1.0f;
+      ((float*)out)[i] = fmaxf(lo, __fadd_rn(__fmul_rn(f, hi - lo), lo));
+    } else {
+      ((float*)out)[i] = normal_from_bits(bits);
+    }
+  }
+}
+
+int fill_grid(size_t n) {
+  const size_t want = (n + 255) / 256, cap = (size_t)smi_num_sms() * 8;
+  const size_t g = want < cap ? want : cap;
+  return (int)(g ? g : 1);
+}
+
 }  // namespace
+
+SMI_API int smi_prng_split(const uint32_t* key, int num, uint32_t* keys_out, void* stream) {
+  if (!key || !keys_out || num < 1) SMI_FAIL(SMI_EINVAL, "smi_prng_split: bad argument");
+  SMI_PROF_BEGIN((cudaStream_t)stream);
+  prng_split_kernel<<<(num + 127) / 128, 128, 0, (cudaStream_t)stream>>>(key, num, keys_out);
+  SMI_LAUNCH_OK_N("prng_split_kernel", (cudaStream_t)stream);
+  return SMI_OK;
+}
+
+SMI_API int smi_prng_uniform_f32(const uint32_t* key, size_t n, float lo, float hi, float* out, void* stream) {
+  if (!key || !out) SMI_FAIL(SMI_EINVAL, "smi_prng_uniform_f32: null pointer");
+  if (n == 0) return SMI_OK;
+  SMI_PROF_BEGIN((cudaStream_t)stream);
+  prng_fill_kernel<1><<<fill_grid(n), 256, 0, (cudaStream_t)stream>>>(key, n, lo, hi, out);
+  SMI_LAUNCH_OK_N("prng_fill_kernel", (cudaStream_t)stream);
+  return SMI_OK;
+}
+
+SMI_API int smi_prng_normal_f32(const uint32_t* key, size_t n, float* out, void* stream) {
+  if (!key || !out) SMI_FAIL(SMI_EINVAL, "smi_prng_normal_f32: null pointer");
+  if (n == 0) return SMI_OK;
+  SMI_PROF_BEGIN((cudaStream_t)stream);
+  prng_fill_kernel<2><<<fill_grid(n), 256, 0, (cudaStream_t)stream>>>(key, n, 0.f, 1.f, out);
+  SMI_LAUNCH_OK_N("prng_fill_kernel", (cudaStream_t)stream);
+  return SMI_OK;
+}
+
+SMI_API int smi_prng_bits_u32(const uint32_t* key, size_t n, uint32_t* out, void* stream) {
+  if (!key || !out) SMI_FAIL(SMI_EINVAL, "smi_prng_bits_u32: null pointer");
+  if (n == 0) return SMI_OK;
+  SMI_PROF_BEGIN((cudaStream_t)stream);
+  prng_fill_kernel<0><<<fill_grid(n), 256, 0, (cudaStream_t)stream>>>(key, n, 0.f, 1.f, out);
+  SMI_LAUNCH_OK_N("prng_fill_kernel", (cudaStream_t)stream);
+  return SMI_OK;
+}
 
 SMI_API int smi_prng_step_f32(const SmiModelDesc* md, const uint32_t* key_in, uint32_t* key_out, int m, int S,
                               int n_total, int B, int row0, int nrows, float* eps, int32_t* idx, void* stream) {
@@ -177,8 +248,9 @@ SMI_API int smi_prng_step_f32(const SmiModelDesc* md, const uint32_t* key_in, ui
     if (smem > 48 * 1024)
       SMI_CUDA_OK(cudaFuncSetAttribute(prng_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   }
+  SMI_PROF_BEGIN((cudaStream_t)stream);
   prng_step_kernel<<<nrows * S, 256, smem, (cudaStream_t)stream>>>(*md, key_in, key_out, m, S, n_total, B, row0, eps,
                                                                    idx);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("prng_step_kernel", (cudaStream_t)stream);
   return SMI_OK;
 }

@@ -171,20 +171,23 @@ int hist_grid() { return smi_num_sms() * 4; }
 size_t smi_select_workspace_bytes() { return 256 + kBins * sizeof(unsigned) + 256; }
 
 int smi_select_hist(const float* D2, size_t n, int pass, unsigned* state, unsigned* hist, cudaStream_t st) {
+  SMI_PROF_BEGIN(st);
   select_hist<<<hist_grid(), kThreads, 0, st>>>((const unsigned*)D2, n, pass, state, hist);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("select_hist", st);
   return SMI_OK;
 }
 
 int smi_select_scan(unsigned* hist, int pass, unsigned long long rank_lo, unsigned* state, cudaStream_t st) {
+  SMI_PROF_BEGIN(st);
   select_scan<<<1, 32, 0, st>>>(hist, pass, (unsigned)rank_lo, state);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("select_scan", st);
   return SMI_OK;
 }
 
 int smi_select_tail(const float* D2, size_t n, unsigned* state, cudaStream_t st) {
+  SMI_PROF_BEGIN(st);
   select_tail<<<hist_grid(), kThreads, 0, st>>>((const unsigned*)D2, n, state);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("select_tail", st);
   return SMI_OK;
 }
 
@@ -192,14 +195,16 @@ int smi_select_finish(const unsigned* state, const unsigned* cnt_le, const unsig
                       unsigned long long rank_hi, int m, float alpha, float* h_out, float* scal,
                       unsigned* rank_out, cudaStream_t st) {
   const float factor = m > 1 ? (float)(1.0 / log((double)m)) : 1.0f;
+  SMI_PROF_BEGIN(st);
   select_finish<<<1, 1, 0, st>>>(state, cnt_le ? cnt_le : state + 3, min_gt ? min_gt : state + 4, (unsigned)rank_hi, factor, alpha, m, h_out, scal, rank_out);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("select_finish", st);
   return SMI_OK;
 }
 
 int smi_select_fixed(float h, int m, float alpha, float* h_out, float* scal, cudaStream_t st) {
+  SMI_PROF_BEGIN(st);
   select_fixed_h<<<1, 1, 0, st>>>(h, alpha, m, h_out, scal);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("select_fixed_h", st);
   return SMI_OK;
 }
 

@@ -251,8 +251,9 @@ int smi_stein_small_run(const float* X, const float* G, int m, int d, float c_at
   unsigned* counter = ar.take<unsigned>(1);
   double* lpart = ar.take<double>(force_blocks(d));
 
+  SMI_PROF_BEGIN(st);
   stein_small_pairs<<<nchunk, kPairThreads, (size_t)m * dc * sizeof(float), st>>>(X, m, d, dc, partial);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("stein_small_pairs", st);
 
   FinishArgs fa;
   fa.partial = partial;
@@ -276,11 +277,13 @@ int smi_stein_small_run(const float* X, const float* G, int m, int d, float c_at
   const size_t fsm = ((size_t)2 * m * m + P) * sizeof(float);
   if (fsm > 40 * 1024)
     SMI_CUDA_OK(cudaFuncSetAttribute(stein_small_finish, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  SMI_PROF_BEGIN(st);
   stein_small_finish<<<1, 256, fsm, st>>>(fa);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("stein_small_finish", st);
   if (dist_only) return SMI_OK;
 
   const int fb = force_blocks(d);
+  SMI_PROF_BEGIN(st);
 #define LAUNCH_FORCE(MP)                                                                           \
   stein_small_force<MP><<<fb, kForceThreads, 0, st>>>(X, G, m, d, c_att, Kmat, rowsum, scal, F, lpart, \
                                                       counter, loss)
@@ -289,6 +292,6 @@ int smi_stein_small_run(const float* X, const float* G, int m, int d, float c_at
   else if (m <= 32) LAUNCH_FORCE(32);
   else LAUNCH_FORCE(64);
 #undef LAUNCH_FORCE
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("stein_small_force", st);
   return SMI_OK;
 }

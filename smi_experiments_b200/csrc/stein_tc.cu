@@ -164,8 +164,9 @@ int launch_gemm(const float* Ah, const float* Al, long long a_rows, const float*
                                      (int)tc::kSmemBytes));
     attr_set[EPI] = true;
   }
+  SMI_PROF_BEGIN(st);
   tc::gemm3xtf32_kernel<EPI><<<grid, tc::kThreads, tc::kSmemBytes, st>>>(ma_h, ma_l, mb_h, mb_l, ga);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("gemm3xtf32_kernel", st);
   return SMI_OK;
 }
 
@@ -206,8 +207,9 @@ size_t smi_stein_tc_workspace_bytes(int rows, int m, int d) {
 // Stage 1: split planes, norms, Gram GEMM -> D2 rows [row0, row0+rows) x m (compact, ld = m).
 static int tc_dist_rows(const float* X, int m, int d, int row0, int rows, TcWs& w, float* D2, cudaStream_t st) {
   const int ldk = pad32(d);
+  SMI_PROF_BEGIN(st);
   split_rows_kernel<<<m, 256, 0, st>>>(X, d, ldk, w.Xh, w.Xl, w.norms);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("split_rows_kernel", st);
   tc::GemmArgs ga = {};
   ga.M = rows;
   ga.N = m;
@@ -223,11 +225,13 @@ static int tc_dist_rows(const float* X, int m, int d, int row0, int rows, TcWs& 
 static int tc_force_rows(const float* X, const float* G, int m, int d, int row0, int rows, float c_att,
                          TcWs& w, float* F, cudaStream_t st) {
   const int ldm = pad32(m);
+  SMI_PROF_BEGIN(st);
   kmat_rows_kernel<<<rows, 256, 0, st>>>(w.D2, m, ldm, w.scal, w.Kh, w.Kl, w.rowsum);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("kmat_rows_kernel", st);
   dim3 yg((d + 31) / 32, ldm / 32);
+  SMI_PROF_BEGIN(st);
   ysplit_t_kernel<<<yg, 256, 0, st>>>(X, G, m, d, ldm, c_att, w.scal, w.Yh, w.Yl);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("ysplit_t_kernel", st);
   tc::GemmArgs ga = {};
   ga.M = rows;
   ga.N = d;
@@ -264,8 +268,9 @@ int smi_stein_tc_run(const float* X, const float* G, int m, int d, int row0, int
       return rc;
   }
   if ((rc = tc_force_rows(X, G, m, d, row0, rows, c_att, w, F, st))) return rc;
+  SMI_PROF_BEGIN(st);
   loss_finish_kernel<<<1, 256, 0, st>>>(w.lpart, 256, loss);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("loss_finish_kernel", st);
   return SMI_OK;
 }
 
@@ -347,7 +352,8 @@ SMI_API int smi_stein_rows_force(const float* X, const float* G, int m, int d, i
   ROWS_PROLOGUE();
   int rc = tc_force_rows(X, G, m, d, row0, rows, c_att, w, F_rows, st);
   if (rc) return rc;
+  SMI_PROF_BEGIN(st);
   sumsq_finish_kernel<<<1, 256, 0, st>>>(w.lpart, 256, sumsq);
-  SMI_LAUNCH_OK();
+  SMI_LAUNCH_OK_N("sumsq_finish_kernel", st);
   return SMI_OK;
 }

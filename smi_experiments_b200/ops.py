@@ -1,0 +1,131 @@
+"""Stage-level operators: torch CUDA tensors in, libsmi (hand-written sm_100a CUDA) underneath.
+
+torch is the container for device memory and streams only; every function here is one
+C-ABI call (include/smi.h).  Nothing falls back to torch math or to the CPU.
+"""
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import (MEDIAN_EXACT_MIDPOINT, MEDIAN_JAX_FP32_INDEX, PATH_AUTO, PATH_SMALL,  # noqa: F401
+                   PATH_TC, call, load)
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise ValueError("libsmi operators take CUDA tensors (there is no CPU path)")
+        if t is not None and not t.is_contiguous():
+            raise ValueError("libsmi operators take contiguous tensors")
+
+
+class Workspace:
+    """Grow-only device scratch buffer handed to the C ABI (the caller owns all memory)."""
+
+    def __init__(self):
+        self.buf = None
+
+    def get(self, nbytes, device):
+        nbytes = int(nbytes)
+        if self.buf is None or self.buf.numel() < nbytes or self.buf.device != device:
+            self.buf = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=device)
+        return self.buf
+
+
+_default_ws = {}
+
+
+def _ws(tag, nbytes, device):
+    w = _default_ws.setdefault((tag, device), Workspace())
+    return w.get(nbytes, device)
+
+
+def device_check():
+    call("smi_device_check")
+
+
+def stein_force(X, G, alpha=1.0, c_att=1.0, median_mode=MEDIAN_JAX_FP32_INDEX, h_fixed=0.0,
+                path=PATH_AUTO, out=None, ws=None):
+    """F, loss, h = Stein force of particles X (m, d) with scores G (m, d).  rows a4-a7."""
+    _need_cuda(X, G)
+    m, d = X.shape
+    F = out if out is not None else torch.empty_like(X)
+    loss = torch.empty(1, dtype=torch.float32, device=X.device)
+    h = torch.empty(1, dtype=torch.float32, device=X.device)
+    nbytes = load().smi_stein_force_workspace_bytes(m, d, path)
+    w = ws.get(nbytes, X.device) if ws is not None else _ws("stein", nbytes, X.device)
+    call("smi_stein_force_f32", _ptr(X), _ptr(G), m, d, c_att, alpha, median_mode, h_fixed, path,
+         _ptr(F), _ptr(loss), _ptr(h), _ptr(w), w.numel(), _stream())
+    return F, loss, h
+
+
+def sqdist(X, path=PATH_AUTO):
+    """Gram-form squared distances D2 (m, m).  row a4."""
+    _need_cuda(X)
+    m, d = X.shape
+    D2 = torch.empty(m, m, dtype=torch.float32, device=X.device)
+    nbytes = load().smi_sqdist_workspace_bytes(m, d, path)
+    w = _ws("stein", nbytes, X.device)
+    call("smi_sqdist_f32", _ptr(X), m, d, path, _ptr(D2), _ptr(w), w.numel(), _stream())
+    return D2
+
+
+def median_bandwidth(D2, median_mode=MEDIAN_JAX_FP32_INDEX):
+    """h, ranks: exact order-statistic bandwidth of a squared-distance matrix.  row a4 (K2).
+    ranks = uint32 bit patterns of the two selected D2 values (as int64 tensor of length 2)."""
+    _need_cuda(D2)
+    m = D2.shape[0]
+    h = torch.empty(1, dtype=torch.float32, device=D2.device)
+    ranks = torch.zeros(2, dtype=torch.int32, device=D2.device)
+    nbytes = load().smi_median_bandwidth_workspace_bytes(m)
+    w = _ws("select", nbytes, D2.device)
+    call("smi_median_bandwidth_f32", _ptr(D2), m, median_mode, _ptr(h), _ptr(ranks), _ptr(w), w.numel(),
+         _stream())
+    return h, ranks
+
+
+def adam(x, mom, vel, F, step, lr, grad_sign=-1.0, b1=0.9, b2=0.999, eps=1e-8, bump_step=True):
+    _need_cuda(x, mom, vel, F, step)
+    call("smi_adam_f32", _ptr(x), _ptr(mom), _ptr(vel), _ptr(F), grad_sign, _ptr(step), int(bump_step),
+         lr, b1, b2, eps, x.numel(), _stream())
+
+
+def adagrad(x, acc, mom, F, step, lr, grad_sign=-1.0, momentum=0.9, bump_step=True):
+    _need_cuda(x, acc, mom, F, step)
+    call("smi_adagrad_f32", _ptr(x), _ptr(acc), _ptr(mom), _ptr(F), grad_sign, _ptr(step), int(bump_step),
+         lr, momentum, x.numel(), _stream())
+
+
+def elbo_grad(md, psi, eps, idx, x, y, S, B, lik_scale=1.0, tau=1.0, row0=0, nrows=None, G=None,
+              elbo=None, ws=None):
+    """G (nrows, d), elbo (nrows): per-particle mixture-ELBO gradients.  row a3."""
+    _need_cuda(psi, eps, idx, x, y)
+    m, d = psi.shape
+    nrows = m - row0 if nrows is None else nrows
+    if G is None:
+        G = torch.empty(nrows, d, dtype=torch.float32, device=psi.device)
+    if elbo is None:
+        elbo = torch.empty(nrows, dtype=torch.float32, device=psi.device)
+    nbytes = load().smi_elbo_grad_workspace_bytes(C.byref(md), m, S, B, nrows)
+    w = ws.get(nbytes, psi.device) if ws is not None else _ws("elbo", nbytes, psi.device)
+    call("smi_elbo_grad_f32", C.byref(md), _ptr(psi), _ptr(eps), _ptr(idx), _ptr(x), _ptr(y), m, S, B,
+         lik_scale, tau, row0, nrows, _ptr(G), _ptr(elbo), _ptr(w), w.numel(), _stream())
+    return G, elbo
+
+
+def prng_step(md, key_in, key_out, m, S, n_total=0, B=0, row0=0, nrows=None, eps=None, idx=None):
+    """threefry key chain of one update: fills eps (nrows, S, L) / idx (nrows, S, B), next key.  row a9."""
+    _need_cuda(key_in, key_out, eps, idx)
+    nrows = m - row0 if nrows is None else nrows
+    call("smi_prng_step_f32", C.byref(md), _ptr(key_in), _ptr(key_out), m, S, n_total, B, row0, nrows,
+         _ptr(eps), _ptr(idx), _stream())

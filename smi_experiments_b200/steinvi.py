@@ -1,0 +1,395 @@
+"""SteinVI / SVGD / ASVGD: the engine surface the reference drives.
+
+Mirrors numpyro.contrib.einstein.{SteinVI, SVGD, ASVGD} as used at
+  experiments/uci_benchmark.py:188-195, experiments/img_classifier.py:160-177,
+  experiments/variance_collapse.py:97-123, experiments/synthetic/in_between_uncertainty.py:119-153,
+  experiments/synthetic/smi_recovery.py:77-86, src/methods/{svgd,asvgd}.py,
+and the calls src/engine_run.py:25-48 and src/model_select/early_stopping.py:16-22,42 make on it:
+init / evaluate / update / run / setup_run / get_params.
+
+One `update` is a fixed sequence of libsmi launches on the current CUDA stream
+  prng_step -> elbo_grad -> stein_force -> optimizer -> loss_record
+with every scalar (loss, bandwidth, step counter, PRNG key) resident on the device, so the
+sequence is captured once into a CUDA graph and replayed; nothing synchronises with the host
+unless the caller reads the loss (the reference does, src/engine_run.py:56).
+
+State handling differs from JAX in one documented way: buffers are updated IN PLACE (the
+equivalent of jit with donated arguments); `update` returns a SteinVIState that aliases the
+engine's buffers.
+"""
+
+import math
+from collections import namedtuple
+from functools import partial
+
+import numpy as np
+import torch
+
+from . import _lib, models, ops
+from .kernels import RBFKernel
+from .models import AutoDelta, AutoNormal, init_to_uniform
+from .optim import OptimState
+
+SteinVIState = namedtuple("SteinVIState", ["optim_state", "rng_key"])
+SteinVIRunResult = namedtuple("SteinVIRunResult", ["params", "state", "losses"])
+
+
+def PRNGKey(seed):
+    """jax.random.PRNGKey(seed) for a 32-bit seed: uint32[2] = (0, seed)."""
+    return np.array([(int(seed) >> 32) & 0xFFFFFFFF, int(seed) & 0xFFFFFFFF], dtype=np.uint32)
+
+
+def _key_tensor(key, device):
+    if isinstance(key, torch.Tensor):
+        t = key.to(device=device)
+        return t.view(torch.int32) if t.dtype != torch.int32 else t.clone()
+    k = np.asarray(key)
+    if k.shape == ():
+        k = PRNGKey(int(k))
+    k = np.ascontiguousarray(k.astype(np.uint32)).view(np.int32)
+    return torch.from_numpy(k.copy()).to(device)
+
+
+def _radius(fn):
+    if fn is None:
+        return 2.0
+    if isinstance(fn, partial):
+        return float(fn.keywords.get("radius", fn.args[0] if fn.args else 2.0))
+    if isinstance(fn, init_to_uniform):
+        return fn.radius
+    if fn is init_to_uniform:
+        return 2.0
+    raise NotImplementedError("only init_to_uniform(radius) initialisation is on the reference's path")
+
+
+class SteinVI:
+    """numpyro.contrib.einstein.SteinVI for the reference's models (see models.py)."""
+
+    def __init__(self, model, guide, optim, kernel_fn, num_stein_particles=10, num_elbo_particles=10,
+                 loss_temperature=1.0, repulsion_temperature=1.0, non_mixture_guide_params_fn=None,
+                 device=None, use_cuda_graph=True, c_att=1.0, **static_kwargs):
+        if not isinstance(model, models.Model):
+            raise TypeError("model must be one of the descriptors in smi_experiments_b200.models "
+                            "(NumPyro callables cannot be traced without NumPyro)")
+        if not isinstance(kernel_fn, RBFKernel):
+            raise TypeError("kernel_fn must be RBFKernel()")
+        self.model = model
+        self.guide = guide
+        self.optim = optim
+        self.kernel_fn = kernel_fn
+        self.num_stein_particles = int(num_stein_particles)
+        self.num_elbo_particles = int(num_elbo_particles)
+        self.loss_temperature = float(loss_temperature)
+        self.repulsion_temperature = float(repulsion_temperature)
+        self.static_kwargs = static_kwargs
+        self.c_att = float(c_att)
+        self.device = torch.device(device if device is not None else "cuda")
+        self.use_cuda_graph = bool(use_cuda_graph)
+        self.md, self.layout = models.make_desc(model, guide.kind)
+        self.guide_sites = [n for n in self.layout.names]
+        self._ws_elbo, self._ws_stein = ops.Workspace(), ops.Workspace()
+        self._bufs = None
+        self._graph = None
+        self._graph_sig = None
+        self.launches_per_update = 0
+
+    # ---- data binding: the reference's call-site kwargs -> device tensors -------------------
+    def _to_dev(self, name, arr, dtype):
+        """Host arrays are staged through pinned memory and copied H2D on the current stream
+        every call; CUDA tensors are used in place."""
+        if isinstance(arr, torch.Tensor) and arr.is_cuda:
+            t = arr if arr.dtype == dtype else arr.to(dtype)
+            return t.contiguous()
+        src = arr if isinstance(arr, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(arr))
+        slot = self._stage.get(name)
+        if slot is None or slot[0].shape != src.shape or slot[0].dtype != src.dtype:
+            pin = torch.empty(src.shape, dtype=src.dtype, pin_memory=True)
+            dev = torch.empty(src.shape, dtype=dtype, device=self.device)
+            raw = dev if src.dtype == dtype else torch.empty(src.shape, dtype=src.dtype, device=self.device)
+            slot = (pin, raw, dev)
+            self._stage[name] = slot
+        pin, raw, dev = slot
+        pin.copy_(src)
+        raw.copy_(pin, non_blocking=True)
+        if raw is not dev:
+            dev.copy_(raw)  # dtype conversion (e.g. uint8 pixels -> fp32), on the device
+        self.h2d_bytes += src.numel() * src.element_size()
+        return dev
+
+    def _bind(self, args, kwargs):
+        kw = dict(self.static_kwargs)
+        kw.update(kwargs)
+        m = self.model
+        self.h2d_bytes = 0
+        if not hasattr(self, "_stage"):
+            self._stage = {}
+        if isinstance(m, models.GaussianTarget):
+            return dict(x=None, y=None, n_total=0, B=0, lik_scale=1.0, idx=False)
+        x = args[0] if len(args) > 0 else kw["x"]
+        y = args[1] if len(args) > 1 else kw["y"]
+        if isinstance(m, models.BNNRegression):
+            xd = self._to_dev("x", x, torch.float32)
+            if xd.dim() == 1:
+                xd = xd[:, None]
+            yd = self._to_dev("y", y, torch.float32).reshape(-1)
+            n = xd.shape[0]
+            sub = kw.get("subsample", None)
+            if sub is None or sub >= n:
+                return dict(x=xd, y=yd, n_total=0, B=n, lik_scale=1.0, idx=False)
+            return dict(x=xd, y=yd, n_total=n, B=int(sub), lik_scale=float(n) / float(sub), idx=True)
+        if isinstance(m, models.BNNClassifier):
+            xd = self._to_dev("x", x, torch.float32)
+            xd = xd.reshape(xd.shape[0], -1)
+            yd = self._to_dev("y", y, torch.int32).reshape(-1)
+            b = xd.shape[0]
+            n = kw.get("n", b)
+            bs = kw.get("batch_size", None)
+            if not ((bs is None and b == n) or bs == b):
+                raise ValueError("batch_size must equal the leading dimension of x (src/models/mlp.py:16)")
+            plate = 0 if (bs is None or bs == n) else int(n)
+            return dict(x=xd, y=yd, n_total=plate, B=b, lik_scale=float(n) / float(b), idx=False)
+        raise TypeError(type(m))
+
+    # ---- buffers ---------------------------------------------------------------------------
+    def _alloc(self, data):
+        m, S, L, d = self.num_stein_particles, self.num_elbo_particles, self.layout.latent_dim, self.layout.particle_dim
+        dev = self.device
+        normal = self.guide.kind == _lib.GUIDE_NORMAL
+        sig = (data["B"], data["n_total"], data["idx"])
+        if self._bufs is not None and self._bufs["sig"] == sig:
+            return self._bufs
+        b = dict(sig=sig)
+        b["eps"] = torch.empty(m, S, L, dtype=torch.float32, device=dev) if normal else None
+        b["idx"] = torch.empty(m, S, data["B"], dtype=torch.int32, device=dev) if data["idx"] else None
+        b["G"] = torch.empty(m, d, dtype=torch.float32, device=dev)
+        b["F"] = torch.empty(m, d, dtype=torch.float32, device=dev)
+        b["elbo"] = torch.empty(m, dtype=torch.float32, device=dev)
+        b["loss"] = torch.zeros(1, dtype=torch.float32, device=dev)
+        b["h"] = torch.zeros(1, dtype=torch.float32, device=dev)
+        b["key_next"] = torch.zeros(2, dtype=torch.int32, device=dev)
+        self._bufs = b
+        self._graph = None
+        return b
+
+    def _own(self, state):
+        """Make `state` the engine's resident state (copy if it lives elsewhere)."""
+        if getattr(self, "_state", None) is not None and state.optim_state.x is self._state.optim_state.x:
+            return self._state
+        os_ = state.optim_state
+        dev = self.device
+        self._state = SteinVIState(
+            OptimState(os_.step.to(dev).clone(), os_.x.to(dev).clone().contiguous(),
+                       os_.a.to(dev).clone(), os_.b.to(dev).clone()),
+            _key_tensor(state.rng_key, dev))
+        self._graph = None
+        return self._state
+
+    # ---- the step --------------------------------------------------------------------------
+    def _tau(self):
+        return self.loss_temperature
+
+    def _launch(self, st, b, data, do_update, ring=None):
+        """Enqueue one step on the current stream.  Returns the number of kernel launches."""
+        m, S = self.num_stein_particles, self.num_elbo_particles
+        os_ = st.optim_state
+        ops.prng_step(self.md, st.rng_key, b["key_next"], m, S, data["n_total"], data["B"] if data["idx"] else 0,
+                      0, m, b["eps"], b["idx"])
+        ops.elbo_grad(self.md, os_.x, b["eps"], b["idx"], data["x"], data["y"], S, max(data["B"], 1),
+                      data["lik_scale"], self._tau(), 0, m, b["G"], b["elbo"], self._ws_elbo)
+        nbytes = _lib.load().smi_stein_force_workspace_bytes(m, self.layout.particle_dim, _lib.PATH_AUTO)
+        w = self._ws_stein.get(nbytes, self.device)
+        _lib.call("smi_stein_force_f32", ops._ptr(os_.x), ops._ptr(b["G"]), m, self.layout.particle_dim,
+                  self.c_att, self.repulsion_temperature, self.kernel_fn.median_mode, self.kernel_fn.h_fixed,
+                  _lib.PATH_AUTO, ops._ptr(b["F"]), ops._ptr(b["loss"]), ops._ptr(b["h"]), ops._ptr(w),
+                  w.numel(), ops._stream())
+        if do_update:
+            self.optim.update(b["F"], os_, -1.0)
+            if ring is not None:
+                _lib.call("smi_loss_record_f32", ops._ptr(b["loss"]), ops._ptr(os_.step), ops._ptr(ring),
+                          ring.numel(), ops._stream())
+            st.rng_key.copy_(b["key_next"])
+
+    def init(self, rng_key, *args, **kwargs):
+        """SteinVI.init (src/engine_run.py:41-47): particles ~ init_to_uniform(radius) per site in
+        unconstrained space, AutoNormal scales = init_scale; returns SteinVIState."""
+        ops.device_check()
+        dev = self.device
+        m, L, d = self.num_stein_particles, self.layout.latent_dim, self.layout.particle_dim
+        key = _key_tensor(rng_key, dev)
+        keys5 = torch.empty(5, 2, dtype=torch.int32, device=dev)
+        _lib.call("smi_prng_split", ops._ptr(key), 5, ops._ptr(keys5), ops._stream())
+        pkeys = torch.empty(m, 2, dtype=torch.int32, device=dev)
+        _lib.call("smi_prng_split", ops._ptr(keys5[4]), m, ops._ptr(pkeys), ops._stream())
+        radius = _radius(self.guide.init_loc_fn)
+        lat = torch.empty(m, L, dtype=torch.float32, device=dev)
+        for i in range(m):
+            _lib.call("smi_prng_uniform_f32", ops._ptr(pkeys[i]), L, -radius, radius, ops._ptr(lat[i]),
+                      ops._stream())
+        psi = torch.empty(m, d, dtype=torch.float32, device=dev)
+        for r in self.layout.rows:
+            psi[:, r["loc"]:r["loc"] + r["size"]] = lat[:, r["lat"]:r["lat"] + r["size"]]
+            if r["rho"] >= 0:
+                psi[:, r["rho"]:r["rho"] + r["size"]] = models.softplus_inv(self.guide.init_scale)
+        self._state = SteinVIState(self.optim.init(psi), keys5[0].clone())
+        self._graph = None
+        return self._state
+
+    def get_params(self, state):
+        """{name: constrained value (m, *site_shape)} with NumPyro's AutoGuide names."""
+        x = state.optim_state.x
+        out = {}
+        for name in self.layout.names:
+            off, shape, site, which = self.layout.leaves[name]
+            v = x[:, off:off + site.size].reshape((x.shape[0],) + tuple(shape))
+            if which == "rho":
+                v = torch.nn.functional.softplus(v)
+            elif self.guide.kind == _lib.GUIDE_DELTA and site.transform == _lib.T_EXP:
+                v = torch.exp(v)
+            out[name] = v
+        return out
+
+    def evaluate(self, state, *args, **kwargs):
+        """Loss of `state` without updating it (same key as the next update; src/engine_run.py:48)."""
+        st = self._own(state)
+        data = self._bind(args, kwargs)
+        b = self._alloc(data)
+        self._launch(st, b, data, do_update=False)
+        return b["loss"].clone().reshape(())
+
+    def update(self, state, *args, **kwargs):
+        """One Stein step (src/engine_run.py:25,30).  Returns (state, loss); loss is a device scalar."""
+        st = self._own(state)
+        data = self._bind(args, kwargs)
+        b = self._alloc(data)
+        ring = getattr(self, "_ring", None)
+        if not self.use_cuda_graph or not self._graphable():
+            self._eager(st, b, data, ring)
+            return st, b["loss"].reshape(())
+        sig = (data["x"].data_ptr() if data["x"] is not None else 0,
+               data["y"].data_ptr() if data["y"] is not None else 0, data["lik_scale"],
+               ring.data_ptr() if ring is not None else 0)
+        if self._graph is None or self._graph_sig != sig:
+            if getattr(self, "_warm_sig", None) != sig:
+                # first call with these buffers: run eagerly (sets kernel attributes), capture next time
+                self._warm_sig = sig
+                self._eager(st, b, data, ring)
+                return st, b["loss"].reshape(())
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._launch(st, b, data, True, ring)
+            self._graph, self._graph_sig = g, sig
+            # capture does not execute: fall through to the replay for this step
+        self._graph.replay()
+        return st, b["loss"].reshape(())
+
+    def _graphable(self):
+        return True
+
+    def _eager(self, st, b, data, ring):
+        n0 = _lib.load().smi_launch_count(0)
+        self._launch(st, b, data, True, ring)
+        # + the 8-byte key copy (a torch D2D copy kernel) that closes the step
+        self.launches_per_update = _lib.load().smi_launch_count(0) - n0 + 1
+
+    def setup_run(self, rng_key, num_steps, args, init_state, kwargs):
+        """(step, diagnostic, collect, extract_state, init_info) as SteinVI.setup_run
+        (src/model_select/early_stopping.py:16-22)."""
+        state = self.init(rng_key, *args, **kwargs) if init_state is None else self._own(init_state)
+        loss0 = self.evaluate(state, *args, **kwargs)
+
+        def step(info):
+            st, _ = info
+            return self.update(st, *args, **kwargs)
+
+        def collect(info):
+            return info[1]
+
+        def extract_state(info):
+            return info[0]
+
+        def diagnostic(info):
+            return "Stein force {:.2f}.".format(float(info[1]))
+
+        return step, diagnostic, collect, extract_state, (state, loss0)
+
+    def run(self, rng_key, num_steps, *args, progress_bar=True, init_state=None, **kwargs):
+        """SteinVI.run: num_steps updates, losses collected ON THE DEVICE (one D2H at the end)."""
+        if num_steps < 1:
+            raise ValueError("num_steps must be a positive integer.")
+        state = self.init(rng_key, *args, **kwargs) if init_state is None else self._own(init_state)
+        start = int(state.optim_state.step.item())
+        # the step kernel sequence ends with ring[(step - 1) mod len] = loss (smi_loss_record_f32)
+        self._ring = torch.zeros(num_steps, dtype=torch.float32, device=self.device)
+        try:
+            for _ in range(num_steps):
+                state, _loss = self.update(state, *args, **kwargs)
+            k = start % num_steps
+            losses = torch.roll(self._ring, -k) if k else self._ring
+        finally:
+            self._ring = None
+            self._graph = None
+        return SteinVIRunResult(self.get_params(state), state, losses)
+
+
+class SVGD(SteinVI):
+    """numpyro.contrib.einstein.SVGD with the reference wrapper's extra `repulsion_temperature`
+    (src/methods/svgd.py:4-24).  AutoDelta guide, one ELBO draw, loss_temperature = 1/m.
+    compat_b1=True reproduces the wrapper's bug B1 (10 particles and default init regardless of
+    the arguments)."""
+
+    def __init__(self, model, optim, kernel_fn, num_stein_particles=10, repulsion_temperature=1.0,
+                 guide_kwargs={}, compat_b1=False, **static_kwargs):
+        if compat_b1:
+            num_stein_particles, guide_kwargs = 10, {}
+        super().__init__(model, AutoDelta(model, **guide_kwargs), optim, kernel_fn,
+                         num_stein_particles=num_stein_particles, num_elbo_particles=1,
+                         loss_temperature=1.0 / float(num_stein_particles),
+                         repulsion_temperature=repulsion_temperature, **static_kwargs)
+
+
+class ASVGD(SVGD):
+    """numpyro.contrib.einstein.ASVGD (src/methods/asvgd.py:4-27): SVGD whose loss temperature
+    follows a cyclical annealing schedule, tau_t = cyc(t) / m."""
+
+    def __init__(self, model, optim, kernel_fn, num_stein_particles=10, num_cycles=10, trans_speed=10,
+                 repulsion_temperature=1.0, guide_kwargs={}, **static_kwargs):
+        super().__init__(model, optim, kernel_fn, num_stein_particles, repulsion_temperature, guide_kwargs,
+                         **static_kwargs)
+        self.num_cycles = int(num_cycles)
+        self.trans_speed = int(trans_speed)
+        self._cyc = None
+        self._t = 0
+
+    @staticmethod
+    def _cyclical_annealing(num_steps, num_cycles, trans_speed):
+        """Schedule of numpyro ASVGD; mirrored at src/engine_run.py:16-18."""
+        norm = float(num_steps + 1) / float(num_cycles)
+        cycle_len = num_steps // num_cycles
+        last_start = (num_cycles - 1) * cycle_len
+
+        def cycle_fn(t):
+            last = min(t // last_start, 1) if last_start > 0 else 1
+            return (1 - last) * ((((t - 1) % cycle_len) + 1) / norm) ** trans_speed + last
+
+        return cycle_fn
+
+    def _graphable(self):
+        return False  # tau changes every step (host scalar)
+
+    def _tau(self):
+        if self._cyc is None:
+            return self.loss_temperature
+        return self._cyc(self._t) / float(self.num_stein_particles)
+
+    def update(self, state, *args, **kwargs):
+        out = super().update(state, *args, **kwargs)
+        self._t += 1
+        return out
+
+    def run(self, rng_key, num_steps, *args, **kwargs):
+        self._cyc = ASVGD._cyclical_annealing(num_steps, self.num_cycles, self.trans_speed)
+        self._t = 0
+        try:
+            return super().run(rng_key, num_steps, *args, **kwargs)
+        finally:
+            self._cyc = None

@@ -1,0 +1,115 @@
+"""Per-particle mixture-ELBO gradients (row a3) against the torch-autograd oracle."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import elbo as oelbo
+from oracle import models as omodels
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5   # north_star: <= 1e-5 relative (fp32) for ELBO and gradients (vs float64 oracle)
+
+
+def _rel(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300))
+
+
+def _setup(pm, om, guide, m, S, seed, radius=0.1, scale=0.1):
+    from smi_experiments_b200 import models, _lib
+    gk = _lib.GUIDE_NORMAL if guide == "normal" else _lib.GUIDE_DELTA
+    md, lay = models.make_desc(pm, gk)
+    rows, L, d = omodels.layout(om, guide)
+    assert (L, d) == (lay.latent_dim, lay.particle_dim)
+    for a, b in zip(rows, lay.rows):
+        assert (a["lat"], a["loc"], a["rho"], a["size"]) == (b["lat"], b["loc"], b["rho"], b["size"])
+    rng = np.random.default_rng(seed)
+    psi = rng.uniform(-radius, radius, (m, d)).astype(np.float32)
+    if guide == "normal":
+        for r in rows:
+            psi[:, r["rho"]:r["rho"] + r["size"]] = np.log(np.expm1(scale)) + 0.3 * rng.standard_normal((m, r["size"]))
+    eps = rng.standard_normal((m, S, L)).astype(np.float32) if guide == "normal" else None
+    return md, psi, eps, rng, L, d
+
+
+def _run(cuda, md, psi, eps, idx, x, y, S, B, lik_scale, tau, row0=0, nrows=None):
+    from smi_experiments_b200 import ops
+    t = lambda a, dt=None: None if a is None else torch.from_numpy(np.ascontiguousarray(a)).to(cuda)
+    G, E = ops.elbo_grad(md, t(psi), t(eps), t(idx), t(x), t(y), S, B, lik_scale, tau, row0, nrows)
+    return G.cpu().numpy(), E.cpu().numpy()
+
+
+@pytest.mark.parametrize("m,S,N,B,I", [(3, 4, 30, 7, 13), (5, 100, 455, 100, 13), (20, 8, 64, 64, 5)])
+def test_uci_bnn_smi(cuda, m, S, N, B, I):
+    from smi_experiments_b200 import models
+    pm, om = models.uci_bnn(I), omodels.uci_bnn(I)
+    md, psi, eps, rng, L, d = _setup(pm, om, "normal", m, S, seed=m + S)
+    x = rng.standard_normal((N, I)).astype(np.float32)
+    y = (x @ rng.standard_normal(I) * 0.3 + 0.1 * rng.standard_normal(N)).astype(np.float32)
+    idx = None if B == N else np.stack([rng.permutation(N)[:B] for _ in range(m * S)]).reshape(m, S, B).astype(np.int32)
+    G, E = _run(cuda, md, psi, eps, idx, x, y, S, B, N / B, 1.0)
+    G64, E64 = oelbo.elbo_grads(om, psi.astype(np.float64), eps, idx, x, y, N, 1.0, "normal", torch.float64)
+    assert _rel(G, G64) <= RTOL
+    assert np.max(np.abs(E - E64) / np.abs(E64)) <= RTOL
+
+
+@pytest.mark.parametrize("h", [5, 50, 100])
+def test_reg_1d_bnn_smi(cuda, h):
+    from smi_experiments_b200 import models
+    pm, om = models.reg_1d_bnn(h), omodels.reg_1d_bnn(h)
+    m, S, N = 5, 10, 40
+    md, psi, eps, rng, L, d = _setup(pm, om, "normal", m, S, seed=h, radius=2.0)
+    x = np.sort(rng.uniform(-1.5, 1.7, N)).astype(np.float32)[:, None]
+    y = (1.5 * np.sin(2 * np.pi * x[:, 0]) + 3 * x[:, 0] + 1).astype(np.float32)
+    G, E = _run(cuda, md, psi, eps, None, x, y, S, N, 1.0, 1.0)
+    G64, E64 = oelbo.elbo_grads(om, psi.astype(np.float64), eps, None, x, y, N, 1.0, "normal", torch.float64)
+    assert _rel(G, G64) <= RTOL
+    assert np.max(np.abs(E - E64) / np.abs(E64)) <= RTOL
+
+
+@pytest.mark.parametrize("guide,m,S,dim", [("normal", 1, 100, 10), ("normal", 20, 100, 100), ("delta", 20, 1, 1000),
+                                           ("delta", 10, 1, 30)])
+def test_gaussian_target(cuda, guide, m, S, dim):
+    from smi_experiments_b200 import models
+    pm, om = models.GaussianTarget(dim), omodels.gaussian(dim)
+    md, psi, eps, rng, L, d = _setup(pm, om, guide, m, S, seed=dim + m, radius=2.0)
+    tau = 1.0 if guide == "normal" else 1.0 / m
+    G, E = _run(cuda, md, psi, eps, None, None, None, S, 0, 1.0, tau)
+    G64, E64 = oelbo.elbo_grads(om, psi.astype(np.float64), eps, None, None, None, None, tau, guide, torch.float64)
+    assert _rel(G, G64) <= RTOL
+    assert np.max(np.abs(E - E64) / np.maximum(np.abs(E64), 1.0)) <= RTOL
+    if guide == "delta":    # closed form: score of N(0, I) scaled by tau
+        np.testing.assert_allclose(G, -tau * psi, rtol=1e-6)
+
+
+@pytest.mark.parametrize("m,S,B,I,H,O,scale255", [(2, 3, 16, 12, 8, 3, False), (3, 5, 128, 784, 100, 10, False),
+                                                  (2, 2, 128, 784, 100, 10, True), (2, 2, 50, 30, 10, 4, False)])
+def test_mnist_mlp_smi(cuda, m, S, B, I, H, O, scale255):
+    from smi_experiments_b200 import models
+    pm, om = models.mnist_mlp(I, H, O), omodels.mnist_mlp(I, H, O)
+    md, psi, eps, rng, L, d = _setup(pm, om, "normal", m, S, seed=B + I, radius=0.5 if not scale255 else 0.05)
+    if scale255:
+        x = rng.integers(0, 256, (B, I)).astype(np.float32)
+    else:
+        x = rng.standard_normal((B, I)).astype(np.float32)
+    y = rng.integers(0, O, B).astype(np.int32)
+    n_total = 60000
+    G, E = _run(cuda, md, psi, eps, None, x, y, S, B, n_total / B, 1.0)
+    idx = np.broadcast_to(np.arange(B), (m, S, B))
+    G64, E64 = oelbo.elbo_grads(om, psi.astype(np.float64), eps, idx, x, y, n_total, 1.0, "normal", torch.float64)
+    assert _rel(G, G64) <= RTOL
+    assert np.max(np.abs(E - E64) / np.abs(E64)) <= RTOL
+
+
+def test_row_sharding(cuda):
+    """Rows [row0, row0 + nrows) computed alone equal those rows of the full call."""
+    from smi_experiments_b200 import models
+    pm, om = models.uci_bnn(4), omodels.uci_bnn(4)
+    m, S, N, B = 6, 5, 20, 20
+    md, psi, eps, rng, L, d = _setup(pm, om, "normal", m, S, seed=1)
+    x = rng.standard_normal((N, 4)).astype(np.float32)
+    y = rng.standard_normal(N).astype(np.float32)
+    G, E = _run(cuda, md, psi, eps, None, x, y, S, B, 1.0, 1.0)
+    G2, E2 = _run(cuda, md, psi, eps[2:5], None, x, y, S, B, 1.0, 1.0, row0=2, nrows=3)
+    assert np.array_equal(G2, G[2:5]) and np.array_equal(E2, E[2:5])
