@@ -159,11 +159,13 @@ int smi_stein_rows_force(const float* X, const float* G, int m, int d, int row0,
 
 /* ---- Optimizers (row a8).  `grad_sign` multiplies F before use: the Stein step hands the
  *      optimizer -F, so pass -1.  `step` is a device int32 holding the number of updates
- *      applied so far; it is read, and incremented by one when `bump_step` is non-zero.  */
+ *      applied so far; it is read, and incremented by one when `bump_step` is non-zero.
+ *      Hyper-parameters are doubles: (1 - b1), (1 - b2), (1 - momentum) are formed in double and
+ *      then rounded to fp32, as JAX does with weakly-typed Python scalars.                  */
 int smi_adam_f32(float* x, float* mom, float* vel, const float* F, float grad_sign, int32_t* step,
-                 int bump_step, float lr, float b1, float b2, float eps, size_t n, void* stream);
+                 int bump_step, double lr, double b1, double b2, double eps, size_t n, void* stream);
 int smi_adagrad_f32(float* x, float* acc, float* mom, const float* F, float grad_sign,
-                    int32_t* step, int bump_step, float lr, float momentum, size_t n, void* stream);
+                    int32_t* step, int bump_step, double lr, double momentum, size_t n, void* stream);
 
 /* ---- Per-particle mixture-ELBO gradients (row a3; NumPyro stein_loss.py).
  *   psi  : (m, d) all particles.   eps : (nrows, S, L) N(0,1) noise of the owned rows (NULL for

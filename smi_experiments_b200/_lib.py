@@ -45,6 +45,7 @@ class SmiError(RuntimeError):
 _P = C.c_void_p
 _I = C.c_int
 _F = C.c_float
+_D = C.c_double
 _Z = C.c_size_t
 _MD = C.POINTER(SmiModelDesc)
 
@@ -70,8 +71,8 @@ PROTOTYPES = {
     "smi_stein_rows_tail": (_I, [_I, _I, _I, _I, _P, _P, _Z, _P]),
     "smi_stein_rows_bandwidth": (_I, [_I, _I, _I, _I, _I, _F, _F, _P, _P, _P, _P, _Z, _P]),
     "smi_stein_rows_force": (_I, [_P, _P, _I, _I, _I, _I, _F, _P, _P, _P, _Z, _P]),
-    "smi_adam_f32": (_I, [_P, _P, _P, _P, _F, _P, _I, _F, _F, _F, _F, _Z, _P]),
-    "smi_adagrad_f32": (_I, [_P, _P, _P, _P, _F, _P, _I, _F, _F, _Z, _P]),
+    "smi_adam_f32": (_I, [_P, _P, _P, _P, _F, _P, _I, _D, _D, _D, _D, _Z, _P]),
+    "smi_adagrad_f32": (_I, [_P, _P, _P, _P, _F, _P, _I, _D, _D, _Z, _P]),
     "smi_elbo_grad_workspace_bytes": (_Z, [_MD, _I, _I, _I, _I]),
     "smi_elbo_grad_f32": (_I, [_MD, _P, _P, _P, _P, _P, _I, _I, _I, _F, _F, _I, _I, _P, _P, _P, _Z, _P]),
     "smi_prng_step_f32": (_I, [_MD, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),

@@ -14,10 +14,12 @@ constexpr int kThreads = 256;
 __device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 
+// omb1 = float(1 - b1), omb2 = float(1 - b2) evaluated in double on the host: JAX folds the
+// python scalars before casting to float32 (1 - 0.999 -> 0.001f, not 1.f - 0.999f).
 __device__ __forceinline__ void adam_one(float& x, float& m, float& v, float g, float lr, float b1,
-                                         float b2, float eps, float c1, float c2) {
-  m = (1.f - b1) * g + b1 * m;
-  v = (1.f - b2) * (g * g) + b2 * v;
+                                         float b2, float omb1, float omb2, float eps, float c1, float c2) {
+  m = omb1 * g + b1 * m;
+  v = omb2 * (g * g) + b2 * v;
   const float mhat = m / c1;
   const float vhat = v / c2;
   x = x - lr * mhat / (sqrtf(vhat) + eps);
@@ -26,7 +28,7 @@ __device__ __forceinline__ void adam_one(float& x, float& m, float& v, float g, 
 __global__ void __launch_bounds__(kThreads)
 adam_kernel(float* __restrict__ x, float* __restrict__ mom, float* __restrict__ vel,
             const float* __restrict__ F, float sign, const int32_t* __restrict__ step, float lr, float b1,
-            float b2, float eps, size_t n) {
+            float b2, float omb1, float omb2, float eps, size_t n) {
   const float t1 = (float)(*step + 1);
   const float c1 = 1.f - powf(b1, t1);
   const float c2 = 1.f - powf(b2, t1);
@@ -34,10 +36,10 @@ adam_kernel(float* __restrict__ x, float* __restrict__ mom, float* __restrict__ 
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
     float4 xv = ld4(x + 4 * i), mv = ld4(mom + 4 * i), vv = ld4(vel + 4 * i), fv = ld4(F + 4 * i);
-    adam_one(xv.x, mv.x, vv.x, sign * fv.x, lr, b1, b2, eps, c1, c2);
-    adam_one(xv.y, mv.y, vv.y, sign * fv.y, lr, b1, b2, eps, c1, c2);
-    adam_one(xv.z, mv.z, vv.z, sign * fv.z, lr, b1, b2, eps, c1, c2);
-    adam_one(xv.w, mv.w, vv.w, sign * fv.w, lr, b1, b2, eps, c1, c2);
+    adam_one(xv.x, mv.x, vv.x, sign * fv.x, lr, b1, b2, omb1, omb2, eps, c1, c2);
+    adam_one(xv.y, mv.y, vv.y, sign * fv.y, lr, b1, b2, omb1, omb2, eps, c1, c2);
+    adam_one(xv.z, mv.z, vv.z, sign * fv.z, lr, b1, b2, omb1, omb2, eps, c1, c2);
+    adam_one(xv.w, mv.w, vv.w, sign * fv.w, lr, b1, b2, omb1, omb2, eps, c1, c2);
     st4(x + 4 * i, xv);
     st4(mom + 4 * i, mv);
     st4(vel + 4 * i, vv);
@@ -45,7 +47,7 @@ adam_kernel(float* __restrict__ x, float* __restrict__ mom, float* __restrict__ 
   if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
     const size_t i = n4 * 4 + threadIdx.x;
     float xv = x[i], mv = mom[i], vv = vel[i];
-    adam_one(xv, mv, vv, sign * F[i], lr, b1, b2, eps, c1, c2);
+    adam_one(xv, mv, vv, sign * F[i], lr, b1, b2, omb1, omb2, eps, c1, c2);
     x[i] = xv;
     mom[i] = mv;
     vel[i] = vv;
@@ -53,24 +55,24 @@ adam_kernel(float* __restrict__ x, float* __restrict__ mom, float* __restrict__ 
 }
 
 __device__ __forceinline__ void adagrad_one(float& x, float& acc, float& mom, float g, float lr,
-                                            float momentum) {
+                                            float momentum, float omm) {
   acc = acc + g * g;
   const float inv = acc > 0.f ? 1.f / sqrtf(acc) : 0.f;
-  mom = (1.f - momentum) * (g * inv) + momentum * mom;
+  mom = omm * (g * inv) + momentum * mom;
   x = x - lr * mom;
 }
 
 __global__ void __launch_bounds__(kThreads)
 adagrad_kernel(float* __restrict__ x, float* __restrict__ acc, float* __restrict__ mom,
-               const float* __restrict__ F, float sign, float lr, float momentum, size_t n) {
+               const float* __restrict__ F, float sign, float lr, float momentum, float omm, size_t n) {
   const size_t n4 = n / 4;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
     float4 xv = ld4(x + 4 * i), av = ld4(acc + 4 * i), mv = ld4(mom + 4 * i), fv = ld4(F + 4 * i);
-    adagrad_one(xv.x, av.x, mv.x, sign * fv.x, lr, momentum);
-    adagrad_one(xv.y, av.y, mv.y, sign * fv.y, lr, momentum);
-    adagrad_one(xv.z, av.z, mv.z, sign * fv.z, lr, momentum);
-    adagrad_one(xv.w, av.w, mv.w, sign * fv.w, lr, momentum);
+    adagrad_one(xv.x, av.x, mv.x, sign * fv.x, lr, momentum, omm);
+    adagrad_one(xv.y, av.y, mv.y, sign * fv.y, lr, momentum, omm);
+    adagrad_one(xv.z, av.z, mv.z, sign * fv.z, lr, momentum, omm);
+    adagrad_one(xv.w, av.w, mv.w, sign * fv.w, lr, momentum, omm);
     st4(x + 4 * i, xv);
     st4(acc + 4 * i, av);
     st4(mom + 4 * i, mv);
@@ -78,7 +80,7 @@ adagrad_kernel(float* __restrict__ x, float* __restrict__ acc, float* __restrict
   if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
     const size_t i = n4 * 4 + threadIdx.x;
     float xv = x[i], av = acc[i], mv = mom[i];
-    adagrad_one(xv, av, mv, sign * F[i], lr, momentum);
+    adagrad_one(xv, av, mv, sign * F[i], lr, momentum, omm);
     x[i] = xv;
     acc[i] = av;
     mom[i] = mv;
@@ -105,13 +107,14 @@ bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 }  // namespace
 
 SMI_API int smi_adam_f32(float* x, float* mom, float* vel, const float* F, float grad_sign, int32_t* step,
-                         int bump_step, float lr, float b1, float b2, float eps, size_t n, void* stream) {
+                         int bump_step, double lr, double b1, double b2, double eps, size_t n, void* stream) {
   if (!x || !mom || !vel || !F || !step) SMI_FAIL(SMI_EINVAL, "smi_adam_f32: null pointer");
   if (!aligned16(x) || !aligned16(mom) || !aligned16(vel) || !aligned16(F))
     SMI_FAIL(SMI_EINVAL, "smi_adam_f32: buffers must be 16-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
   SMI_PROF_BEGIN(st);
-  adam_kernel<<<grid_for(n), kThreads, 0, st>>>(x, mom, vel, F, grad_sign, step, lr, b1, b2, eps, n);
+  adam_kernel<<<grid_for(n), kThreads, 0, st>>>(x, mom, vel, F, grad_sign, step, (float)lr, (float)b1, (float)b2,
+                                                (float)(1.0 - b1), (float)(1.0 - b2), (float)eps, n);
   SMI_LAUNCH_OK_N("adam_kernel", st);
   if (bump_step) {
     SMI_PROF_BEGIN(st);
@@ -122,14 +125,15 @@ SMI_API int smi_adam_f32(float* x, float* mom, float* vel, const float* F, float
 }
 
 SMI_API int smi_adagrad_f32(float* x, float* acc, float* mom, const float* F, float grad_sign,
-                            int32_t* step, int bump_step, float lr, float momentum, size_t n,
+                            int32_t* step, int bump_step, double lr, double momentum, size_t n,
                             void* stream) {
   if (!x || !acc || !mom || !F) SMI_FAIL(SMI_EINVAL, "smi_adagrad_f32: null pointer");
   if (!aligned16(x) || !aligned16(acc) || !aligned16(mom) || !aligned16(F))
     SMI_FAIL(SMI_EINVAL, "smi_adagrad_f32: buffers must be 16-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
   SMI_PROF_BEGIN(st);
-  adagrad_kernel<<<grid_for(n), kThreads, 0, st>>>(x, acc, mom, F, grad_sign, lr, momentum, n);
+  adagrad_kernel<<<grid_for(n), kThreads, 0, st>>>(x, acc, mom, F, grad_sign, (float)lr, (float)momentum,
+                                                   (float)(1.0 - momentum), n);
   SMI_LAUNCH_OK_N("adagrad_kernel", st);
   if (bump_step && step) {
     SMI_PROF_BEGIN(st);

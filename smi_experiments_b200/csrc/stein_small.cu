@@ -5,7 +5,7 @@
 // counts the reference's SMI experiments use (experiments/uci_benchmark.py:188-195: 5;
 // BASELINE configs: 5-20).  Three launches, all deterministic (fixed summation order):
 //   1. pairs  : per d-chunk partial Gram x_i.x_j and difference-form |x_i-x_j|^2 for i<=j
-//   2. finish : reduce partials, Gram-form distances -> bitonic sort in smem -> median ->
+//   2. finish : reduce partials, pairwise distances -> bitonic sort in smem -> median ->
 //               bandwidth h; K = exp(-|x_i-x_j|^2/h) from the DIFFERENCE form (as the
 //               reference's kernel does), row sums
 //   3. force  : F = c_att K G + c (rowsum(K) * X - K X), c = 2 alpha/(h m); |F|_F
@@ -121,14 +121,18 @@ __global__ void __launch_bounds__(256) stein_small_finish(FinishArgs a) {
     sqd[i * m + j] = sqd[j * m + i] = (float)s;
   }
   __syncthreads();
-  // (b) Gram-form distances, as all_pairs_eucl_dist does: sqrt(max(|a|^2+|b|^2-2ab, 0))
+  // (b) pairwise distances for the median.  all_pairs_eucl_dist evaluates |a|^2+|b|^2-2ab, which
+  // in exact arithmetic is the squared difference; the difference form is used here because the
+  // Gram form cancels catastrophically in fp32 once particles sit close together around a common
+  // offset (every AutoNormal particle shares rho ~ softplus^-1(0.1)).  d2_out still reports the
+  // Gram form (smi_sqdist_f32's contract), with the exact-zero diagonal.
   for (int t = threadIdx.x; t < P; t += blockDim.x) {
     float v = INFINITY;
     if (t < mm) {
       const int i = t / m, j = t - i * m;
-      const float d2 = fmaxf((gram[i * m + i] + gram[j * m + j]) - 2.f * gram[t], 0.f);
-      if (a.d2_out) a.d2_out[t] = d2;
-      v = sqrtf(d2);
+      if (a.d2_out)
+        a.d2_out[t] = i == j ? 0.f : fmaxf((gram[i * m + i] + gram[j * m + j]) - 2.f * gram[t], 0.f);
+      v = sqrtf(sqd[t]);
     }
     srt[t] = v;
   }
@@ -178,16 +182,19 @@ stein_small_force(const float* __restrict__ X, const float* __restrict__ G, int 
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   double sq = 0.0;
   if (k < d) {
+    // the repulsive term c (rowsum_i x_i - sum_j K_ij x_j) is translation invariant: particles
+    // are taken relative to particle 0 so that a common offset does not cancel in fp32
+    const float x0 = __ldg(X + k);
     float y[MP];
 #pragma unroll
     for (int j = 0; j < MP; ++j)
-      if (j < m) y[j] = c_att * __ldg(G + (size_t)j * d + k) - c * __ldg(X + (size_t)j * d + k);
+      if (j < m) y[j] = c_att * __ldg(G + (size_t)j * d + k) - c * (__ldg(X + (size_t)j * d + k) - x0);
     for (int i = 0; i < m; ++i) {
       float acc = 0.f;
 #pragma unroll
       for (int j = 0; j < MP; ++j)
         if (j < m) acc = fmaf(ks[i * m + j], y[j], acc);
-      const float f = fmaf(c * rs[i], __ldg(X + (size_t)i * d + k), acc);
+      const float f = fmaf(c * rs[i], __ldg(X + (size_t)i * d + k) - x0, acc);
       if (F) F[(size_t)i * d + k] = f;
       sq += (double)f * (double)f;
     }

@@ -24,10 +24,33 @@ __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
   lo = x - hi;                                            // exact in fp32
 }
 
-// One CTA per particle row: X row -> hi / lo planes (zero padded to ld) + squared norm.
+// Column means of X (m x d), two deterministic stages: per row-slab partial sums, then the mean.
+// Distances and the repulsive term are translation invariant; working on X - mean keeps the Gram
+// form |a|^2 + |b|^2 - 2ab from cancelling when the particles share a large common offset.
+constexpr int kMeanSlabs = 64;
 __global__ void __launch_bounds__(256)
-split_rows_kernel(const float* __restrict__ X, int d, int ld, float* __restrict__ Xh, float* __restrict__ Xl,
-                  float* __restrict__ norms) {
+colsum_kernel(const float* __restrict__ X, int m, int d, double* __restrict__ part) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= d) return;
+  const int per = (m + kMeanSlabs - 1) / kMeanSlabs;
+  const int r0 = blockIdx.y * per, r1 = min(m, r0 + per);
+  double s = 0.0;
+  for (int r = r0; r < r1; ++r) s += (double)__ldg(X + (size_t)r * d + k);
+  part[(size_t)blockIdx.y * d + k] = s;
+}
+__global__ void __launch_bounds__(256)
+colmean_kernel(const double* __restrict__ part, int m, int d, float* __restrict__ mean) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= d) return;
+  double s = 0.0;
+  for (int b = 0; b < kMeanSlabs; ++b) s += part[(size_t)b * d + k];
+  mean[k] = (float)(s / (double)m);
+}
+
+// One CTA per particle row: centred X row -> hi / lo planes (zero padded to ld) + squared norm.
+__global__ void __launch_bounds__(256)
+split_rows_kernel(const float* __restrict__ X, const float* __restrict__ mean, int d, int ld,
+                  float* __restrict__ Xh, float* __restrict__ Xl, float* __restrict__ norms) {
   __shared__ double red[32];
   const int row = blockIdx.x;
   const float* x = X + (size_t)row * d;
@@ -35,7 +58,7 @@ split_rows_kernel(const float* __restrict__ X, int d, int ld, float* __restrict_
   float* l = Xl + (size_t)row * ld;
   double s = 0.0;
   for (int k = threadIdx.x; k < ld; k += blockDim.x) {
-    float v = k < d ? __ldg(x + k) : 0.f, hi, lo;
+    float v = k < d ? __ldg(x + k) - __ldg(mean + k) : 0.f, hi, lo;
     split_tf32(v, hi, lo);
     h[k] = hi;
     l[k] = lo;
@@ -70,8 +93,9 @@ kmat_rows_kernel(const float* __restrict__ D2, int m, int ldm, const float* __re
 
 // Y = c_att G - c X, transposed into (d x ldm) hi / lo planes through a 32 x 32 smem tile.
 __global__ void __launch_bounds__(256)
-ysplit_t_kernel(const float* __restrict__ X, const float* __restrict__ G, int m, int d, int ldm, float c_att,
-                const float* __restrict__ scal, float* __restrict__ Yh, float* __restrict__ Yl) {
+ysplit_t_kernel(const float* __restrict__ X, const float* __restrict__ G, const float* __restrict__ mean, int m,
+                int d, int ldm, float c_att, const float* __restrict__ scal, float* __restrict__ Yh,
+                float* __restrict__ Yl) {
   __shared__ float tile[32][33];
   const float c = scal[1];
   const int j0 = blockIdx.y * 32, k0 = blockIdx.x * 32;
@@ -79,7 +103,8 @@ ysplit_t_kernel(const float* __restrict__ X, const float* __restrict__ G, int m,
   for (int r = ty; r < 32; r += 8) {
     const int j = j0 + r, k = k0 + tx;
     float y = 0.f;
-    if (j < m && k < d) y = c_att * __ldg(G + (size_t)j * d + k) - c * __ldg(X + (size_t)j * d + k);
+    if (j < m && k < d)
+      y = c_att * __ldg(G + (size_t)j * d + k) - c * (__ldg(X + (size_t)j * d + k) - __ldg(mean + k));
     tile[r][tx] = y;
   }
   __syncthreads();
@@ -173,8 +198,8 @@ int launch_gemm(const float* Ah, const float* Al, long long a_rows, const float*
 inline int pad32(int v) { return (v + 31) / 32 * 32; }
 
 struct TcWs {
-  float *Xh, *Xl, *norms, *D2, *Kh, *Kl, *rowsum, *Yh, *Yl, *scal;
-  double* lpart;
+  float *Xh, *Xl, *norms, *D2, *Kh, *Kl, *rowsum, *Yh, *Yl, *scal, *mean;
+  double *lpart, *mpart;
   void* sel;
 };
 
@@ -190,6 +215,8 @@ size_t carve(SmiArena& ar, TcWs& w, int rows, int m, int d) {
   w.Yh = ar.take<float>((size_t)d * ldm);
   w.Yl = ar.take<float>((size_t)d * ldm);
   w.scal = ar.take<float>(4);
+  w.mean = ar.take<float>(d);
+  w.mpart = ar.take<double>((size_t)kMeanSlabs * d);
   w.lpart = ar.take<double>(256);
   w.sel = ar.take<char>(smi_select_workspace_bytes());
   return ar.off;
@@ -208,7 +235,16 @@ size_t smi_stein_tc_workspace_bytes(int rows, int m, int d) {
 static int tc_dist_rows(const float* X, int m, int d, int row0, int rows, TcWs& w, float* D2, cudaStream_t st) {
   const int ldk = pad32(d);
   SMI_PROF_BEGIN(st);
-  split_rows_kernel<<<m, 256, 0, st>>>(X, d, ldk, w.Xh, w.Xl, w.norms);
+  {
+    dim3 g((d + 255) / 256, kMeanSlabs);
+    colsum_kernel<<<g, 256, 0, st>>>(X, m, d, w.mpart);
+    SMI_LAUNCH_OK_N("colsum_kernel", st);
+    SMI_PROF_BEGIN(st);
+    colmean_kernel<<<(d + 255) / 256, 256, 0, st>>>(w.mpart, m, d, w.mean);
+    SMI_LAUNCH_OK_N("colmean_kernel", st);
+    SMI_PROF_BEGIN(st);
+  }
+  split_rows_kernel<<<m, 256, 0, st>>>(X, w.mean, d, ldk, w.Xh, w.Xl, w.norms);
   SMI_LAUNCH_OK_N("split_rows_kernel", st);
   tc::GemmArgs ga = {};
   ga.M = rows;
@@ -217,6 +253,8 @@ static int tc_dist_rows(const float* X, int m, int d, int row0, int rows, TcWs& 
   ga.ldc = m;
   ga.na = w.norms + row0;
   ga.nb = w.norms;
+  ga.diag_shift = row0;
+  ga.symmetric = (rows == m && row0 == 0) ? 1 : 0;
   return launch_gemm<tc::EPI_GRAM>(w.Xh + (size_t)row0 * ldk, w.Xl + (size_t)row0 * ldk, rows, w.Xh, w.Xl, m,
                                    ldk, ga, st);
 }
@@ -230,7 +268,7 @@ static int tc_force_rows(const float* X, const float* G, int m, int d, int row0,
   SMI_LAUNCH_OK_N("kmat_rows_kernel", st);
   dim3 yg((d + 31) / 32, ldm / 32);
   SMI_PROF_BEGIN(st);
-  ysplit_t_kernel<<<yg, 256, 0, st>>>(X, G, m, d, ldm, c_att, w.scal, w.Yh, w.Yl);
+  ysplit_t_kernel<<<yg, 256, 0, st>>>(X, G, w.mean, m, d, ldm, c_att, w.scal, w.Yh, w.Yl);
   SMI_LAUNCH_OK_N("ysplit_t_kernel", st);
   tc::GemmArgs ga = {};
   ga.M = rows;
@@ -239,6 +277,7 @@ static int tc_force_rows(const float* X, const float* G, int m, int d, int row0,
   ga.ldc = d;
   ga.X = X + (size_t)row0 * d;
   ga.ldx = d;
+  ga.xmean = w.mean;
   ga.rowsum = w.rowsum;
   ga.scal = w.scal;
   ga.lpart = w.lpart;

@@ -19,7 +19,10 @@ namespace tc {
 constexpr int BM = 128, BN = 256, BK = 32;
 constexpr int kStages = 2;
 constexpr int kAccStages = 2;
-constexpr int kThreads = 256;
+constexpr int kChunkKB = 8;        // K blocks per accumulation chunk: 8 x 32 = 256 (96 tensor-core accumulations)
+constexpr int kEpiWarps = 8;       // warps 4..11: lane quarter = warp % 4, column half = (warp - 4) / 4
+constexpr int kThreads = 128 + 32 * kEpiWarps;
+constexpr int kEpiCols = BN / 2;   // columns per epilogue thread
 constexpr uint32_t kABytes = BM * BK * 4;  // 16 KB
 constexpr uint32_t kBBytes = BN * BK * 4;  // 32 KB
 constexpr uint32_t kStageBytes = 2 * kABytes + 2 * kBBytes;  // 96 KB
@@ -36,8 +39,11 @@ struct GemmArgs {
   // EPI_GRAM
   const float* na;      // [M] squared norms of the A rows
   const float* nb;      // [N] squared norms of the B rows
+  int diag_shift;       // column of the diagonal element of row r is r + diag_shift (row0 when sharded)
+  int symmetric;        // A and B are the same particle set: compute tiles touching j >= i, mirror-write
   // EPI_FORCE
   const float* X;       // [M x ldx] particles of the A rows
+  const float* xmean;   // [N] column means: the epilogue uses X - mean (translation invariance)
   long long ldx;
   const float* rowsum;  // [M]
   const float* scal;    // scal[1] = c
@@ -53,7 +59,25 @@ __device__ __forceinline__ void tile_coords(int t, int tiles_m, int tiles_n, int
   tm = first_m + r % gsz;
   tn = r / gsz;
 }
+// Symmetric Gram: tile (tm, tn) is needed iff it holds an element with column >= row.
+__device__ __forceinline__ bool tile_needed(const GemmArgs& a, int tm, int tn) {
+  return !a.symmetric || (tn + 1) * BN > tm * BM;
+}
 
+template <int REGS>
+__device__ __forceinline__ void reg_dec() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS));
+}
+template <int REGS>
+__device__ __forceinline__ void reg_inc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS));
+}
+
+// The tensor core adds into its fp32 accumulator with truncation, so a long K loop drifts
+// linearly (measured: ~0.25 ulp per accumulation).  The K loop is therefore cut into chunks of
+// kChunkKB blocks; each chunk starts a fresh TMEM accumulator (two of them ping-pong) and the
+// epilogue warps add finished chunks into fp32 registers with round-to-nearest while the next
+// chunk's MMAs run.
 template <int EPI>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm3xtf32_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
@@ -67,11 +91,12 @@ gemm3xtf32_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_con
   uint64_t* tfull = bars + 2 * kStages;    // [kAccStages]
   uint64_t* tempty = tfull + kAccStages;   // [kAccStages]
   uint32_t* tmem_slot = (uint32_t*)(tempty + kAccStages);
-  double* red = (double*)(tmem_slot + 2);  // [4]
+  double* red = (double*)(tmem_slot + 2);  // [kEpiWarps]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ntiles = args.tiles_m * args.tiles_n;
   const int nkb = args.K / BK;
+  const int nchunks = (nkb + kChunkKB - 1) / kChunkKB;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a_hi);
@@ -86,7 +111,7 @@ gemm3xtf32_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_con
     }
     for (int a = 0; a < kAccStages; ++a) {
       mbar_init(tfull + a, 1);
-      mbar_init(tempty + a, 128);
+      mbar_init(tempty + a, 32 * kEpiWarps);
     }
     fence_mbar_init();
   }
@@ -99,72 +124,86 @@ gemm3xtf32_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_con
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (elect_one()) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        int tm, tn;
-        tile_coords(t, args.tiles_m, args.tiles_n, tm, tn);
-        for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait(empty + stage, phase ^ 1);
-          uint8_t* sa = smem + stage * kStageBytes;
-          mbar_arrive_expect_tx(full + stage, kStageBytes);
-          tma_load_2d(sa, &map_a_hi, full + stage, kb * BK, tm * BM);
-          tma_load_2d(sa + kABytes, &map_a_lo, full + stage, kb * BK, tm * BM);
-          tma_load_2d(sa + 2 * kABytes, &map_b_hi, full + stage, kb * BK, tn * BN);
-          tma_load_2d(sa + 2 * kABytes + kBBytes, &map_b_lo, full + stage, kb * BK, tn * BN);
-          if (++stage == kStages) {
-            stage = 0;
-            phase ^= 1;
+  if (warp < 4) {
+    reg_dec<40>();
+    if (warp == 0) {
+      // ===================== TMA producer =====================
+      if (elect_one()) {
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+          int tm, tn;
+          tile_coords(t, args.tiles_m, args.tiles_n, tm, tn);
+          if (!tile_needed(args, tm, tn)) continue;
+          for (int kb = 0; kb < nkb; ++kb) {
+            mbar_wait(empty + stage, phase ^ 1);
+            uint8_t* sa = smem + stage * kStageBytes;
+            mbar_arrive_expect_tx(full + stage, kStageBytes);
+            tma_load_2d(sa, &map_a_hi, full + stage, kb * BK, tm * BM);
+            tma_load_2d(sa + kABytes, &map_a_lo, full + stage, kb * BK, tm * BM);
+            tma_load_2d(sa + 2 * kABytes, &map_b_hi, full + stage, kb * BK, tn * BN);
+            tma_load_2d(sa + 2 * kABytes + kBBytes, &map_b_lo, full + stage, kb * BK, tn * BN);
+            if (++stage == kStages) {
+              stage = 0;
+              phase ^= 1;
+            }
           }
         }
       }
-    }
-    __syncwarp();
-  } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (elect_one()) {
-      constexpr uint32_t idesc = make_idesc_tf32(BM, BN);
-      int stage = 0, acc = 0;
-      uint32_t phase = 0, acc_phase = 0;
-      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        mbar_wait(tempty + acc, acc_phase ^ 1);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)acc * BN;
-        for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait(full + stage, phase);
-          tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * kStageBytes);
-          const uint64_t a_hi = make_smem_desc_sw128(sa);
-          const uint64_t a_lo = make_smem_desc_sw128(sa + kABytes);
-          const uint64_t b_hi = make_smem_desc_sw128(sa + 2 * kABytes);
-          const uint64_t b_lo = make_smem_desc_sw128(sa + 2 * kABytes + kBBytes);
+      __syncwarp();
+    } else if (warp == 1) {
+      // ===================== MMA issuer =====================
+      if (elect_one()) {
+        constexpr uint32_t idesc = make_idesc_tf32(BM, BN);
+        int stage = 0, acc = 0;
+        uint32_t phase = 0, acc_phase = 0;
+        for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+          int tm, tn;
+          tile_coords(t, args.tiles_m, args.tiles_n, tm, tn);
+          if (!tile_needed(args, tm, tn)) continue;
+          for (int ch = 0; ch < nchunks; ++ch) {
+            mbar_wait(tempty + acc, acc_phase ^ 1);
+            tc_fence_after();
+            const uint32_t d_tmem = tmem_base + (uint32_t)acc * BN;
+            const int kb_end = min(nkb, (ch + 1) * kChunkKB);
+            for (int kb = ch * kChunkKB; kb < kb_end; ++kb) {
+              mbar_wait(full + stage, phase);
+              tc_fence_after();
+              const uint32_t sa = smem_u32(smem + stage * kStageBytes);
+              const uint64_t a_hi = make_smem_desc_sw128(sa);
+              const uint64_t a_lo = make_smem_desc_sw128(sa + kABytes);
+              const uint64_t b_hi = make_smem_desc_sw128(sa + 2 * kABytes);
+              const uint64_t b_lo = make_smem_desc_sw128(sa + 2 * kABytes + kBBytes);
+              const uint32_t first = kb != ch * kChunkKB;
 #pragma unroll
-          for (int ks = 0; ks < BK / 8; ++ks) {
-            const uint64_t adv = (uint64_t)(ks * 32 >> 4);  // +32 bytes inside the swizzle atom
-            mma_tf32_ss(d_tmem, a_lo + adv, b_hi + adv, idesc, (kb | ks) != 0);
-            mma_tf32_ss(d_tmem, a_hi + adv, b_lo + adv, idesc, 1u);
-            mma_tf32_ss(d_tmem, a_hi + adv, b_hi + adv, idesc, 1u);
+              for (int ks = 0; ks < BK / 8; ++ks) {
+                const uint64_t adv = (uint64_t)(ks * 32 >> 4);  // +32 bytes inside the swizzle atom
+                // small terms first: they are absorbed before the accumulator grows
+                mma_tf32_ss(d_tmem, a_lo + adv, b_hi + adv, idesc, first | (uint32_t)(ks != 0));
+                mma_tf32_ss(d_tmem, a_hi + adv, b_lo + adv, idesc, 1u);
+                mma_tf32_ss(d_tmem, a_hi + adv, b_hi + adv, idesc, 1u);
+              }
+              mma_commit(empty + stage);  // smem slot free once these MMAs retire
+              if (++stage == kStages) {
+                stage = 0;
+                phase ^= 1;
+              }
+            }
+            mma_commit(tfull + acc);  // chunk accumulator ready for the epilogue warps
+            if (++acc == kAccStages) {
+              acc = 0;
+              acc_phase ^= 1;
+            }
           }
-          mma_commit(empty + stage);  // smem slot free once these MMAs retire
-          if (++stage == kStages) {
-            stage = 0;
-            phase ^= 1;
-          }
-        }
-        mma_commit(tfull + acc);  // accumulator ready for the epilogue
-        if (++acc == kAccStages) {
-          acc = 0;
-          acc_phase ^= 1;
         }
       }
+      __syncwarp();
     }
-    __syncwarp();
-  } else if (warp >= 4) {
-    // ===================== epilogue =====================
-    const int q = warp - 4;  // == warp % 4: TMEM lanes [32q, 32q+32)
+  } else {
+    // ===================== epilogue: chunk drain + tile store =====================
+    reg_inc<232>();
+    const int q = warp & 3;              // TMEM lanes [32q, 32q+32)
+    const int half = (warp - 4) >> 2;    // columns [128 half, 128 half + 128)
     int acc = 0;
     uint32_t acc_phase = 0;
     double sq = 0.0;
@@ -172,60 +211,96 @@ gemm3xtf32_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_con
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
       int tm, tn;
       tile_coords(t, args.tiles_m, args.tiles_n, tm, tn);
-      mbar_wait(tfull + acc, acc_phase);
-      tc_fence_after();
+      if (!tile_needed(args, tm, tn)) continue;
+      float sum[kEpiCols];
+#pragma unroll
+      for (int j = 0; j < kEpiCols; ++j) sum[j] = 0.f;
+      for (int ch = 0; ch < nchunks; ++ch) {
+        mbar_wait(tfull + acc, acc_phase);
+        tc_fence_after();
+#pragma unroll
+        for (int cc = 0; cc < kEpiCols / 32; ++cc) {
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + half * kEpiCols + cc * 32), r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) sum[cc * 32 + j] += __uint_as_float(r[j]);
+        }
+        tc_fence_before();
+        mbar_arrive(tempty + acc);
+        if (++acc == kAccStages) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+      // ---- tile epilogue from registers ----
       const int row = tm * BM + q * 32 + lane;
       const bool row_ok = row < args.M;
+      const int colbase = tn * BN + half * kEpiCols;
       float ra = 0.f;
       if (row_ok) ra = EPI == EPI_GRAM ? args.na[row] : c * args.rowsum[row];
       float* crow = args.C + (long long)row * args.ldc;
       const bool vec_ok = (args.ldc & 3) == 0;
-#pragma unroll 1
-      for (int cc = 0; cc < BN / 32; ++cc) {
-        uint32_t r[32];
-        __syncwarp();
-        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + cc * 32), r);
-        tmem_ld_wait();
-        const int col0 = tn * BN + cc * 32;
-        if (!row_ok || col0 >= args.N) continue;
-        float v[32];
-        if (EPI == EPI_GRAM) {
+      if (EPI == EPI_GRAM) {
+        const int grow = row + args.diag_shift;   // global particle index of this row
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const float nbj = col0 + j < args.N ? __ldg(args.nb + col0 + j) : 0.f;
-            v[j] = fmaxf((ra + nbj) - 2.f * __uint_as_float(r[j]), 0.f);
-          }
-        } else {
-          const float* xrow = args.X + (long long)row * args.ldx;
+        for (int j = 0; j < kEpiCols; ++j) {
+          const int col = colbase + j;
+          const float nbj = col < args.N ? __ldg(args.nb + col) : 0.f;
+          float v = fmaxf((ra + nbj) - 2.f * sum[j], 0.f);
+          // |x_i - x_i|^2 is exactly 0 in the difference form the reference's kernel uses
+          if (col == grow) v = 0.f;
+          sum[j] = v;
+        }
+        if (args.symmetric) {
+          // each unordered pair is produced once (by the tile holding column >= row) and written
+          // to both triangles: D2 is exactly symmetric and the lower tiles are never computed.
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const float xv = col0 + j < args.N ? __ldg(xrow + col0 + j) : 0.f;
-            v[j] = fmaf(ra, xv, __uint_as_float(r[j]));
-            if (col0 + j < args.N) sq += (double)v[j] * (double)v[j];
+          for (int j = 0; j < kEpiCols; ++j) {
+            const int col = colbase + j;
+            // transposed store: the 32 lanes of a warp write 32 consecutive floats of row `col`
+            if (row_ok && col < args.N && col > grow) args.C[(long long)col * args.ldc + row] = sum[j];
           }
         }
-        if (vec_ok && col0 + 32 <= args.N) {
+      } else {
+        const float* xrow = args.X + (long long)row * args.ldx;
 #pragma unroll
-          for (int j = 0; j < 32; j += 4)
-            *reinterpret_cast<float4*>(crow + col0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (col0 + j < args.N) crow[col0 + j] = v[j];
+        for (int j = 0; j < kEpiCols; ++j) {
+          const int col = colbase + j;
+          const bool ok = row_ok && col < args.N;
+          const float xv = ok ? __ldg(xrow + col) - __ldg(args.xmean + col) : 0.f;
+          const float v = fmaf(ra, xv, sum[j]);
+          sum[j] = v;
+          if (ok) sq += (double)v * (double)v;
         }
       }
-      tc_fence_before();
-      mbar_arrive(tempty + acc);
-      if (++acc == kAccStages) {
-        acc = 0;
-        acc_phase ^= 1;
+      if (row_ok) {
+        const int grow = row + args.diag_shift;
+#pragma unroll
+        for (int j = 0; j < kEpiCols; j += 4) {
+          const int col = colbase + j;
+          if (col >= args.N) continue;
+          if (EPI == EPI_GRAM && args.symmetric && col + 3 < grow) continue;   // lower triangle: mirrored
+          const bool lower_mix = EPI == EPI_GRAM && args.symmetric && col < grow;
+          if (vec_ok && col + 4 <= args.N && !lower_mix) {
+            *reinterpret_cast<float4*>(crow + col) = make_float4(sum[j], sum[j + 1], sum[j + 2], sum[j + 3]);
+          } else {
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+              if (col + e < args.N && !(lower_mix && col + e < grow)) crow[col + e] = sum[j + e];
+          }
+        }
       }
     }
     if (EPI == EPI_FORCE) {
       sq = warp_sum(sq);
-      if (lane == 0) red[q] = sq;
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (q == 0 && lane == 0) args.lpart[blockIdx.x] = ((red[0] + red[1]) + red[2]) + red[3];
+      if (lane == 0) red[warp - 4] = sq;
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+      if (warp == 4 && lane == 0) {
+        double tsum = 0.0;
+        for (int w = 0; w < kEpiWarps; ++w) tsum += red[w];
+        args.lpart[blockIdx.x] = tsum;
+      }
     }
   }
   __syncwarp();

@@ -98,7 +98,13 @@ def test_mnist_mlp_smi(cuda, m, S, B, I, H, O, scale255):
     G, E = _run(cuda, md, psi, eps, None, x, y, S, B, n_total / B, 1.0)
     idx = np.broadcast_to(np.arange(B), (m, S, B))
     G64, E64 = oelbo.elbo_grads(om, psi.astype(np.float64), eps, idx, x, y, n_total, 1.0, "normal", torch.float64)
-    assert _rel(G, G64) <= RTOL
+    tol = RTOL
+    if scale255:
+        # raw 0-255 pixels saturate tanh: the gradient is ill-conditioned in fp32.  Calibrate the
+        # tolerance with the fp32 oracle's own distance to the float64 oracle.
+        G32, _ = oelbo.elbo_grads(om, psi, eps, idx, x, y, n_total, 1.0, "normal", torch.float32)
+        tol = max(RTOL, 2.0 * _rel(G32, G64))
+    assert _rel(G, G64) <= tol
     assert np.max(np.abs(E - E64) / np.abs(E64)) <= RTOL
 
 

@@ -28,9 +28,11 @@ def test_adam_matches_oracle(cuda, n):
         ops.adam(xt, mt, vt, torch.from_numpy(F).to(cuda), step, 1e-2)
         xo, mo, vo = ooptim.adam_update(it, -F, xo, mo, vo, 1e-2)
     assert int(step.item()) == 3
-    np.testing.assert_allclose(xt.cpu().numpy(), xo, rtol=1e-5, atol=1e-7)
-    np.testing.assert_allclose(mt.cpu().numpy(), mo, rtol=1e-6, atol=1e-9)
-    np.testing.assert_allclose(vt.cpu().numpy(), vo, rtol=1e-6, atol=1e-12)
+    # elementwise: device FMA contraction vs numpy's separate roundings -> a few ulp of the larger
+    # operand (atol), 1e-5 relative otherwise (north_star tolerance)
+    np.testing.assert_allclose(xt.cpu().numpy(), xo, rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(mt.cpu().numpy(), mo, rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(vt.cpu().numpy(), vo, rtol=1e-5, atol=1e-9)
 
 
 @pytest.mark.parametrize("n", [2, 4097, 179220 * 10])
@@ -47,9 +49,9 @@ def test_adagrad_matches_oracle(cuda, n):
         F[::7] = 0.0     # zero gradients exercise the where(acc > 0, ., 0) branch
         ops.adagrad(xt, at, mt, torch.from_numpy(F).to(cuda), step, 0.8)
         xo, ao, mo = ooptim.adagrad_update(it, -F, xo, ao, mo, 0.8)
-    np.testing.assert_allclose(xt.cpu().numpy(), xo, rtol=1e-5, atol=1e-7)
-    np.testing.assert_allclose(at.cpu().numpy(), ao, rtol=1e-6)
-    np.testing.assert_allclose(mt.cpu().numpy(), mo, rtol=1e-5, atol=1e-8)
+    np.testing.assert_allclose(xt.cpu().numpy(), xo, rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(at.cpu().numpy(), ao, rtol=1e-5)
+    np.testing.assert_allclose(mt.cpu().numpy(), mo, rtol=1e-5, atol=1e-7)
 
 
 def _key(dev, k):
