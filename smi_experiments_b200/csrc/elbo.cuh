@@ -12,7 +12,7 @@
 #include "common.cuh"
 
 constexpr int kGuideKT = 64;      // latent indices per CTA tile
-constexpr int kGuideMaxM = 64;    // mixture components supported by the AutoNormal path
+constexpr int kGuideMaxM = 256;   // mixture components supported by the AutoNormal path
 
 struct ElboWs {
   int* loc_of;     // [L] latent index -> offset of loc in psi

@@ -16,6 +16,7 @@
 namespace {
 
 constexpr float kLog2Pi = 1.8378770664093453f;
+constexpr int kMaxCompPerLane = kGuideMaxM / 32;
 
 __device__ __forceinline__ float softplus_f(float x) {
   // jax.nn.softplus = logaddexp(x, 0)
@@ -152,8 +153,11 @@ guide_weights_kernel(const SmiModelDesc md, const float* __restrict__ QP, const 
   if (wid >= nrows * S) return;
   const int r = wid / S, s = wid - r * S;
   const int L = md.latent_dim;
-  double lq[2] = {-INFINITY, -INFINITY};  // components lane, lane + 32; kept in double: |lq| ~ L
-  for (int c = 0; c < 2; ++c) {
+  double lq[kMaxCompPerLane];  // components lane, lane + 32, ...; kept in double: |lq| ~ L
+  double mx = -INFINITY;
+#pragma unroll
+  for (int c = 0; c < kMaxCompPerLane; ++c) {
+    lq[c] = -INFINITY;
     const int j = lane + 32 * c;
     if (j >= m) continue;
     double a = 0.0;
@@ -161,15 +165,20 @@ guide_weights_kernel(const SmiModelDesc md, const float* __restrict__ QP, const 
     double ld = 0.0;
     for (int b = 0; b < nlb; ++b) ld += logdet_part[(size_t)j * nlb + b];
     lq[c] = -0.5 * a - ld - 0.5 * (double)L * (double)kLog2Pi;
+    mx = fmax(mx, lq[c]);
   }
-  double mx = fmax(lq[0], lq[1]);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-  const float e0 = lq[0] > -INFINITY ? expf((float)(lq[0] - mx)) : 0.f;
-  const float e1 = lq[1] > -INFINITY ? expf((float)(lq[1] - mx)) : 0.f;
-  const float sum = warp_sum(e0 + e1);
-  if (lane < m) W[((size_t)r * S + s) * m + lane] = e0 / sum;
-  if (lane + 32 < m) W[((size_t)r * S + s) * m + lane + 32] = e1 / sum;
+  float e[kMaxCompPerLane], part = 0.f;
+#pragma unroll
+  for (int c = 0; c < kMaxCompPerLane; ++c) {
+    e[c] = lq[c] > -INFINITY ? expf((float)(lq[c] - mx)) : 0.f;
+    part += e[c];
+  }
+  const float sum = warp_sum(part);
+#pragma unroll
+  for (int c = 0; c < kMaxCompPerLane; ++c)
+    if (lane + 32 * c < m) W[((size_t)r * S + s) * m + lane + 32 * c] = e[c] / sum;
   if (lane == 0) {
     float logjac = 0.f;  // log |d theta / d u| = u on exp sites
     for (int t = 0; t < md.n_sites; ++t)
@@ -243,6 +252,75 @@ guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, 
     G[(size_t)r * d + rho_of[k]] = b * inv * sigmoid_f(psi[(size_t)i * d + rho_of[k]]);
   }
   if (kt == 0 && elbo && threadIdx.x < 32) {  // mean_s (tau log p - log q), fixed order
+    double v = 0.0;
+    for (int s = threadIdx.x; s < S; s += 32)
+      v += (double)tau * (double)LOGP[(size_t)r * S + s] - (double)LOGQ[(size_t)r * S + s];
+    v = warp_sum(v);
+    if (threadIdx.x == 0) elbo[r] = (float)(v / (double)S);
+  }
+}
+
+// Same as guide_grad_kernel for m > 64: the per-latent component tables live in shared memory
+// (mt / qt [m][64]) instead of registers.
+__global__ void __launch_bounds__(256)
+guide_grad_big_kernel(const float* __restrict__ psi, const float* __restrict__ eps, const float* __restrict__ MU,
+                      const float* __restrict__ SIG, const float* __restrict__ ISIG, const float* __restrict__ W,
+                      const float* __restrict__ DZ, const float* __restrict__ LOGP, const float* __restrict__ LOGQ,
+                      const int* __restrict__ loc_of, const int* __restrict__ rho_of, const int* __restrict__ tr_of,
+                      int m, int S, int L, int d, float tau, int row0, float* __restrict__ G,
+                      float* __restrict__ elbo) {
+  extern __shared__ float sm[];
+  float* wt = sm;                          // [S][m]
+  float* mt = wt + (size_t)S * m;          // [m][64]
+  float* qt = mt + (size_t)m * 64;         // [m][64]
+  float* part = qt + (size_t)m * 64;       // [4][64][2]
+  const int kt = blockIdx.x, r = blockIdx.y, i = row0 + r;
+  const int kk = threadIdx.x & 63, sg = threadIdx.x >> 6;
+  const int k = kt * kGuideKT + kk;
+  for (int t = threadIdx.x; t < S * m; t += blockDim.x) wt[t] = W[(size_t)r * S * m + t];
+  for (int t = threadIdx.x; t < m * 64; t += blockDim.x) {
+    const int j = t >> 6, c = t & 63, kc = kt * kGuideKT + c;
+    float mu = 0.f, q = 0.f;
+    if (kc < L) {
+      mu = MU[(size_t)j * L + kc];
+      const float is = ISIG[(size_t)j * L + kc];
+      q = is * is;
+    }
+    mt[t] = mu;
+    qt[t] = q;
+  }
+  __syncthreads();
+  float gl = 0.f, gs = 0.f;
+  if (k < L) {
+    const float mu_i = MU[(size_t)i * L + k], sg_i = SIG[(size_t)i * L + k], is_i = ISIG[(size_t)i * L + k];
+    const float jac = tr_of[k] == SMI_T_EXP ? 1.f : 0.f;
+    for (int s = sg; s < S; s += 4) {
+      const size_t e = ((size_t)r * S + s) * L + k;
+      const float ep = eps[e];
+      const float z = fmaf(sg_i, ep, mu_i);
+      float T = 0.f;
+      for (int j = 0; j < m; ++j) T = fmaf(wt[s * m + j] * (z - mt[j * 64 + kk]), qt[j * 64 + kk], T);
+      const float du = fmaf(tau, DZ[e], T) + jac;
+      const float wi = wt[s * m + i];
+      gl += du - wi * ep * is_i;
+      gs += du * ep - wi * (ep * ep - 1.f) * is_i;
+    }
+  }
+  part[(sg * 64 + kk) * 2] = gl;
+  part[(sg * 64 + kk) * 2 + 1] = gs;
+  __syncthreads();
+  if (sg == 0 && k < L) {
+    float a = 0.f, b = 0.f;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      a += part[(g * 64 + kk) * 2];
+      b += part[(g * 64 + kk) * 2 + 1];
+    }
+    const float inv = 1.f / (float)S;
+    G[(size_t)r * d + loc_of[k]] = a * inv;
+    G[(size_t)r * d + rho_of[k]] = b * inv * sigmoid_f(psi[(size_t)i * d + rho_of[k]]);
+  }
+  if (kt == 0 && elbo && threadIdx.x < 32) {
     double v = 0.0;
     for (int s = threadIdx.x; s < S; s += 32)
       v += (double)tau * (double)LOGP[(size_t)r * S + s] - (double)LOGQ[(size_t)r * S + s];
@@ -355,7 +433,17 @@ int smi_guide_grad(const SmiModelDesc& md, const float* psi, const float* eps, i
   if (m <= 8) return launch_grad<8>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
   if (m <= 16) return launch_grad<16>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
   if (m <= 32) return launch_grad<32>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
-  return launch_grad<64>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
+  if (m <= 64) return launch_grad<64>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
+  const size_t smem = ((size_t)S * m + (size_t)2 * m * 64 + 4 * 64 * 2) * sizeof(float);
+  if (smem > 220 * 1024) SMI_FAIL(SMI_ELIMIT, "guide_grad: S * m = %d x %d too large for shared memory", S, m);
+  SMI_CUDA_OK(cudaFuncSetAttribute(guide_grad_big_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid(w.nkt, nrows);
+  SMI_PROF_BEGIN(st);
+  guide_grad_big_kernel<<<grid, 256, smem, st>>>(psi, eps, w.MU, w.SIG, w.ISIG, w.W, w.DZ, w.LOGP, w.LOGQ, w.loc_of,
+                                                 w.rho_of, w.tr_of, m, S, md.latent_dim, md.particle_dim, tau, row0,
+                                                 G, elbo);
+  SMI_LAUNCH_OK_N("guide_grad_big_kernel", st);
+  return SMI_OK;
 }
 
 int smi_delta_gather(const SmiModelDesc& md, const float* psi, int row0, int nrows, ElboWs& w, cudaStream_t st) {

@@ -1,0 +1,250 @@
+"""Particle-row sharding across the GPUs of one node.
+
+The reference is single-device; this is the scale-out the north star adds.  One process per GPU
+(torch.distributed, NCCL over NVLink).  Rank r owns particle rows [r m/R, (r+1) m/R): their
+optimizer state, their ELBO gradients and their rows of D, K and F.  Per step
+
+  1. all-gather particles X                  (m d fp32 across the node)
+  2. all-gather scores G  -- on a side stream, overlapped with 3
+  3. local rows of the Gram / distance matrix; exact median by radix select:
+       3 x (local histogram -> integer all-reduce SUM of 2048 bins -> scan), then a tail pass
+       (all-reduce SUM of count(<= a), MIN of min(> a))            -- integers: h is bit-identical
+       for every world size
+  4. local rows of the force; all-reduce SUM of sum F^2 (double)  -> loss
+  5. local optimizer update
+
+`stein_force_rows` holds only the choreography; the per-rank compute comes from a backend
+object (LibsmiRows: the CUDA kernels through the C ABI).  The CPU test-suite drives the same
+choreography over gloo with a NumPy stand-in backend (tests/test_dist_gloo.py).
+"""
+
+import ctypes as C
+import math
+
+import torch
+import torch.distributed as dist
+
+from . import _lib, ops
+from .optim import OptimState
+from .steinvi import SteinVI, SteinVIState
+
+
+def partition(m, world, rank):
+    """Contiguous equal row blocks (m must divide evenly: all-gathers are in place)."""
+    if m % world != 0:
+        raise ValueError("num_stein_particles (%d) must be a multiple of the world size (%d)" % (m, world))
+    per = m // world
+    return rank * per, per
+
+
+class LibsmiRows:
+    """Per-rank stages of the row-sharded Stein force on the GPU (smi_stein_rows_* in include/smi.h)."""
+
+    def __init__(self, m, d, row0, rows, device):
+        self.m, self.d, self.row0, self.rows, self.device = m, d, row0, rows, device
+        lib = _lib.load()
+        self.ws = torch.empty(int(lib.smi_stein_rows_workspace_bytes(rows, m, d)), dtype=torch.uint8, device=device)
+        self.hist_buf = torch.zeros(2048, dtype=torch.int32, device=device)
+        self.cnt_min = torch.zeros(2, dtype=torch.int32, device=device)
+        self.h = torch.zeros(1, dtype=torch.float32, device=device)
+        self.sumsq = torch.zeros(1, dtype=torch.float64, device=device)
+        self.F = torch.empty(rows, d, dtype=torch.float32, device=device)
+        self.cnt64 = torch.zeros(1, dtype=torch.int64, device=device)
+        self.min64 = torch.zeros(1, dtype=torch.int64, device=device)
+
+    def _w(self):
+        return ops._ptr(self.ws), self.ws.numel()
+
+    def dist(self, X):
+        _lib.call("smi_stein_rows_dist", ops._ptr(X), self.m, self.d, self.row0, self.rows, *self._w(), ops._stream())
+
+    def hist(self, p):
+        _lib.call("smi_stein_rows_hist", self.m, self.d, self.row0, self.rows, p, ops._ptr(self.hist_buf), *self._w(),
+                  ops._stream())
+        return self.hist_buf
+
+    def scan(self, p, median_mode):
+        _lib.call("smi_stein_rows_scan", self.m, self.d, self.row0, self.rows, p, median_mode,
+                  ops._ptr(self.hist_buf), *self._w(), ops._stream())
+
+    def tail(self):
+        """(count(<= a), min(> a)) of the local rows as int64 tensors (0xffffffff = none above)."""
+        _lib.call("smi_stein_rows_tail", self.m, self.d, self.row0, self.rows, ops._ptr(self.cnt_min), *self._w(),
+                  ops._stream())
+        wide = self.cnt_min.to(torch.int64) & 0xFFFFFFFF
+        self.cnt64.copy_(wide[0:1])
+        self.min64.copy_(wide[1:2])
+        return self.cnt64, self.min64
+
+    def bandwidth(self, cnt64, min64, median_mode, alpha, h_fixed):
+        if cnt64 is not None:
+            self.cnt_min.copy_(torch.cat([cnt64, min64]).to(torch.int32))     # wraps back to the uint32 bits
+        _lib.call("smi_stein_rows_bandwidth", self.m, self.d, self.row0, self.rows, median_mode, alpha, h_fixed,
+                  ops._ptr(self.cnt_min[0:1]), ops._ptr(self.cnt_min[1:2]), ops._ptr(self.h), *self._w(),
+                  ops._stream())
+        return self.h
+
+    def force(self, X, G, c_att):
+        _lib.call("smi_stein_rows_force", ops._ptr(X), ops._ptr(G), self.m, self.d, self.row0, self.rows, c_att,
+                  ops._ptr(self.F), ops._ptr(self.sumsq), *self._w(), ops._stream())
+        return self.F, self.sumsq
+
+
+def stein_force_rows(backend, X, G, group=None, alpha=1.0, c_att=1.0, median_mode=_lib.MEDIAN_JAX_FP32_INDEX,
+                     h_fixed=0.0, wait_G=None):
+    """Row-sharded Stein force.  X, G: ALL m particles / scores (already all-gathered; G may still
+    be in flight -- `wait_G()` is called right before the force stage).  Returns (F_rows, loss, h)."""
+    m = backend.m
+    backend.dist(X)
+    cnt = mn = None
+    if not (h_fixed > 0.0 or m == 1):
+        for p in range(3):
+            hist = backend.hist(p)
+            dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)     # integers: exact, order-free
+            backend.scan(p, median_mode)
+        cnt, mn = backend.tail()
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
+        dist.all_reduce(mn, op=dist.ReduceOp.MIN, group=group)
+    h = backend.bandwidth(cnt, mn, median_mode, alpha, h_fixed)
+    if wait_G is not None:
+        wait_G()
+    F, sumsq = backend.force(X, G, c_att)
+    dist.all_reduce(sumsq, op=dist.ReduceOp.SUM, group=group)
+    loss = torch.sqrt(sumsq).to(torch.float32)
+    return F, loss, h
+
+
+class ShardedSteinVI(SteinVI):
+    """SteinVI with the particles row-sharded over the ranks of the default process group.
+    Same surface as SteinVI; `state.optim_state.x` is the full (m, d) particle matrix (replicated,
+    all-gathered every step), the optimizer slots cover the local rows only."""
+
+    def __init__(self, *args, group=None, **kwargs):
+        kwargs.setdefault("use_cuda_graph", False)
+        super().__init__(*args, **kwargs)
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.row0, self.nrows = partition(self.num_stein_particles, self.world, self.rank)
+        self._rows_backend = None
+        self._side = None
+
+    def _graphable(self):
+        return False
+
+    def init(self, rng_key, *args, **kwargs):
+        st = super().init(rng_key, *args, **kwargs)         # every rank draws the same full init
+        x = st.optim_state.x
+        r0, n = self.row0, self.nrows
+        self._state = SteinVIState(OptimState(st.optim_state.step, x, torch.zeros_like(x[r0:r0 + n]),
+                                              torch.zeros_like(x[r0:r0 + n])), st.rng_key)
+        return self._state
+
+    def _own(self, state):
+        if getattr(self, "_state", None) is not None and state.optim_state.x is self._state.optim_state.x:
+            return self._state
+        raise ValueError("ShardedSteinVI updates the state its own init() returned")
+
+    def _alloc(self, data):
+        b = super()._alloc(data)
+        if "G_all" not in b:
+            m, S, L, d = self.num_stein_particles, self.num_elbo_particles, self.layout.latent_dim, self.layout.particle_dim
+            dev, n = self.device, self.nrows
+            normal = self.guide.kind == _lib.GUIDE_NORMAL
+            b["eps"] = torch.empty(n, S, L, dtype=torch.float32, device=dev) if normal else None
+            b["idx"] = torch.empty(n, S, data["B"], dtype=torch.int32, device=dev) if data["idx"] else None
+            b["G_all"] = b["G"]
+            b["elbo"] = torch.empty(n, dtype=torch.float32, device=dev)
+        return b
+
+    def _launch(self, st, b, data, do_update, ring=None):
+        m, S, d = self.num_stein_particles, self.num_elbo_particles, self.layout.particle_dim
+        r0, n = self.row0, self.nrows
+        os_ = st.optim_state
+        X = os_.x
+        ops.prng_step(self.md, st.rng_key, b["key_next"], m, S, data["n_total"], data["B"] if data["idx"] else 0,
+                      r0, n, b["eps"], b["idx"])
+        G_rows = b["G_all"][r0:r0 + n]
+        ops.elbo_grad(self.md, X, b["eps"], b["idx"], data["x"], data["y"], S, max(data["B"], 1), data["lik_scale"],
+                      self._tau(), r0, n, G_rows, b["elbo"], self._ws_elbo)
+        if m <= 64:
+            # small m: every rank evaluates the (tiny) full force after gathering the scores
+            dist.all_gather_into_tensor(b["G_all"], G_rows, group=self.group)
+            nbytes = _lib.load().smi_stein_force_workspace_bytes(m, d, _lib.PATH_SMALL)
+            w = self._ws_stein.get(nbytes, self.device)
+            _lib.call("smi_stein_force_f32", ops._ptr(X), ops._ptr(b["G_all"]), m, d, self.c_att,
+                      self.repulsion_temperature, self.kernel_fn.median_mode, self.kernel_fn.h_fixed, _lib.PATH_SMALL,
+                      ops._ptr(b["F"]), ops._ptr(b["loss"]), ops._ptr(b["h"]), ops._ptr(w), w.numel(), ops._stream())
+            F_rows = b["F"][r0:r0 + n]
+        else:
+            if self._rows_backend is None:
+                self._rows_backend = LibsmiRows(m, d, r0, n, self.device)
+                self._side = torch.cuda.Stream(device=self.device)
+            cur = torch.cuda.current_stream()
+            self._side.wait_stream(cur)
+            with torch.cuda.stream(self._side):         # scores travel while the distances are computed
+                dist.all_gather_into_tensor(b["G_all"], G_rows, group=self.group)
+            F_rows, loss, h = stein_force_rows(self._rows_backend, X, b["G_all"], self.group,
+                                               self.repulsion_temperature, self.c_att, self.kernel_fn.median_mode,
+                                               self.kernel_fn.h_fixed, wait_G=lambda: cur.wait_stream(self._side))
+            b["loss"].copy_(loss)
+            b["h"].copy_(h)
+        if do_update:
+            rows_state = OptimState(os_.step, X[r0:r0 + n], os_.a, os_.b)
+            self.optim.update(F_rows, rows_state, -1.0)
+            if ring is not None:
+                _lib.call("smi_loss_record_f32", ops._ptr(b["loss"]), ops._ptr(os_.step), ops._ptr(ring),
+                          ring.numel(), ops._stream())
+            st.rng_key.copy_(b["key_next"])
+            dist.all_gather_into_tensor(X, X[r0:r0 + n], group=self.group)      # in place
+
+
+def bench_sharded_force(m, d, reps, flush, pk):
+    """bench.py's Stein-force sweep point at N > 1: rank r holds rows of X, G; one timed unit =
+    all-gather X, all-gather G (overlapped), row-sharded force.  Max over ranks."""
+    import numpy as np
+    world, rank = dist.get_world_size(), dist.get_rank()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    r0, n = partition(m, world, rank)
+    gen = torch.Generator(device=dev).manual_seed(4 + rank)
+    X = torch.empty(m, d, device=dev)
+    G = torch.empty(m, d, device=dev)
+    X[r0:r0 + n] = torch.randn(n, d, device=dev, generator=gen)
+    G[r0:r0 + n] = torch.randn(n, d, device=dev, generator=gen)
+    be = LibsmiRows(m, d, r0, n, dev)
+    side = torch.cuda.Stream(device=dev)
+
+    def unit():
+        cur = torch.cuda.current_stream()
+        dist.all_gather_into_tensor(X, X[r0:r0 + n])
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            dist.all_gather_into_tensor(G, G[r0:r0 + n])
+        return stein_force_rows(be, X, G, wait_G=lambda: cur.wait_stream(side))
+
+    for _ in range(2):
+        unit()
+    torch.cuda.synchronize()
+    dist.barrier()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+    for a, b in evs:
+        flush()
+        dist.barrier()
+        a.record()
+        F, loss, h = unit()
+        b.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([float(np.mean([a.elapsed_time(b) for a, b in evs]))], dtype=torch.float64, device=dev)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms)
+    W = 4.0 * m * m * d
+    tf32_peak = 1100.0 * pk["bf16"] / 2250.0
+    peak = world * tf32_peak / 3.0
+    nv_bytes = 2.0 * (world - 1) / world * m * d * 4.0          # received per rank per step
+    t_comm = nv_bytes / 770e9 * 1e3
+    t_flop = W / world / (tf32_peak / 3.0 * 1e12) * 1e3
+    return dict(m=m, d=d, ms=ms, gflops=W / ms / 1e6, flop_per_step=W, loss=float(loss), h=float(h),
+                roofline=dict(bound="tensor", achieved=W / ms / 1e9, peak=peak, unit="TFLOP/s",
+                              frac=(W / ms / 1e9) / peak, traffic=None,
+                              nvlink_bytes_per_rank=nv_bytes, t_comm_ms_at_770GBs=t_comm, t_flop_ms=t_flop,
+                              note="N x (TF32 peak / 3); fused target = max(t_flop, t_comm)"))
