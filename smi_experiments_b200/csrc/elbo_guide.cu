@@ -224,14 +224,15 @@ guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, 
     }
     const float mu_i = MU[(size_t)i * L + k], sg_i = SIG[(size_t)i * L + k], is_i = ISIG[(size_t)i * L + k];
     const float jac = tr_of[k] == SMI_T_EXP ? 1.f : 0.f;
+#pragma unroll 4
     for (int s = sg; s < S; s += 4) {
       const size_t e = ((size_t)r * S + s) * L + k;
-      const float ep = eps[e];
+      const float ep = __ldg(eps + e);
       const float z = fmaf(sg_i, ep, mu_i);
       float T = 0.f;
 #pragma unroll
       for (int j = 0; j < MP; ++j) T = fmaf(wt[s * MP + j] * (z - mu[j]), q[j], T);
-      const float du = fmaf(tau, DZ[e], T) + jac;
+      const float du = fmaf(tau, __ldg(DZ + e), T) + jac;
       const float wi = wt[s * MP + i];
       gl += du - wi * ep * is_i;
       gs += du * ep - wi * (ep * ep - 1.f) * is_i;
@@ -430,9 +431,14 @@ static int launch_grad(const SmiModelDesc& md, const float* psi, const float* ep
 
 int smi_guide_grad(const SmiModelDesc& md, const float* psi, const float* eps, int m, int S, float tau,
                    int row0, int nrows, ElboWs& w, float* G, float* elbo, cudaStream_t st) {
+  if (m <= 4) return launch_grad<4>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
   if (m <= 8) return launch_grad<8>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
+  if (m <= 12) return launch_grad<12>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
   if (m <= 16) return launch_grad<16>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
+  if (m <= 20) return launch_grad<20>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
+  if (m <= 24) return launch_grad<24>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
   if (m <= 32) return launch_grad<32>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
+  if (m <= 48) return launch_grad<48>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
   if (m <= 64) return launch_grad<64>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
   const size_t smem = ((size_t)S * m + (size_t)2 * m * 64 + 4 * 64 * 2) * sizeof(float);
   if (smem > 220 * 1024) SMI_FAIL(SMI_ELIMIT, "guide_grad: S * m = %d x %d too large for shared memory", S, m);

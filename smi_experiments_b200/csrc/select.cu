@@ -34,12 +34,17 @@ __device__ __forceinline__ void hist_add(unsigned* sh, unsigned key, bool valid,
   }
 }
 
+// Per-warp private histograms (8 warps x 2048 bins x 4 B = 64 KB of shared memory): distances of
+// high-dimensional particles concentrate in a handful of bins, so a CTA-wide histogram serialises
+// on a few addresses; with one histogram per warp the only contention left is inside the warp and
+// __match_any_sync folds that into one atomic per distinct digit.
 __global__ void __launch_bounds__(kThreads)
 select_hist(const unsigned* __restrict__ keys, size_t n, int pass, const unsigned* __restrict__ state,
             unsigned* __restrict__ hist) {
-  __shared__ unsigned sh[kBins];
-  for (int t = threadIdx.x; t < kBins; t += blockDim.x) sh[t] = 0u;
+  extern __shared__ unsigned sh_all[];  // [kThreads / 32][kBins]
+  for (int t = threadIdx.x; t < kBins * (kThreads / 32); t += blockDim.x) sh_all[t] = 0u;
   __syncthreads();
+  unsigned* sh = sh_all + (threadIdx.x >> 5) * kBins;
   const int shift = pass_shift(pass), bits = pass_bits(pass);
   const unsigned prefix = pass == 0 ? 0u : state[0];
   const int hs = shift + bits;  // bits above this pass's digit
@@ -48,15 +53,20 @@ select_hist(const unsigned* __restrict__ keys, size_t n, int pass, const unsigne
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   // every lane of a warp runs the same trip count (ballot/match need the full warp)
   const size_t base = (size_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31);
-  for (size_t i0 = base; i0 < n4; i0 += stride) {
-    const size_t i = i0 + (threadIdx.x & 31);
-    const bool in = i < n4;
-    uint4 v = make_uint4(0, 0, 0, 0);
+  for (size_t i0 = base; i0 < n4; i0 += 2 * stride) {
+    const size_t i = i0 + (threadIdx.x & 31), j = i + stride;
+    const bool in = i < n4, jn = j < n4;
+    uint4 v = make_uint4(0, 0, 0, 0), u = make_uint4(0, 0, 0, 0);
     if (in) v = k4[i];
+    if (jn) u = k4[j];
     hist_add(sh, v.x, in && (pass == 0 || (v.x >> hs) == prefix), shift, bits);
     hist_add(sh, v.y, in && (pass == 0 || (v.y >> hs) == prefix), shift, bits);
     hist_add(sh, v.z, in && (pass == 0 || (v.z >> hs) == prefix), shift, bits);
     hist_add(sh, v.w, in && (pass == 0 || (v.w >> hs) == prefix), shift, bits);
+    hist_add(sh, u.x, jn && (pass == 0 || (u.x >> hs) == prefix), shift, bits);
+    hist_add(sh, u.y, jn && (pass == 0 || (u.y >> hs) == prefix), shift, bits);
+    hist_add(sh, u.z, jn && (pass == 0 || (u.z >> hs) == prefix), shift, bits);
+    hist_add(sh, u.w, jn && (pass == 0 || (u.w >> hs) == prefix), shift, bits);
   }
   if (blockIdx.x == 0 && threadIdx.x < 32) {  // tail (n % 4 elements)
     const size_t i = n4 * 4 + threadIdx.x;
@@ -65,8 +75,12 @@ select_hist(const unsigned* __restrict__ keys, size_t n, int pass, const unsigne
     hist_add(sh, key, in && (pass == 0 || (key >> hs) == prefix), shift, bits);
   }
   __syncthreads();
-  for (int t = threadIdx.x; t < kBins; t += blockDim.x)
-    if (sh[t]) atomicAdd(hist + t, sh[t]);
+  for (int t = threadIdx.x; t < kBins; t += blockDim.x) {
+    unsigned c = 0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) c += sh_all[w * kBins + t];
+    if (c) atomicAdd(hist + t, c);
+  }
 }
 
 // One warp: locate the bin holding the remaining rank, update the state, clear the histogram.
@@ -164,7 +178,7 @@ __global__ void select_fixed_h(float h, float alpha, int m, float* __restrict__ 
   }
 }
 
-int hist_grid() { return smi_num_sms() * 4; }
+int hist_grid() { return smi_num_sms() * 3; }  // 64 KB of histograms per CTA: 3 CTAs per SM
 
 }  // namespace
 
@@ -172,7 +186,13 @@ size_t smi_select_workspace_bytes() { return 256 + kBins * sizeof(unsigned) + 25
 
 int smi_select_hist(const float* D2, size_t n, int pass, unsigned* state, unsigned* hist, cudaStream_t st) {
   SMI_PROF_BEGIN(st);
-  select_hist<<<hist_grid(), kThreads, 0, st>>>((const unsigned*)D2, n, pass, state, hist);
+  constexpr size_t kHistSmem = (size_t)kBins * (kThreads / 32) * sizeof(unsigned);
+  static bool attr = false;
+  if (!attr) {
+    SMI_CUDA_OK(cudaFuncSetAttribute(select_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kHistSmem));
+    attr = true;
+  }
+  select_hist<<<hist_grid(), kThreads, kHistSmem, st>>>((const unsigned*)D2, n, pass, state, hist);
   SMI_LAUNCH_OK_N("select_hist", st);
   return SMI_OK;
 }

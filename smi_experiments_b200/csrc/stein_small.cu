@@ -18,42 +18,50 @@
 namespace {
 
 constexpr int kPairThreads = 256;
-constexpr int kForceThreads = 256;
+constexpr int kForceThreads = 128;  // one column per thread: small CTAs spread d over the SMs
+constexpr int kMaxPairs = 64 * 65 / 2;
+constexpr int kPairSlices = 4;
 
 __host__ __device__ inline int pairs_of(int m) { return m * (m + 1) / 2; }
 
 // ---------------------------------------------------------------------------------------
+// grid (column chunks, pair slices): every CTA stages its column chunk of all m particles and its
+// warps take pairs p = slice * warps + w, stepping by the total warp count of the chunk.
 __global__ void __launch_bounds__(kPairThreads)
 stein_small_pairs(const float* __restrict__ X, int m, int d, int dc, float* __restrict__ partial) {
   extern __shared__ float xs[];  // [m][dc]
+  __shared__ unsigned char pi[kMaxPairs], pj[kMaxPairs];
   const int k0 = blockIdx.x * dc;
   const int len = min(dc, d - k0);
   for (int t = threadIdx.x; t < m * dc; t += blockDim.x) {
     const int i = t / dc, k = t - i * dc;
     xs[t] = k < len ? __ldg(X + (size_t)i * d + k0 + k) : 0.f;
   }
+  const int np = pairs_of(m);
+  for (int i = threadIdx.x; i < m; i += blockDim.x) {  // row i starts at pair index i*m - i(i-1)/2
+    const int base = i * m - (i * (i - 1)) / 2;
+    for (int j = i; j < m; ++j) {
+      pi[base + j - i] = (unsigned char)i;
+      pj[base + j - i] = (unsigned char)j;
+    }
+  }
   __syncthreads();
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
-  const int np = pairs_of(m);
   float* out = partial + (size_t)blockIdx.x * np * 2;
-  int p = 0;
-  for (int i = 0; i < m; ++i) {
-    for (int j = i; j < m; ++j, ++p) {
-      if (p % nw != w) continue;  // warp-uniform
-      const float* xi = xs + i * dc;
-      const float* xj = xs + j * dc;
-      float g = 0.f, s = 0.f;
-      for (int k = lane; k < dc; k += 32) {
-        const float a = xi[k], b = xj[k], df = a - b;
-        g = fmaf(a, b, g);
-        s = fmaf(df, df, s);
-      }
-      g = warp_sum(g);
-      s = warp_sum(s);
-      if (lane == 0) {
-        out[2 * p] = g;
-        out[2 * p + 1] = s;
-      }
+  for (int p = blockIdx.y * nw + w; p < np; p += nw * gridDim.y) {
+    const float* xi = xs + pi[p] * dc;
+    const float* xj = xs + pj[p] * dc;
+    float g = 0.f, sq = 0.f;
+    for (int k = lane; k < dc; k += 32) {
+      const float a = xi[k], b = xj[k], df = a - b;
+      g = fmaf(a, b, g);
+      sq = fmaf(df, df, sq);
+    }
+    g = warp_sum(g);
+    sq = warp_sum(sq);
+    if (lane == 0) {
+      out[2 * p] = g;
+      out[2 * p + 1] = sq;
     }
   }
 }
@@ -104,11 +112,14 @@ __global__ void __launch_bounds__(256) stein_small_finish(FinishArgs a) {
   __shared__ float s_h;
   const int np = pairs_of(m);
   // (a) deterministic reduction of the chunk partials, in double
-  for (int p = threadIdx.x; p < np; p += blockDim.x) {
+  for (int p = threadIdx.x; p < np; p += blockDim.x) {  // one thread per pair, fixed order
     double g = 0.0, s = 0.0;
-    for (int c = 0; c < a.nchunk; ++c) {
-      g += (double)a.partial[((size_t)c * np + p) * 2];
-      s += (double)a.partial[((size_t)c * np + p) * 2 + 1];
+    const float2* src = reinterpret_cast<const float2*>(a.partial) + p;
+#pragma unroll 8
+    for (int c = 0; c < a.nchunk; ++c) {  // independent loads: the unrolled batch hides the L2 latency
+      const float2 v = src[(size_t)c * np];
+      g += (double)v.x;
+      s += (double)v.y;
     }
     // decode p -> (i, j), i <= j
     int i = 0, rem = p;
@@ -218,7 +229,7 @@ stein_small_force(const float* __restrict__ X, const float* __restrict__ G, int 
 }  // namespace
 
 // ---------------------------------------------------------------------------------------
-static int small_dc(int m) { return m <= 32 ? 256 : 128; }
+static int small_dc(int m) { return m <= 32 ? 128 : 64; }
 static int small_nchunk(int m, int d) { return (d + small_dc(m) - 1) / small_dc(m); }
 static int force_blocks(int d) { return (d + kForceThreads - 1) / kForceThreads; }
 
@@ -259,7 +270,8 @@ int smi_stein_small_run(const float* X, const float* G, int m, int d, float c_at
   double* lpart = ar.take<double>(force_blocks(d));
 
   SMI_PROF_BEGIN(st);
-  stein_small_pairs<<<nchunk, kPairThreads, (size_t)m * dc * sizeof(float), st>>>(X, m, d, dc, partial);
+  stein_small_pairs<<<dim3(nchunk, kPairSlices), kPairThreads, (size_t)m * dc * sizeof(float), st>>>(X, m, d, dc,
+                                                                                                   partial);
   SMI_LAUNCH_OK_N("stein_small_pairs", st);
 
   FinishArgs fa;

@@ -108,6 +108,23 @@ def test_mnist_mlp_smi(cuda, m, S, B, I, H, O, scale255):
     assert np.max(np.abs(E - E64) / np.abs(E64)) <= RTOL
 
 
+def test_many_particles_mixture(cuda):
+    """m > 64 mixture components (weak-scaling runs: 20 particles per GPU x 8 GPUs = 160)."""
+    from smi_experiments_b200 import models
+    pm, om = models.uci_bnn(3), omodels.uci_bnn(3)
+    m, S, N, B = 70, 3, 12, 12
+    md, psi, eps, rng, L, d = _setup(pm, om, "normal", m, S, seed=9)
+    x = rng.standard_normal((N, 3)).astype(np.float32)
+    y = rng.standard_normal(N).astype(np.float32)
+    G, E = _run(cuda, md, psi, eps, None, x, y, S, B, 1.0, 1.0)
+    G64, E64 = oelbo.elbo_grads(om, psi.astype(np.float64), eps, None, x, y, N, 1.0, "normal", torch.float64)
+    assert _rel(G, G64) <= RTOL
+    assert np.max(np.abs(E - E64) / np.abs(E64)) <= RTOL
+    # rows of a sharded call agree with the full call
+    G2, E2 = _run(cuda, md, psi, eps[60:70], None, x, y, S, B, 1.0, 1.0, row0=60, nrows=10)
+    assert np.array_equal(G2, G[60:70])
+
+
 def test_row_sharding(cuda):
     """Rows [row0, row0 + nrows) computed alone equal those rows of the full call."""
     from smi_experiments_b200 import models
