@@ -76,7 +76,12 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
   float* it = mt + kGuideKT * 32;       // [64][32]
   const int kt = blockIdx.x, r = blockIdx.y, i = row0 + r;
   const int k0 = kt * kGuideKT;
-  const int ts = threadIdx.x & 31, tj = threadIdx.x >> 5;
+  // component chunks of JCH = 4 * njg <= 32 columns chosen to divide m evenly (m = 20 -> one chunk
+  // of 20, not a padded 32); thread = (draw group ts < 32, component group tj < njg)
+  const int nch = (m + 31) / 32;
+  const int njg = (((m + nch - 1) / nch) + 3) >> 2, JCH = njg << 2;
+  const int tj = threadIdx.x % njg, ts = threadIdx.x / njg;
+  const bool lane_on = ts < 32;
   for (int sb = 0; sb < S; sb += 128) {
     __syncthreads();
     // stage z tile (and write Z): coalesced along k
@@ -91,13 +96,13 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
       }
       zt[kk * 128 + (sl ^ ((kk & 7) << 2))] = z;
     }
-    for (int jb = 0; jb < m; jb += 32) {
+    for (int jb = 0; jb < m; jb += JCH) {
       __syncthreads();
-      for (int t = threadIdx.x; t < 32 * kGuideKT; t += blockDim.x) {
+      for (int t = threadIdx.x; t < JCH * kGuideKT; t += blockDim.x) {
         const int jl = t / kGuideKT, kk = t - jl * kGuideKT;
         const int j = jb + jl, k = k0 + kk;
         float mu = 0.f, is = 0.f;  // is = 0 masks padded latents and components
-        if (j < m && k < L) {
+        if (j < m && jl < JCH && k < L) {
           mu = MU[(size_t)j * L + k];
           is = ISIG[(size_t)j * L + k];
         }
@@ -106,6 +111,7 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
         it[kk * 32 + c] = is;
       }
       __syncthreads();
+      if (!lane_on) continue;   // (no barrier below this point inside the chunk)
       float acc[4][4];
 #pragma unroll
       for (int a = 0; a < 4; ++a)
@@ -135,7 +141,7 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
           const int j = jb + tj * 4 + b;
-          if (j < m) QP[(((size_t)r * nkt + kt) * S + s) * m + j] = acc[a][b];
+          if (j < m && tj * 4 + b < JCH) QP[(((size_t)r * nkt + kt) * S + s) * m + j] = acc[a][b];
         }
       }
     }
@@ -261,9 +267,12 @@ guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, 
   }
 }
 
-// Same as guide_grad_kernel for m > 64: the per-latent component tables live in shared memory
-// (mt / qt [m][64]) instead of registers.
-__global__ void __launch_bounds__(256)
+// Same as guide_grad_kernel for m > 64 (weak-scaling runs: 20 particles per GPU x N GPUs).  The
+// component tables no longer fit in registers, so the roles are swapped: each thread keeps its
+// draws (z_s and the running T_s, 16 of each per pass) in registers and streams the components
+// through in chunks of 16.
+constexpr int kBigNS = 16, kBigJC = 16;
+__global__ void __launch_bounds__(256, 2)
 guide_grad_big_kernel(const float* __restrict__ psi, const float* __restrict__ eps, const float* __restrict__ MU,
                       const float* __restrict__ SIG, const float* __restrict__ ISIG, const float* __restrict__ W,
                       const float* __restrict__ DZ, const float* __restrict__ LOGP, const float* __restrict__ LOGQ,
@@ -271,40 +280,62 @@ guide_grad_big_kernel(const float* __restrict__ psi, const float* __restrict__ e
                       int m, int S, int L, int d, float tau, int row0, float* __restrict__ G,
                       float* __restrict__ elbo) {
   extern __shared__ float sm[];
-  float* wt = sm;                          // [S][m]
-  float* mt = wt + (size_t)S * m;          // [m][64]
-  float* qt = mt + (size_t)m * 64;         // [m][64]
-  float* part = qt + (size_t)m * 64;       // [4][64][2]
+  float* wt = sm;                                   // [S][m] (+ kBigJC floats of slack)
+  float* part = wt + (size_t)S * m + kBigJC;        // [4][64][2]
   const int kt = blockIdx.x, r = blockIdx.y, i = row0 + r;
   const int kk = threadIdx.x & 63, sg = threadIdx.x >> 6;
   const int k = kt * kGuideKT + kk;
   for (int t = threadIdx.x; t < S * m; t += blockDim.x) wt[t] = W[(size_t)r * S * m + t];
-  for (int t = threadIdx.x; t < m * 64; t += blockDim.x) {
-    const int j = t >> 6, c = t & 63, kc = kt * kGuideKT + c;
-    float mu = 0.f, q = 0.f;
-    if (kc < L) {
-      mu = MU[(size_t)j * L + kc];
-      const float is = ISIG[(size_t)j * L + kc];
-      q = is * is;
-    }
-    mt[t] = mu;
-    qt[t] = q;
-  }
+  for (int t = threadIdx.x; t < kBigJC; t += blockDim.x) wt[(size_t)S * m + t] = 0.f;
   __syncthreads();
   float gl = 0.f, gs = 0.f;
   if (k < L) {
     const float mu_i = MU[(size_t)i * L + k], sg_i = SIG[(size_t)i * L + k], is_i = ISIG[(size_t)i * L + k];
     const float jac = tr_of[k] == SMI_T_EXP ? 1.f : 0.f;
-    for (int s = sg; s < S; s += 4) {
-      const size_t e = ((size_t)r * S + s) * L + k;
-      const float ep = eps[e];
-      const float z = fmaf(sg_i, ep, mu_i);
-      float T = 0.f;
-      for (int j = 0; j < m; ++j) T = fmaf(wt[s * m + j] * (z - mt[j * 64 + kk]), qt[j * 64 + kk], T);
-      const float du = fmaf(tau, DZ[e], T) + jac;
-      const float wi = wt[s * m + i];
-      gl += du - wi * ep * is_i;
-      gs += du * ep - wi * (ep * ep - 1.f) * is_i;
+    for (int sb = 0; sb < S; sb += 4 * kBigNS) {
+      float zz[kBigNS], T[kBigNS];
+#pragma unroll
+      for (int t = 0; t < kBigNS; ++t) {
+        const int s = sb + sg + 4 * t;
+        const float ep = s < S ? __ldg(eps + ((size_t)r * S + s) * L + k) : 0.f;
+        zz[t] = fmaf(sg_i, ep, mu_i);
+        T[t] = 0.f;
+      }
+      for (int jb = 0; jb < m; jb += kBigJC) {
+        float mu[kBigJC], q[kBigJC];
+#pragma unroll
+        for (int j = 0; j < kBigJC; ++j) {
+          mu[j] = 0.f, q[j] = 0.f;
+          if (jb + j < m) {
+            mu[j] = __ldg(MU + (size_t)(jb + j) * L + k);
+            const float is = __ldg(ISIG + (size_t)(jb + j) * L + k);
+            q[j] = is * is;
+          }
+        }
+#pragma unroll
+        for (int t = 0; t < kBigNS; ++t) {
+          const int s = sb + sg + 4 * t;
+          if (s < S) {
+            const float* row = wt + (size_t)s * m + jb;   // warp-uniform: broadcast reads
+            float acc = T[t];
+#pragma unroll
+            for (int j = 0; j < kBigJC; ++j) acc = fmaf(row[j] * (zz[t] - mu[j]), q[j], acc);
+            T[t] = acc;
+          }
+        }
+      }
+#pragma unroll
+      for (int t = 0; t < kBigNS; ++t) {
+        const int s = sb + sg + 4 * t;
+        if (s < S) {
+          const size_t e = ((size_t)r * S + s) * L + k;
+          const float ep = __ldg(eps + e);
+          const float du = fmaf(tau, __ldg(DZ + e), T[t]) + jac;
+          const float wi = wt[(size_t)s * m + i];
+          gl += du - wi * ep * is_i;
+          gs += du * ep - wi * (ep * ep - 1.f) * is_i;
+        }
+      }
     }
   }
   part[(sg * 64 + kk) * 2] = gl;
@@ -438,9 +469,7 @@ int smi_guide_grad(const SmiModelDesc& md, const float* psi, const float* eps, i
   if (m <= 20) return launch_grad<20>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
   if (m <= 24) return launch_grad<24>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
   if (m <= 32) return launch_grad<32>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
-  if (m <= 48) return launch_grad<48>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
-  if (m <= 64) return launch_grad<64>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
-  const size_t smem = ((size_t)S * m + (size_t)2 * m * 64 + 4 * 64 * 2) * sizeof(float);
+  const size_t smem = ((size_t)S * m + kBigJC + 4 * 64 * 2) * sizeof(float);
   if (smem > 220 * 1024) SMI_FAIL(SMI_ELIMIT, "guide_grad: S * m = %d x %d too large for shared memory", S, m);
   SMI_CUDA_OK(cudaFuncSetAttribute(guide_grad_big_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid(w.nkt, nrows);

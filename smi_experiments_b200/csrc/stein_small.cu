@@ -101,7 +101,7 @@ struct FinishArgs {
   unsigned* counter;
 };
 
-__global__ void __launch_bounds__(256) stein_small_finish(FinishArgs a) {
+__global__ void __launch_bounds__(1024) stein_small_finish(FinishArgs a) {
   extern __shared__ float sm[];
   const int m = a.m, mm = m * m;
   int P = 1;
@@ -297,7 +297,7 @@ int smi_stein_small_run(const float* X, const float* G, int m, int d, float c_at
   if (fsm > 40 * 1024)
     SMI_CUDA_OK(cudaFuncSetAttribute(stein_small_finish, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   SMI_PROF_BEGIN(st);
-  stein_small_finish<<<1, 256, fsm, st>>>(fa);
+  stein_small_finish<<<1, m <= 16 ? 256 : 1024, fsm, st>>>(fa);
   SMI_LAUNCH_OK_N("stein_small_finish", st);
   if (dist_only) return SMI_OK;
 
@@ -308,7 +308,10 @@ int smi_stein_small_run(const float* X, const float* G, int m, int d, float c_at
                                                       counter, loss)
   if (m <= 8) LAUNCH_FORCE(8);
   else if (m <= 16) LAUNCH_FORCE(16);
+  else if (m <= 24) LAUNCH_FORCE(24);
   else if (m <= 32) LAUNCH_FORCE(32);
+  else if (m <= 40) LAUNCH_FORCE(40);
+  else if (m <= 48) LAUNCH_FORCE(48);
   else LAUNCH_FORCE(64);
 #undef LAUNCH_FORCE
   SMI_LAUNCH_OK_N("stein_small_force", st);
