@@ -1,0 +1,390 @@
+// Regression BNN log-joint and its gradient per ELBO draw on the tensor cores (row a3).
+//
+// Restates reference src/models/uci_bnn.py:21-68 (ReLU, prec ~ Gamma(1, 0.1)) and
+// src/models/reg_1d_bnn.py:22-67 (tanh, fixed sigma) as a hand-derived forward + backward.
+// One CTA per draw, 12 warps.  The five layer products of a draw
+//     h1 = act(x W1 + b1)            [B x H] = [B x I][I x H]
+//     h2 = act(h1 W2 + b2)           [B x H] = [B x H][H x H]
+//     [dW2; db2] = [h1, 1]^T dh2     [H+1 x H], K = B
+//     dh1 = (dh2 W2^T) act'(h1)      [B x H], K = H
+//     [dW1; db1] = [x, 1]^T dh1      [I+1 x H], K = B
+// are tiny and differ per draw (every draw has its own weights), so they are issued as warp-level
+// mma.sync.m16n8k8 TF32 tiles with the 3xTF32 split done in registers (hi = top 19 bits,
+// lo = x - hi; lo*hi + hi*lo + hi*hi, fp32 accumulate) -- FP32-accurate, no extra shared memory.
+// This is the legacy (HMMA) tensor path: per-draw operands make the tcgen05 route need either
+// A-from-TMEM or MN-major SWIZZLE_128B_BASE32B staging of every activation in two planes, which
+// does not fit two draws per SM; it is the planned next step.
+//
+// Every operand lives in shared memory as [reduction index][output index] (output contiguous), so
+// A and B fragments are gathered by the same conflict-free pattern (row strides = 8 mod 16 words),
+// and each activation is kept in two layouts ([b][j] and [j][b]) because it is an output-side
+// operand of one product and a reduction-side operand of another.
+#include <math.h>
+
+#include "elbo.cuh"
+
+namespace {
+
+constexpr float kLog2Pi = 1.8378770664093453f;
+constexpr int kThreads = 384;
+constexpr int kWarps = kThreads / 32;
+
+template <int ACT>
+__device__ __forceinline__ float act_f(float v) {
+  return ACT == SMI_ACT_RELU ? fmaxf(v, 0.f) : tanhf(v);
+}
+template <int ACT>
+__device__ __forceinline__ float dact_from_out(float h) {
+  return ACT == SMI_ACT_RELU ? (h > 0.f ? 1.f : 0.f) : 1.f - h * h;
+}
+
+__host__ __device__ inline int up8(int v) { return (v + 7) & ~7; }
+// row stride with (stride mod 16) == 8: fragment gathers hit 32 distinct banks
+__host__ __device__ inline int stride8(int v) {
+  const int s = up8(v);
+  return (s & 15) == 8 ? s : s + 8;
+}
+
+struct MmaOffsets {
+  int prec, w1, b1, w2, b2, w3, b3;
+};
+
+// Shared-memory plan (floats).  R* = reduction extents padded to the MMA K step (zero rows).
+struct MmaPlan {
+  int BP, HP, IP, BR, HR, IR;
+  int W1p, W2p, W2T, b1, b2, w3, xs, xT, hA, hT, hB, yb, dout, total;
+  __host__ __device__ MmaPlan(int B, int I, int H) {
+    BR = up8(B), HR = up8(H), IR = up8(I);
+    BP = stride8(B), HP = stride8(H + 1), IP = up8(I + 1);
+    int o = 0;
+    W1p = o, o += IR * HP;        // W1[i][j]
+    W2p = o, o += HR * HP;        // W2[k][j]
+    W2T = o, o += HR * HP;        // W2[k][j] stored [j][k]
+    b1 = o, o += HP;
+    b2 = o, o += HP;
+    w3 = o, o += HP;
+    xs = o, o += BR * IP;         // x[b][i], column I = 1
+    xT = o, o += IR * BP;         // x stored [i][b]
+    hA = o, o += BR * HP + 16;    // h1[b][j] (column H = 1), later dh1;  + slack for M-tile over-reads
+    hT = o, o += HR * BP + 16;    // h1 stored [j][b], later dh2 stored [j][b]
+    hB = o, o += BR * HP;         // h2[b][j], then dh2 in place
+    yb = o, o += BR;
+    dout = o, o += BR;
+    total = (o + 3) & ~3;
+  }
+};
+
+__device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
+  hi = __float_as_uint(x) & 0xFFFFE000u;
+  lo = __float_as_uint(x - __uint_as_float(hi));
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+// C[m0 .. m0+16) x [n0 .. n0 + 8 NT) += sum_{r < R8} PT[r][m] * Q[r][n]   (R8 multiple of 8)
+// Fragment maps of mma.m16n8k8 (g = lane / 4, t = lane % 4):
+//   A: a0 (g, t) a1 (g+8, t) a2 (g, t+4) a3 (g+8, t+4);  B: b0 (k=t, n=g) b1 (k=t+4, n=g)
+//   C: c0 (g, 2t) c1 (g, 2t+1) c2 (g+8, 2t) c3 (g+8, 2t+1)
+template <int NT>
+__device__ __forceinline__ void mma_unit(float (&acc)[NT][4], int R8, const float* __restrict__ PT, int ps, int m0,
+                                         const float* __restrict__ Q, int qs, int n0) {
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const float* pa = PT + t * ps + m0 + g;
+  const float* pb = Q + t * qs + n0 + g;
+  const int ps4 = 4 * ps, qs4 = 4 * qs;
+#pragma unroll 2
+  for (int k0 = 0; k0 < R8; k0 += 8) {
+    uint32_t ah[4], al[4];
+    split_tf32(pa[0], ah[0], al[0]);
+    split_tf32(pa[8], ah[1], al[1]);
+    split_tf32(pa[ps4], ah[2], al[2]);
+    split_tf32(pa[ps4 + 8], ah[3], al[3]);
+#pragma unroll
+    for (int u = 0; u < NT; ++u) {   // tiles past the valid range read finite padding and are dropped by the caller
+      uint32_t bh[2], bl[2];
+      split_tf32(pb[u * 8], bh[0], bl[0]);
+      split_tf32(pb[qs4 + u * 8], bh[1], bl[1]);
+      mma_tf32(acc[u], al, bh);   // small terms first
+      mma_tf32(acc[u], ah, bl);
+      mma_tf32(acc[u], ah, bh);
+    }
+    pa += 8 * ps;
+    pb += 8 * qs;
+  }
+}
+
+// Whole product: units (16-row tile, group of NT 8-column tiles) round-robin over the warps.
+// emit(row, col, v0, v1) receives the pair (row, col), (row, col + 1).
+template <int NT, typename Emit>
+__device__ __forceinline__ void mma_gemm(int M, int N, int R8, const float* __restrict__ PT, int ps,
+                                         const float* __restrict__ Q, int qs, Emit emit) {
+  const int ntm = (M + 15) >> 4, ntn = (N + 7) >> 3, ng = (ntn + NT - 1) / NT;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  for (int u = warp; u < ntm * ng; u += kWarps) {
+    const int m0 = (u / ng) << 4, nb = (u % ng) * NT, n0 = nb << 3;
+    const int nv = min(NT, ntn - nb);
+    float acc[NT][4];
+#pragma unroll
+    for (int a = 0; a < NT; ++a) acc[a][0] = acc[a][1] = acc[a][2] = acc[a][3] = 0.f;
+    mma_unit<NT>(acc, R8, PT, ps, m0, Q, qs, n0);
+#pragma unroll
+    for (int a = 0; a < NT; ++a) {
+      if (a < nv) {
+        emit(m0 + g, n0 + a * 8 + 2 * t, acc[a][0], acc[a][1]);
+        emit(m0 + g + 8, n0 + a * 8 + 2 * t, acc[a][2], acc[a][3]);
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+template <int ACT>
+__global__ void __launch_bounds__(kThreads, 2)
+bnn_reg_mma_kernel(const float* __restrict__ Z, const int32_t* __restrict__ idx, const float* __restrict__ x,
+                   const float* __restrict__ y, int L, int I, int H, int B, int noise, float sigma,
+                   float lik_scale, MmaOffsets o, float* __restrict__ DZ, float* __restrict__ LOGP) {
+  extern __shared__ __align__(16) float sm[];
+  const MmaPlan pl(B, I, H);
+  const int BP = pl.BP, HP = pl.HP, IP = pl.IP, BR = pl.BR, HR = pl.HR, IR = pl.IR;
+  float* W1p = sm + pl.W1p;
+  float* W2p = sm + pl.W2p;
+  float* W2T = sm + pl.W2T;
+  float* b1 = sm + pl.b1;
+  float* b2 = sm + pl.b2;
+  float* w3 = sm + pl.w3;
+  float* xs = sm + pl.xs;
+  float* xT = sm + pl.xT;
+  float* hA = sm + pl.hA;
+  float* hT = sm + pl.hT;
+  float* hB = sm + pl.hB;
+  float* yb = sm + pl.yb;
+  float* dout = sm + pl.dout;
+  __shared__ double red[32];
+  __shared__ float s_prec_grad;
+  const int n = blockIdx.x;
+  const float* __restrict__ z = Z + (size_t)n * L;
+  float* __restrict__ dz = DZ + (size_t)n * L;
+  const bool gamma = noise == SMI_NOISE_GAMMA_PREC;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // zero everything once: reduction-side padding rows / columns must be exact zeros
+  for (int t = threadIdx.x; t < pl.total / 4; t += blockDim.x)
+    reinterpret_cast<float4*>(sm)[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+  __syncthreads();
+
+  // ---- stage the draw ----
+  double lprior = 0.0;  // sum of theta^2 over the Normal(0, 1) sites
+  {  // W1 / W2 as 4 x 4 tiles: 16 independent global loads per thread, float4 stores
+    const int ntj = (H + 3) >> 2, nti = (I + 3) >> 2, ntk = (H + 3) >> 2;
+    for (int t = threadIdx.x; t < nti * ntj + ntk * ntj; t += blockDim.x) {
+      const bool second = t >= nti * ntj;
+      const int tt = second ? t - nti * ntj : t;
+      const int r0 = (tt / ntj) << 2, j0 = (tt % ntj) << 2;
+      const int rows = second ? H : I;
+      const float* src = z + (second ? o.w2 : o.w1);
+      float v[4][4], ss = 0.f;
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          v[a][c] = (r0 + a < rows && j0 + c < H) ? src[(r0 + a) * H + j0 + c] : 0.f;
+          ss = fmaf(v[a][c], v[a][c], ss);
+        }
+      lprior += (double)ss;
+      float* dst = second ? W2p : W1p;
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+        if (r0 + a < rows) *reinterpret_cast<float4*>(dst + (r0 + a) * HP + j0) = make_float4(v[a][0], v[a][1], v[a][2], v[a][3]);
+      if (second) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          if (j0 + c < H) *reinterpret_cast<float4*>(W2T + (j0 + c) * HP + r0) = make_float4(v[0][c], v[1][c], v[2][c], v[3][c]);
+      }
+    }
+  }
+  for (int j = threadIdx.x; j < H; j += blockDim.x) {
+    const float v1 = z[o.b1 + j], v2 = z[o.b2 + j], v3 = z[o.w3 + j];
+    lprior += (double)(v1 * v1) + (double)(v2 * v2) + (double)(v3 * v3);
+    b1[j] = v1, b2[j] = v2, w3[j] = v3;
+  }
+  {
+    const int nci = IP >> 2;
+    for (int t = threadIdx.x; t < B * nci; t += blockDim.x) {
+      const int b = t / nci, i0 = (t - b * nci) << 2;
+      const int row = idx ? idx[(size_t)n * B + b] : b;
+      float v[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int i = i0 + c;
+        v[c] = i < I ? __ldg(x + (size_t)row * I + i) : (i == I ? 1.f : 0.f);   // column I: ones (bias gradient)
+        if (i < I) xT[i * BP + b] = v[c];
+      }
+      *reinterpret_cast<float4*>(xs + b * IP + i0) = make_float4(v[0], v[1], v[2], v[3]);
+      if (i0 == 0) yb[b] = y[row];
+    }
+  }
+  const float b3 = z[o.b3];
+  const float prec = gamma ? expf(z[o.prec]) : 1.f / (sigma * sigma);
+  __syncthreads();
+
+  // ---- forward 1: h1 = act(x W1 + b1) -> hA [b][j] (column H = 1) and hT [j][b] ----
+  mma_gemm<4>(B, H + 1, IR, xT, BP, W1p, HP, [&](int b, int j, float v0, float v1) {
+    if (b >= BR) return;
+    const bool live = b < B;
+    const float h0 = live ? (j < H ? act_f<ACT>(v0 + b1[j]) : (j == H ? 1.f : 0.f)) : 0.f;
+    const float h1v = live ? (j + 1 < H ? act_f<ACT>(v1 + b1[j + 1]) : (j + 1 == H ? 1.f : 0.f)) : 0.f;
+    *reinterpret_cast<float2*>(hA + b * HP + j) = make_float2(h0, h1v);
+    if (j < H) hT[j * BP + b] = h0;
+    if (j + 1 < H) hT[(j + 1) * BP + b] = h1v;
+  });
+  __syncthreads();
+  // ---- forward 2: h2 = act(h1 W2 + b2) -> hB [b][j] ----
+  mma_gemm<4>(B, H, HR, hT, BP, W2p, HP, [&](int b, int j, float v0, float v1) {
+    if (b >= BR) return;
+    const bool live = b < B;
+    const float h0 = (live && j < H) ? act_f<ACT>(v0 + b2[j]) : 0.f;
+    const float h1v = (live && j + 1 < H) ? act_f<ACT>(v1 + b2[j + 1]) : 0.f;
+    *reinterpret_cast<float2*>(hB + b * HP + j) = make_float2(h0, h1v);
+  });
+  __syncthreads();
+  // ---- output layer (one thread per row), residuals ----
+  double ll = 0.0;
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    float out = b3;
+    const float4* hr = reinterpret_cast<const float4*>(hB + b * HP);
+    const float4* wr = reinterpret_cast<const float4*>(w3);
+    for (int q = 0; q < (HP >> 2); ++q) {   // padded columns of w3 are zero
+      const float4 h4 = hr[q], w4 = wr[q];
+      out = fmaf(h4.x, w4.x, out);
+      out = fmaf(h4.y, w4.y, out);
+      out = fmaf(h4.z, w4.z, out);
+      out = fmaf(h4.w, w4.w, out);
+    }
+    const float r = yb[b] - out;
+    dout[b] = lik_scale * prec * r;
+    ll += (double)(-0.5f * prec * r * r);
+    yb[b] = r;  // keep the residual for d/d prec
+  }
+  ll = block_sum(ll, red);  // (its barriers publish dout / yb)
+  double lp_const = 0.0;
+  if (threadIdx.x == 0) lp_const = (double)B * (0.5 * (double)logf(prec) - 0.5 * (double)kLog2Pi);
+  __syncthreads();
+  // ---- backward: output layer ----
+  for (int j = threadIdx.x; j < H; j += blockDim.x) {
+    float g = 0.f;
+    for (int b = 0; b < B; ++b) g = fmaf(dout[b], hB[b * HP + j], g);
+    dz[o.w3 + j] = g - w3[j];
+  }
+  if (threadIdx.x == blockDim.x - 1) {
+    float g = 0.f;
+    for (int b = 0; b < B; ++b) g += dout[b];
+    dz[o.b3] = g - b3;
+    if (gamma) {
+      float gp = 0.f;
+      for (int b = 0; b < B; ++b) gp += -0.5f * yb[b] * yb[b] + 0.5f / prec;
+      s_prec_grad = lik_scale * gp;
+    }
+  }
+  __syncthreads();
+  // dh2 = dout w3 act'(h2): in place (hB) and transposed into hT (h1^T is dead); 4 x 4 tiles
+  {
+    const int ntj = HP >> 2, ntb = BR >> 2;
+    for (int t = threadIdx.x; t < ntb * ntj; t += blockDim.x) {
+      const int b0 = (t / ntj) << 2, j0 = (t % ntj) << 2;
+      const float4 w4 = *reinterpret_cast<const float4*>(w3 + j0);
+      const float wv[4] = {w4.x, w4.y, w4.z, w4.w};
+      float v[4][4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+        const float4 h4 = *reinterpret_cast<const float4*>(hB + (b0 + a) * HP + j0);
+        const float hv[4] = {h4.x, h4.y, h4.z, h4.w};
+        const float dv = dout[b0 + a];   // 0 for padded rows
+#pragma unroll
+        for (int c = 0; c < 4; ++c) v[a][c] = (j0 + c < H) ? dv * wv[c] * dact_from_out<ACT>(hv[c]) : 0.f;
+        *reinterpret_cast<float4*>(hB + (b0 + a) * HP + j0) = make_float4(v[a][0], v[a][1], v[a][2], v[a][3]);
+      }
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        if (j0 + c < H) *reinterpret_cast<float4*>(hT + (j0 + c) * BP + b0) = make_float4(v[0][c], v[1][c], v[2][c], v[3][c]);
+    }
+  }
+  __syncthreads();
+  // ---- layer 2: [dW2; db2] = [h1, 1]^T dh2 ----
+  mma_gemm<3>(H + 1, H, BR, hA, HP, hB, HP, [&](int k, int j, float v0, float v1) {
+    if (k > H) return;
+    if (j < H) {
+      if (k < H) dz[o.w2 + k * H + j] = v0 - W2p[k * HP + j];
+      else dz[o.b2 + j] = v0 - b2[j];
+    }
+    if (j + 1 < H) {
+      if (k < H) dz[o.w2 + k * H + j + 1] = v1 - W2p[k * HP + j + 1];
+      else dz[o.b2 + j + 1] = v1 - b2[j + 1];
+    }
+  });
+  __syncthreads();
+  // ---- dh1 = (dh2 W2^T) act'(h1), written over h1 (each element touched by one thread) ----
+  mma_gemm<4>(B, H, HR, hT, BP, W2T, HP, [&](int b, int k, float v0, float v1) {
+    if (b >= BR) return;
+    const float2 h = *reinterpret_cast<const float2*>(hA + b * HP + k);
+    const bool live = b < B;
+    const float d0 = (live && k < H) ? v0 * dact_from_out<ACT>(h.x) : 0.f;
+    const float d1 = (live && k + 1 < H) ? v1 * dact_from_out<ACT>(h.y) : 0.f;
+    *reinterpret_cast<float2*>(hA + b * HP + k) = make_float2(d0, d1);
+  });
+  __syncthreads();
+  // ---- layer 1: [dW1; db1] = [x, 1]^T dh1 ----
+  mma_gemm<1>(I + 1, H, BR, xs, IP, hA, HP, [&](int i, int j, float v0, float v1) {
+    if (i > I) return;
+    if (j < H) {
+      if (i < I) dz[o.w1 + i * H + j] = v0 - W1p[i * HP + j];
+      else dz[o.b1 + j] = v0 - b1[j];
+    }
+    if (j + 1 < H) {
+      if (i < I) dz[o.w1 + i * H + j + 1] = v1 - W1p[i * HP + j + 1];
+      else dz[o.b1 + j + 1] = v1 - b1[j + 1];
+    }
+  });
+  // ---- priors, precision site, log p ----
+  lprior = block_sum(lprior, red);
+  if (threadIdx.x == 0) {
+    double lp = -0.5 * lprior - 0.5 * (double)(L - (gamma ? 1 : 0)) * (double)kLog2Pi - 0.5 * (double)(b3 * b3);
+    if (gamma) {
+      lp += (double)(logf(0.1f) - 0.1f * prec);           // Gamma(1, rate 0.1)
+      dz[o.prec] = (s_prec_grad - 0.1f) * prec;           // d theta / d u = theta
+    }
+    LOGP[n] = (float)(lp + (double)lik_scale * (ll + lp_const));
+  }
+}
+
+}  // namespace
+
+size_t smi_bnn_reg_mma_smem_bytes(int I, int H, int B) { return (size_t)MmaPlan(B, I, H).total * sizeof(float); }
+
+// Returns SMI_ELIMIT (without launching) when the draw does not fit in shared memory.
+int smi_bnn_reg_mma_launch(const SmiModelDesc& md, const float* Z, const int32_t* idx, const float* x, const float* y,
+                           int ndraws, int B, float lik_scale, const int* off7, float* DZ, float* LOGP,
+                           cudaStream_t st) {
+  const int I = md.in_dim, H = md.hidden, L = md.latent_dim;
+  const size_t smem = smi_bnn_reg_mma_smem_bytes(I, H, B);
+  if (smem > 220 * 1024) SMI_FAIL(SMI_ELIMIT, "bnn_reg: network + minibatch need %zu B of shared memory", smem);
+  MmaOffsets o;
+  o.prec = off7[0], o.w1 = off7[1], o.b1 = off7[2], o.w2 = off7[3], o.b2 = off7[4], o.w3 = off7[5], o.b3 = off7[6];
+  SMI_PROF_BEGIN(st);
+  if (md.act == SMI_ACT_RELU) {
+    SMI_CUDA_OK(cudaFuncSetAttribute(bnn_reg_mma_kernel<SMI_ACT_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)smem));
+    bnn_reg_mma_kernel<SMI_ACT_RELU><<<ndraws, kThreads, smem, st>>>(Z, idx, x, y, L, I, H, B, md.noise, md.sigma,
+                                                                     lik_scale, o, DZ, LOGP);
+  } else {
+    SMI_CUDA_OK(cudaFuncSetAttribute(bnn_reg_mma_kernel<SMI_ACT_TANH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)smem));
+    bnn_reg_mma_kernel<SMI_ACT_TANH><<<ndraws, kThreads, smem, st>>>(Z, idx, x, y, L, I, H, B, md.noise, md.sigma,
+                                                                     lik_scale, o, DZ, LOGP);
+  }
+  SMI_LAUNCH_OK_N("bnn_reg_mma_kernel", st);
+  return SMI_OK;
+}

@@ -8,6 +8,7 @@
 // One CTA per draw.  The whole network (weights, minibatch, activations, weight gradients)
 // lives in shared memory; layer products are register-tiled fp32 FMA loops.
 #include <math.h>
+#include <stdlib.h>
 
 #include "elbo.cuh"
 
@@ -192,17 +193,25 @@ bnn_reg_kernel(const float* __restrict__ Z, const int32_t* __restrict__ idx, con
     }
     W1p[t] = v;
   }
-  for (int t = threadIdx.x; t < H * HP; t += blockDim.x) {
-    const int k = t / HP, j = t - k * HP;
-    float v = 0.f;
-    if (j < H) {
-      v = z[o.w2 + k * H + j];
-      lprior += (double)(v * v);
-      W2T[j * HP + k] = v;
-    } else {
-      W2T[k * HP + j] = 0.f;  // pad columns of the transposed copy
+  {  // W2 as 4 x 4 tiles: 16 independent global loads per thread, float4 stores to both copies
+    const int nt = HP >> 2;
+    for (int t = threadIdx.x; t < nt * nt; t += blockDim.x) {
+      const int k0 = (t / nt) << 2, j0 = (t % nt) << 2;
+      float v[4][4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) v[a][c] = (k0 + a < H && j0 + c < H) ? z[o.w2 + (k0 + a) * H + j0 + c] : 0.f;
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) lprior += (double)(v[a][c] * v[a][c]);
+        if (k0 + a < H) *reinterpret_cast<float4*>(W2p + (k0 + a) * HP + j0) = make_float4(v[a][0], v[a][1], v[a][2], v[a][3]);
+      }
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        if (j0 + c < H) *reinterpret_cast<float4*>(W2T + (j0 + c) * HP + k0) = make_float4(v[0][c], v[1][c], v[2][c], v[3][c]);
     }
-    W2p[t] = v;
   }
   for (int j = threadIdx.x; j < HP; j += blockDim.x) {
     float v1 = 0.f, v2 = 0.f, v3 = 0.f;
@@ -304,12 +313,26 @@ bnn_reg_kernel(const float* __restrict__ Z, const int32_t* __restrict__ idx, con
   }
   __syncthreads();
   // dh2 in place of h2 (row layout) and transposed into hT (h1^T is dead after the second product)
-  for (int t = threadIdx.x; t < BP * HP; t += blockDim.x) {
-    const int b = t / HP, j = t - b * HP;
-    float v = 0.f;
-    if (b < B && j < H) v = dout[b] * w3[j] * dact_from_out<ACT>(hB[t]);
-    hB[t] = v;
-    if (j < H) hT[j * BP + b] = v;
+  {
+    const int ntj = HP >> 2, ntb = BP >> 2;
+    for (int t = threadIdx.x; t < ntb * ntj; t += blockDim.x) {
+      const int b0 = (t / ntj) << 2, j0 = (t % ntj) << 2;
+      const float4 w4 = *reinterpret_cast<const float4*>(w3 + j0);
+      const float wv[4] = {w4.x, w4.y, w4.z, w4.w};
+      float v[4][4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+        const float4 h4 = *reinterpret_cast<const float4*>(hB + (b0 + a) * HP + j0);
+        const float hv[4] = {h4.x, h4.y, h4.z, h4.w};
+        const float dv = dout[b0 + a];   // 0 for padded rows
+#pragma unroll
+        for (int c = 0; c < 4; ++c) v[a][c] = (j0 + c < H) ? dv * wv[c] * dact_from_out<ACT>(hv[c]) : 0.f;
+        *reinterpret_cast<float4*>(hB + (b0 + a) * HP + j0) = make_float4(v[a][0], v[a][1], v[a][2], v[a][3]);
+      }
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        if (j0 + c < H) *reinterpret_cast<float4*>(hT + (j0 + c) * BP + b0) = make_float4(v[0][c], v[1][c], v[2][c], v[3][c]);
+    }
   }
   __syncthreads();
   // ---- layer 2: [dW2; db2] = [h1, 1]^T dh2 ----
@@ -404,6 +427,9 @@ size_t reg_smem_bytes(int L, int I, int H, int B) {
 
 }  // namespace
 
+int smi_bnn_reg_mma_launch(const SmiModelDesc& md, const float* Z, const int32_t* idx, const float* x, const float* y,
+                           int ndraws, int B, float lik_scale, const int* off7, float* DZ, float* LOGP,
+                           cudaStream_t st);
 int smi_model_cls_logp_grad(const SmiModelDesc& md, const float* Z, const float* x, const int32_t* y, int ndraws,
                             int B, float lik_scale, float* DZ, float* LOGP, cudaStream_t st);
 
@@ -433,6 +459,13 @@ int smi_model_logp_grad(const SmiModelDesc& md, const float* Z, const int32_t* i
   if (s[0].size != I * H || s[1].size != H || s[2].size != H * H || s[3].size != H || s[4].size != H ||
       s[5].size != 1)
     SMI_FAIL(SMI_EINVAL, "bnn_reg site sizes do not match in_dim=%d hidden=%d", I, H);
+  {  // tensor-core kernel (elbo_bnn_mma.cu); the fp32 FMA kernel below is kept for SMI_BNN_FMA=1 comparisons
+    static const bool use_fma = getenv("SMI_BNN_FMA") != nullptr;
+    if (!use_fma) {
+      const int off7[7] = {o.prec, o.w1, o.b1, o.w2, o.b2, o.w3, o.b3};
+      return smi_bnn_reg_mma_launch(md, Z, idx, x, (const float*)y, ndraws, B, lik_scale, off7, DZ, LOGP, st);
+    }
+  }
   const size_t smem = reg_smem_bytes(L, I, H, B);
   if (smem > 220 * 1024) SMI_FAIL(SMI_ELIMIT, "bnn_reg: network + minibatch need %zu B of shared memory", smem);
   if (md.act == SMI_ACT_RELU) {
