@@ -167,6 +167,15 @@ int smi_adam_f32(float* x, float* mom, float* vel, const float* F, float grad_si
 int smi_adagrad_f32(float* x, float* acc, float* mom, const float* F, float grad_sign,
                     int32_t* step, int bump_step, double lr, double momentum, size_t n, void* stream);
 
+/* Gated forms used inside run loops: identical arithmetic, but the whole update is skipped when
+ * *skip != 0 (skip may be NULL), and the step counter is NOT bumped here -- smi_step_commit_f32
+ * closes the step.                                                                          */
+int smi_adam_gated_f32(float* x, float* mom, float* vel, const float* F, float grad_sign,
+                       const int32_t* step, double lr, double b1, double b2, double eps, size_t n,
+                       const int32_t* skip, void* stream);
+int smi_adagrad_gated_f32(float* x, float* acc, float* mom, const float* F, float grad_sign, double lr,
+                          double momentum, size_t n, const int32_t* skip, void* stream);
+
 /* ---- Per-particle mixture-ELBO gradients (row a3; NumPyro stein_loss.py).
  *   psi  : (m, d) all particles.   eps : (nrows, S, L) N(0,1) noise of the owned rows (NULL for
  *   AutoDelta).  idx : (nrows, S, B) int32 subsample rows into x / y, or NULL = every draw uses
@@ -209,6 +218,23 @@ int smi_prng_bits_u32(const uint32_t* key, size_t n, uint32_t* out, void* stream
  *   ring[(step - 1) mod ring_len] = *loss, `step` being the device counter the optimizer
  *   bumped for this update.                                                               */
 int smi_loss_record_f32(const float* loss, const int32_t* step, float* ring, int ring_len, void* stream);
+
+/* ---- End of one update inside a device-side run loop: replaces the
+ *      loop-carried bookkeeping of SteinVI.run / fori_collect and of OnlineEarlyStop.step
+ *      (reference src/model_select/early_stopping.py:24-62), with no host round trip.
+ *   If skip != NULL and *skip != 0: nothing happens (the run has stopped; the gated optimizer
+ *   left the particles alone).  Otherwise, with t = *step:
+ *     *step = t + 1;  ring[t mod ring_len] = *loss (ring may be NULL);
+ *     key <- key_next (both uint32[2], may both be NULL);
+ *     es (may be NULL) = {t_es, fast_avg, slow_avg} float32:
+ *        tau = min(t_es, period_x), avg_x = loss / (tau + 1) + (tau / (tau + 1)) * decay_x * avg_x
+ *        for x in {fast (period), slow (10 * period)};  t_es += 1;
+ *        *skip = 1 when fast_avg > 2 * slow_avg.
+ *   fast_decay = exp(log(1e-3) / period), slow_decay = exp(log(1e-3) / (10 period)), evaluated
+ *   by the caller in float32 as the reference does.                                        */
+int smi_step_commit_f32(const float* loss, int32_t* step, float* ring, int ring_len,
+                        const uint32_t* key_next, uint32_t* key, float* es, int32_t* skip,
+                        float fast_decay, float slow_decay, int period, void* stream);
 
 #ifdef __cplusplus
 }

@@ -11,6 +11,7 @@ from .kernels import RBFKernel  # noqa: F401
 from .models import (AutoDelta, AutoNormal, BNNClassifier, BNNRegression, GaussianTarget,  # noqa: F401
                      init_to_uniform, mnist_mlp, reg_1d_bnn, uci_bnn)
 from .optim import Adagrad, Adam  # noqa: F401
+from .early_stop import OnlineEarlyStop  # noqa: F401
 from .steinvi import ASVGD, SVGD, PRNGKey, SteinVI, SteinVIRunResult, SteinVIState  # noqa: F401
 
 __version__ = "0.1.0"

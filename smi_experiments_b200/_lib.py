@@ -81,6 +81,9 @@ PROTOTYPES = {
     "smi_prng_normal_f32": (_I, [_P, _Z, _P, _P]),
     "smi_prng_bits_u32": (_I, [_P, _Z, _P, _P]),
     "smi_loss_record_f32": (_I, [_P, _P, _P, _I, _P]),
+    "smi_adam_gated_f32": (_I, [_P, _P, _P, _P, _F, _P, _D, _D, _D, _D, _Z, _P, _P]),
+    "smi_adagrad_gated_f32": (_I, [_P, _P, _P, _P, _F, _D, _D, _Z, _P, _P]),
+    "smi_step_commit_f32": (_I, [_P, _P, _P, _I, _P, _P, _P, _P, _F, _F, _I, _P]),
 }
 
 _lib = None

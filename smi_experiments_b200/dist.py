@@ -191,11 +191,14 @@ class ShardedSteinVI(SteinVI):
             b["h"].copy_(h)
         if do_update:
             rows_state = OptimState(os_.step, X[r0:r0 + n], os_.a, os_.b)
-            self.optim.update(F_rows, rows_state, -1.0)
-            if ring is not None:
-                _lib.call("smi_loss_record_f32", ops._ptr(b["loss"]), ops._ptr(os_.step), ops._ptr(ring),
-                          ring.numel(), ops._stream())
-            st.rng_key.copy_(b["key_next"])
+            es = getattr(self, "_es", None)
+            skip = es["skip"] if es is not None else None
+            self.optim.update_gated(F_rows, rows_state, -1.0, skip)
+            if es is None:
+                ops.step_commit(b["loss"], os_.step, ring, b["key_next"], st.rng_key)
+            else:   # every rank holds the same loss, so every rank takes the same stopping decision
+                ops.step_commit(b["loss"], os_.step, ring, b["key_next"], st.rng_key, es["avg"], skip,
+                                es["fast_decay"], es["slow_decay"], es["period"])
             dist.all_gather_into_tensor(X, X[r0:r0 + n], group=self.group)      # in place
 
 

@@ -106,6 +106,29 @@ def adagrad(x, acc, mom, F, step, lr, grad_sign=-1.0, momentum=0.9, bump_step=Tr
          lr, momentum, x.numel(), _stream())
 
 
+def adam_gated(x, mom, vel, F, step, lr, grad_sign=-1.0, b1=0.9, b2=0.999, eps=1e-8, skip=None):
+    """Adam without the step bump, skipped on the device when *skip != 0 (run loops, row n1)."""
+    _need_cuda(x, mom, vel, F, step, skip)
+    call("smi_adam_gated_f32", _ptr(x), _ptr(mom), _ptr(vel), _ptr(F), grad_sign, _ptr(step), lr, b1, b2, eps,
+         x.numel(), _ptr(skip), _stream())
+
+
+def adagrad_gated(x, acc, mom, F, lr, grad_sign=-1.0, momentum=0.9, skip=None):
+    _need_cuda(x, acc, mom, F, skip)
+    call("smi_adagrad_gated_f32", _ptr(x), _ptr(acc), _ptr(mom), _ptr(F), grad_sign, lr, momentum, x.numel(),
+         _ptr(skip), _stream())
+
+
+def step_commit(loss, step, ring=None, key_next=None, key=None, es=None, skip=None, fast_decay=0.0,
+                slow_decay=0.0, period=1):
+    """Close one update on the device: step += 1, ring[t % len] = loss, key <- key_next, and the
+    OnlineEarlyStop averages / skip flag (src/model_select/early_stopping.py:24-62).  row n1."""
+    _need_cuda(loss, step, ring, key_next, key, es, skip)
+    call("smi_step_commit_f32", _ptr(loss), _ptr(step), _ptr(ring), 0 if ring is None else ring.numel(),
+         _ptr(key_next), _ptr(key), _ptr(es), _ptr(skip), float(fast_decay), float(slow_decay), int(period),
+         _stream())
+
+
 def elbo_grad(md, psi, eps, idx, x, y, S, B, lik_scale=1.0, tau=1.0, row0=0, nrows=None, G=None,
               elbo=None, ws=None):
     """G (nrows, d), elbo (nrows): per-particle mixture-ELBO gradients.  row a3."""

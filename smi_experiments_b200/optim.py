@@ -39,6 +39,13 @@ class Adam(_Optim):
                  self.eps)
         return state
 
+    def update_gated(self, F, state, grad_sign=-1.0, skip=None):
+        """As update, but the step counter is left to ops.step_commit and the whole pass is a
+        no-op on the device once *skip is set (early-stopped run)."""
+        ops.adam_gated(state.x, state.a, state.b, F, state.step, self.step_size, grad_sign, self.b1, self.b2,
+                       self.eps, skip)
+        return state
+
 
 class Adagrad(_Optim):
     """jax.example_libraries.optimizers.adagrad (momentum 0.9) as wrapped by numpyro.optim.Adagrad."""
@@ -50,4 +57,8 @@ class Adagrad(_Optim):
 
     def update(self, F, state, grad_sign=-1.0):
         ops.adagrad(state.x, state.a, state.b, F, state.step, self.step_size, grad_sign, self.momentum)
+        return state
+
+    def update_gated(self, F, state, grad_sign=-1.0, skip=None):
+        ops.adagrad_gated(state.x, state.a, state.b, F, self.step_size, grad_sign, self.momentum, skip)
         return state

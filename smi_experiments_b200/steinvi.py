@@ -203,11 +203,20 @@ class SteinVI:
                   _lib.PATH_AUTO, ops._ptr(b["F"]), ops._ptr(b["loss"]), ops._ptr(b["h"]), ops._ptr(w),
                   w.numel(), ops._stream())
         if do_update:
-            self.optim.update(b["F"], os_, -1.0)
-            if ring is not None:
-                _lib.call("smi_loss_record_f32", ops._ptr(b["loss"]), ops._ptr(os_.step), ops._ptr(ring),
-                          ring.numel(), ops._stream())
-            st.rng_key.copy_(b["key_next"])
+            self._commit(st, b, ring)
+
+    def _commit(self, st, b, ring):
+        """Optimizer + end-of-step bookkeeping, all on the device: gated by the early-stop flag
+        when an OnlineEarlyStop run is active (early_stop.py), one commit kernel for the step
+        counter, the loss ring, the PRNG key and the stopping rule."""
+        es = getattr(self, "_es", None)
+        skip = es["skip"] if es is not None else None
+        self.optim.update_gated(b["F"], st.optim_state, -1.0, skip)
+        if es is None:
+            ops.step_commit(b["loss"], st.optim_state.step, ring, b["key_next"], st.rng_key)
+        else:
+            ops.step_commit(b["loss"], st.optim_state.step, ring, b["key_next"], st.rng_key, es["avg"], skip,
+                            es["fast_decay"], es["slow_decay"], es["period"])
 
     def init(self, rng_key, *args, **kwargs):
         """SteinVI.init (src/engine_run.py:41-47): particles ~ init_to_uniform(radius) per site in
@@ -267,7 +276,8 @@ class SteinVI:
             return st, b["loss"].reshape(())
         sig = (data["x"].data_ptr() if data["x"] is not None else 0,
                data["y"].data_ptr() if data["y"] is not None else 0, data["lik_scale"],
-               ring.data_ptr() if ring is not None else 0)
+               ring.data_ptr() if ring is not None else 0,
+               self._es["avg"].data_ptr() if getattr(self, "_es", None) is not None else 0)
         if self._graph is None or self._graph_sig != sig:
             if getattr(self, "_warm_sig", None) != sig:
                 # first call with these buffers: run eagerly (sets kernel attributes), capture next time
@@ -288,8 +298,7 @@ class SteinVI:
     def _eager(self, st, b, data, ring):
         n0 = _lib.load().smi_launch_count(0)
         self._launch(st, b, data, True, ring)
-        # + the 8-byte key copy (a torch D2D copy kernel) that closes the step
-        self.launches_per_update = _lib.load().smi_launch_count(0) - n0 + 1
+        self.launches_per_update = _lib.load().smi_launch_count(0) - n0
 
     def setup_run(self, rng_key, num_steps, args, init_state, kwargs):
         """(step, diagnostic, collect, extract_state, init_info) as SteinVI.setup_run
