@@ -236,6 +236,27 @@ int smi_step_commit_f32(const float* loss, int32_t* step, float* ring, int ring_
                         const uint32_t* key_next, uint32_t* key, float* es, int32_t* skip,
                         float fast_decay, float slow_decay, int period, void* stream);
 
+/* ---- Posterior predictive + regression metrics: the step AFTER the path.
+ *      Replaces MixtureGuidePredictive / Predictive as used by the reference's samplers
+ *      (src/metrics.py:216-237, experiments/uci_benchmark.py:297-316) for the regression BNNs,
+ *      and rmse_fn / nll_reg_fn / lppd_fn (src/metrics.py:222-268).
+ *   psi (m, d) particles; key uint32[2]; x (n, in_dim); y (n) observed targets or NULL.
+ *   AutoNormal: draw s picks particle a_s uniformly and samples its Normal; AutoDelta: draw s is
+ *   particle s mod m (Predictive(num_samples=1, batch_ndims=1)).
+ *   Outputs (row-major, any may be NULL except y_loc): assign (S) int32; latents (S, L) constrained,
+ *   model order; y_loc (S, n); y_draw (S, n) ~ N(y_loc, sigma_s); loglik (S, n) (needs y).   */
+int smi_predictive_reg_f32(const SmiModelDesc* md, const float* psi, int m, const uint32_t* key,
+                           int num_samples, const float* x, int n, const float* y, int32_t* assign,
+                           float* latents, float* y_loc, float* y_draw, float* loglik, void* stream);
+size_t smi_metric_workspace_bytes(int num_samples, int n);
+/* out[0] = sqrt(mean_{s,i} (y_i - y_loc[s][i])^2)                                            */
+int smi_metric_rmse_f32(const float* y_loc, const float* y, int num_samples, int n, float* out, void* ws,
+                        size_t ws_bytes, void* stream);
+/* lpd_i = logsumexp_s loglik[s][i] - log S (written to lpd (n) when not NULL);
+ * out2[0] = -mean_i lpd_i (nll_reg_fn), out2[1] = sum_i lpd_i (lppd_fn)                      */
+int smi_metric_nll_f32(const float* loglik, int num_samples, int n, float* out2, float* lpd, void* ws,
+                       size_t ws_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,79 @@
+"""TEST INFRASTRUCTURE (oracle): CPU restatement of the reference's posterior predictive and
+regression metrics.
+
+Follows the reference's samplers and metric functions:
+  src/metrics.py:216-224  smi_sampler  -> MixtureGuidePredictive(model, guide, params, num_samples,
+                                          return_sites, guide_sites)        [numpyro, not in the tree]
+  src/metrics.py:227-237  svgd_sampler -> Predictive(..., num_samples=1, batch_ndims=1)
+  src/metrics.py:249-253  rmse_fn      sqrt(mean((y[None] - y_loc) ** 2))
+  src/metrics.py:256-263  nll_reg_fn   -(logsumexp(lls, 0) - log S).mean()
+  src/metrics.py:222-246  lppd_fn      sum_i (logsumexp_s ll_si - log S)
+MixtureGuidePredictive lives in numpyro.contrib.einstein (floating master, absent here): its
+published algorithm -- draw a component uniformly, sample that particle's guide, run the model --
+is restated with the key chain documented in smi_experiments_b200/csrc/predictive.cu.
+Parity unpinned (no reference fixture exists for predictive draws).
+"""
+import numpy as np
+import torch
+
+from . import models, prng
+
+
+def softplus(x):
+    return np.maximum(x, 0) + np.log1p(np.exp(-np.abs(x)))
+
+
+def predictive_reg(spec, psi, key, num_samples, x, y=None, guide="normal", dtype=np.float64):
+    """dict(assign (S,), latents (S, L), y_loc (S, n), y (S, n), loglik (S, n) | None)."""
+    rows, L, d = models.layout(spec, guide)
+    psi = np.asarray(psi, dtype)
+    m, S, n = psi.shape[0], int(num_samples), x.shape[0]
+    ka, kg, km = prng.split(np.asarray(key, np.uint32), 3)
+    if guide == "normal":
+        assign = prng.randint_bits_to_index(prng.random_bits(ka, S), m)
+    else:
+        assign = (np.arange(S) % m).astype(np.int32)
+    dkeys, nkeys = prng.split(kg, S), prng.split(km, S)
+    lat = np.zeros((S, L), dtype)
+    noise = np.zeros((S, n), dtype)
+    for s in range(S):
+        kk = dkeys[s]
+        p = psi[assign[s]]
+        for r in rows:
+            kk, sub = prng.split(kk, 2)
+            u = p[r["loc"]:r["loc"] + r["size"]]
+            if guide == "normal":
+                eps = prng.normal(sub, r["size"]).astype(dtype)
+                u = u + softplus(p[r["rho"]:r["rho"] + r["size"]]) * eps
+            lat[s, r["lat"]:r["lat"] + r["size"]] = np.exp(u) if r["transform"] == models.T_EXP else u
+        noise[s] = prng.normal(nkeys[s], n).astype(dtype)
+    tdt = torch.float64 if dtype == np.float64 else torch.float32
+    theta = torch.from_numpy(lat).to(tdt)
+    xb = torch.from_numpy(np.asarray(x, dtype)).to(tdt).reshape(n, -1)[None].expand(S, n, -1)
+    y_loc = models.forward(spec, theta, xb).numpy()
+    if spec.noise == "gamma":
+        sigma = np.sqrt(1.0 / lat[:, rows[0]["lat"]])[:, None]
+    else:
+        sigma = np.full((S, 1), spec.sigma, dtype)
+    out = dict(assign=assign, latents=lat, y_loc=y_loc, y=y_loc + sigma * noise, loglik=None)
+    if y is not None:
+        z = (np.asarray(y, dtype)[None] - y_loc) / sigma
+        out["loglik"] = -0.5 * z * z - np.log(sigma) - 0.5 * np.log(2 * np.pi)
+    return out
+
+
+def rmse(y_loc, y):
+    return float(np.sqrt(np.mean((np.asarray(y)[None] - y_loc) ** 2)))
+
+
+def lpd(loglik):
+    mx = loglik.max(0)
+    return mx + np.log(np.exp(loglik - mx).sum(0)) - np.log(loglik.shape[0])
+
+
+def nll_reg(loglik):
+    return float(-lpd(loglik).mean())
+
+
+def lppd(loglik):
+    return float(lpd(loglik).sum())

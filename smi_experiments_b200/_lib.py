@@ -84,6 +84,10 @@ PROTOTYPES = {
     "smi_adam_gated_f32": (_I, [_P, _P, _P, _P, _F, _P, _D, _D, _D, _D, _Z, _P, _P]),
     "smi_adagrad_gated_f32": (_I, [_P, _P, _P, _P, _F, _D, _D, _Z, _P, _P]),
     "smi_step_commit_f32": (_I, [_P, _P, _P, _I, _P, _P, _P, _P, _F, _F, _I, _P]),
+    "smi_predictive_reg_f32": (_I, [_MD, _P, _I, _P, _I, _P, _I, _P, _P, _P, _P, _P, _P, _P]),
+    "smi_metric_workspace_bytes": (_Z, [_I, _I]),
+    "smi_metric_rmse_f32": (_I, [_P, _P, _I, _I, _P, _P, _Z, _P]),
+    "smi_metric_nll_f32": (_I, [_P, _I, _I, _P, _P, _P, _Z, _P]),
 }
 
 _lib = None

@@ -1,0 +1,259 @@
+// Posterior predictive draws and regression metrics on the device.
+//
+// Restates what the reference does after the path with NumPyro's MixtureGuidePredictive /
+// Predictive (reference src/metrics.py:216-224 smi_sampler, :227-237 svgd_sampler; called at
+// experiments/uci_benchmark.py:297-316) for the regression BNNs (src/models/uci_bnn.py:21-68,
+// src/models/reg_1d_bnn.py:22-67):
+//   assignment a_s ~ Uniform{0..m-1};  u_s = loc_a + softplus(rho_a) eps_s;  theta = T(u)
+//   y_loc[s][n] = act(act(x_n W1 + b1) W2 + b2) . w3 + b3,   y[s][n] ~ N(y_loc, sigma_s)
+//   loglik[s][n] = log N(y_n; y_loc[s][n], sigma_s)           (numpyro.infer.log_likelihood)
+// and the metrics of src/metrics.py:249-268:
+//   rmse = sqrt(mean_{s,n} (y_n - y_loc[s][n])^2)
+//   nll  = -mean_n (logsumexp_s loglik[s][n] - log S),  lppd = sum_n (logsumexp_s ... - log S)
+// One CTA per draw: the draw's network is generated into shared memory (threefry noise, never
+// written to HBM), then one warp per data row.  Reductions are two-stage and fixed-order.
+//
+// Key chain (NumPyro's handler order could not be checked here -- SURVEY.md 8c "parity
+// unpinned"; it is restated identically in oracle/predictive.py): split(key, 3) = (assign, guide,
+// model); a_s = (bits(assign)[s] * m) >> 32; draw key = split(guide, S)[s], then one
+// (key, subkey) split per latent site in model order as in prng.cu; y noise = normal(split(model, S)[s], (n,)).
+#include <math.h>
+
+#include "common.cuh"
+#include "prng.cuh"
+
+namespace {
+
+using namespace smi_prng;
+
+constexpr float kLog2Pi = 1.8378770664093453f;
+constexpr int kThreads = 256;
+constexpr int kMaxHPerLane = 4;   // hidden <= 128
+
+__device__ __forceinline__ float softplus_f(float x) { return fmaxf(x, 0.f) + log1pf(expf(-fabsf(x))); }
+
+template <int ACT>
+__device__ __forceinline__ float act_f(float v) {
+  return ACT == SMI_ACT_RELU ? fmaxf(v, 0.f) : tanhf(v);
+}
+
+struct PredOffsets {
+  int prec, w1, b1, w2, b2, w3, b3;
+};
+
+template <int ACT>
+__global__ void __launch_bounds__(kThreads)
+predictive_reg_kernel(const SmiModelDesc md, PredOffsets o, const float* __restrict__ psi, int m,
+                      const uint32_t* __restrict__ key, int S, const float* __restrict__ x, int n,
+                      const float* __restrict__ y, int32_t* __restrict__ assign, float* __restrict__ latents,
+                      float* __restrict__ y_loc, float* __restrict__ y_draw, float* __restrict__ loglik) {
+  extern __shared__ float sm[];
+  const int L = md.latent_dim, d = md.particle_dim, I = md.in_dim, H = md.hidden;
+  float* th = sm;                 // [L] constrained latents of this draw
+  float* hbuf = sm + ((L + 3) & ~3);   // [warps][H] first hidden layer of the row a warp works on
+  __shared__ Key site_key[SMI_MAX_SITES];
+  __shared__ Key noise_key;
+  __shared__ int s_a;
+  const int s = blockIdx.x;
+  const bool delta = md.guide == SMI_GUIDE_DELTA;
+  if (threadIdx.x == 0) {
+    const Key k0 = {key[0], key[1]};
+    const Key ka = split_at(k0, 0), kg = split_at(k0, 1), km = split_at(k0, 2);
+    // AutoDelta (Predictive with batch_ndims = 1): draw s IS particle s
+    s_a = delta ? s % m : (int)(((unsigned long long)bits_at(ka, (uint32_t)s) * (unsigned long long)m) >> 32);
+    Key kk = split_at(kg, (uint32_t)s);
+    for (int t = 0; t < md.n_sites; ++t) {
+      site_key[t] = split_at(kk, 1);
+      kk = split_at(kk, 0);
+    }
+    noise_key = split_at(km, (uint32_t)s);
+    if (assign) assign[s] = s_a;
+  }
+  __syncthreads();
+  const float* p = psi + (size_t)s_a * d;
+  for (int t = 0; t < md.n_sites; ++t) {
+    const SmiSite st = md.sites[t];
+    const Key k = site_key[t];
+    for (int q = threadIdx.x; q < st.size; q += blockDim.x) {
+      float u = p[st.loc + q];
+      if (!delta) u = fmaf(softplus_f(p[st.rho + q]), normal_from_bits(bits_at(k, (uint32_t)q)), u);
+      const float v = st.transform == SMI_T_EXP ? expf(u) : u;
+      th[st.lat + q] = v;
+      if (latents) latents[(size_t)s * L + st.lat + q] = v;
+    }
+  }
+  __syncthreads();
+  const float sigma = md.noise == SMI_NOISE_GAMMA_PREC ? sqrtf(1.f / th[o.prec]) : md.sigma;
+  const float lognorm = -logf(sigma) - 0.5f * kLog2Pi;
+  const float* W1 = th + o.w1;
+  const float* W2 = th + o.w2;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  float* h1 = hbuf + warp * H;
+  for (int r = warp; r < n; r += nw) {
+    const float* xr = x + (size_t)r * I;
+    for (int j = lane; j < H; j += 32) {
+      float a = th[o.b1 + j];
+      for (int i = 0; i < I; ++i) a = fmaf(__ldg(xr + i), W1[i * H + j], a);
+      h1[j] = act_f<ACT>(a);
+    }
+    __syncwarp();
+    float part = 0.f;
+#pragma unroll
+    for (int c = 0; c < kMaxHPerLane; ++c) {
+      const int j = lane + 32 * c;
+      if (j < H) {
+        float a = th[o.b2 + j];
+        for (int k = 0; k < H; ++k) a = fmaf(h1[k], W2[k * H + j], a);
+        part = fmaf(act_f<ACT>(a), th[o.w3 + j], part);
+      }
+    }
+    __syncwarp();
+    const float out = warp_sum(part) + th[o.b3];
+    if (lane == 0) {
+      const size_t e = (size_t)s * n + r;
+      y_loc[e] = out;
+      if (y_draw) y_draw[e] = fmaf(sigma, normal_from_bits(bits_at(noise_key, (uint32_t)r)), out);
+      if (loglik) {
+        const float z = (y[r] - out) / sigma;
+        loglik[e] = -0.5f * z * z + lognorm;
+      }
+    }
+  }
+}
+
+// ---- metrics ------------------------------------------------------------------------------
+// Stage 1 of the squared-error sum: each CTA reduces a fixed slice (grid-stride, double), stage 2
+// is the last kernel below; both orders are fixed, so the result is run-to-run reproducible.
+__global__ void __launch_bounds__(kThreads)
+sqerr_partial_kernel(const float* __restrict__ y_loc, const float* __restrict__ y, int S, int n,
+                     double* __restrict__ part) {
+  __shared__ double red[32];
+  const size_t total = (size_t)S * n, stride = (size_t)gridDim.x * blockDim.x;
+  double acc = 0.0;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
+    const float df = y[e % n] - y_loc[e];
+    acc += (double)(df * df);
+  }
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) part[blockIdx.x] = acc;
+}
+
+__global__ void rmse_finish_kernel(const double* __restrict__ part, int nparts, double count, float* __restrict__ out) {
+  __shared__ double red[32];
+  double acc = 0.0;
+  for (int t = threadIdx.x; t < nparts; t += blockDim.x) acc += part[t];
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) out[0] = (float)sqrt(acc / count);
+}
+
+// One CTA per data point: logsumexp over the S draws of loglik[:, i] (two passes: max, then sum).
+__global__ void __launch_bounds__(kThreads)
+lse_columns_kernel(const float* __restrict__ loglik, int S, int n, float* __restrict__ lpd) {
+  __shared__ double red[32];
+  __shared__ float s_max;
+  const int i = blockIdx.x;
+  float mx = -INFINITY;
+  for (int s = threadIdx.x; s < S; s += blockDim.x) mx = fmaxf(mx, loglik[(size_t)s * n + i]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  float* fred = reinterpret_cast<float*>(red);
+  if ((threadIdx.x & 31) == 0) fred[threadIdx.x >> 5] = mx;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float v = fred[0];
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) v = fmaxf(v, fred[w]);
+    s_max = v;
+  }
+  __syncthreads();
+  const float m0 = s_max;
+  double acc = 0.0;
+  for (int s = threadIdx.x; s < S; s += blockDim.x) acc += (double)expf(loglik[(size_t)s * n + i] - m0);
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) lpd[i] = (float)((double)m0 + log(acc) - log((double)S));
+}
+
+__global__ void nll_finish_kernel(const float* __restrict__ lpd, int n, float* __restrict__ out) {
+  __shared__ double red[32];
+  double acc = 0.0;
+  for (int t = threadIdx.x; t < n; t += blockDim.x) acc += (double)lpd[t];
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) {
+    out[0] = (float)(-acc / (double)n);   // nll_reg_fn (src/metrics.py:256-263)
+    out[1] = (float)acc;                  // lppd_fn   (src/metrics.py:222-246)
+  }
+}
+
+int pred_offsets(const SmiModelDesc& md, PredOffsets& o) {
+  const bool gamma = md.noise == SMI_NOISE_GAMMA_PREC;
+  if (md.n_sites != (gamma ? 7 : 6)) SMI_FAIL(SMI_EINVAL, "predictive: regression BNN expects %d sites", gamma ? 7 : 6);
+  const SmiSite* s = md.sites + (gamma ? 1 : 0);
+  o.prec = gamma ? md.sites[0].lat : -1;
+  o.w1 = s[0].lat, o.b1 = s[1].lat, o.w2 = s[2].lat, o.b2 = s[3].lat, o.w3 = s[4].lat, o.b3 = s[5].lat;
+  const int I = md.in_dim, H = md.hidden;
+  if (s[0].size != I * H || s[1].size != H || s[2].size != H * H || s[3].size != H || s[4].size != H || s[5].size != 1)
+    SMI_FAIL(SMI_EINVAL, "predictive: site sizes do not match in_dim=%d hidden=%d", I, H);
+  return SMI_OK;
+}
+
+constexpr int kSqerrBlocks = 296;
+
+}  // namespace
+
+SMI_API int smi_predictive_reg_f32(const SmiModelDesc* md, const float* psi, int m, const uint32_t* key,
+                                   int num_samples, const float* x, int n, const float* y, int32_t* assign,
+                                   float* latents, float* y_loc, float* y_draw, float* loglik, void* stream) {
+  if (!md || !psi || !key || !x || !y_loc) SMI_FAIL(SMI_EINVAL, "smi_predictive_reg_f32: null pointer");
+  if (md->kind != SMI_MODEL_BNN_REG) SMI_FAIL(SMI_EINVAL, "smi_predictive_reg_f32: regression BNN descriptors only");
+  if (m < 1 || num_samples < 1 || n < 1) SMI_FAIL(SMI_EINVAL, "smi_predictive_reg_f32: m=%d S=%d n=%d", m, num_samples, n);
+  if (loglik && !y) SMI_FAIL(SMI_EINVAL, "smi_predictive_reg_f32: loglik needs the observed y");
+  if (md->hidden > 32 * kMaxHPerLane) SMI_FAIL(SMI_ELIMIT, "smi_predictive_reg_f32: hidden %d > 128", md->hidden);
+  PredOffsets o;
+  if (int rc = pred_offsets(*md, o)) return rc;
+  const size_t smem = ((size_t)((md->latent_dim + 3) & ~3) + (size_t)(kThreads / 32) * md->hidden) * sizeof(float);
+  if (smem > 200 * 1024) SMI_FAIL(SMI_ELIMIT, "smi_predictive_reg_f32: network of %d latents exceeds shared memory", md->latent_dim);
+  cudaStream_t st = (cudaStream_t)stream;
+  auto kern = md->act == SMI_ACT_RELU ? predictive_reg_kernel<SMI_ACT_RELU> : predictive_reg_kernel<SMI_ACT_TANH>;
+  if (smem > 48 * 1024) SMI_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  SMI_PROF_BEGIN(st);
+  kern<<<num_samples, kThreads, smem, st>>>(*md, o, psi, m, key, num_samples, x, n, y, assign, latents, y_loc, y_draw,
+                                            loglik);
+  SMI_LAUNCH_OK_N("predictive_reg_kernel", st);
+  return SMI_OK;
+}
+
+SMI_API size_t smi_metric_workspace_bytes(int num_samples, int n) {
+  (void)num_samples;
+  return smi_align_up(kSqerrBlocks * sizeof(double), 256) + smi_align_up((size_t)(n > 0 ? n : 1) * sizeof(float), 256);
+}
+
+SMI_API int smi_metric_rmse_f32(const float* y_loc, const float* y, int num_samples, int n, float* out, void* ws,
+                                size_t ws_bytes, void* stream) {
+  if (!y_loc || !y || !out || !ws) SMI_FAIL(SMI_EINVAL, "smi_metric_rmse_f32: null pointer");
+  if (num_samples < 1 || n < 1) SMI_FAIL(SMI_EINVAL, "smi_metric_rmse_f32: S=%d n=%d", num_samples, n);
+  if (ws_bytes < smi_metric_workspace_bytes(num_samples, n)) SMI_FAIL(SMI_ENOSPC, "smi_metric_rmse_f32: workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  double* part = (double*)ws;
+  SMI_PROF_BEGIN(st);
+  sqerr_partial_kernel<<<kSqerrBlocks, kThreads, 0, st>>>(y_loc, y, num_samples, n, part);
+  SMI_LAUNCH_OK_N("sqerr_partial_kernel", st);
+  SMI_PROF_BEGIN(st);
+  rmse_finish_kernel<<<1, kThreads, 0, st>>>(part, kSqerrBlocks, (double)num_samples * (double)n, out);
+  SMI_LAUNCH_OK_N("rmse_finish_kernel", st);
+  return SMI_OK;
+}
+
+SMI_API int smi_metric_nll_f32(const float* loglik, int num_samples, int n, float* out2, float* lpd, void* ws,
+                               size_t ws_bytes, void* stream) {
+  if (!loglik || !out2 || !ws) SMI_FAIL(SMI_EINVAL, "smi_metric_nll_f32: null pointer");
+  if (num_samples < 1 || n < 1) SMI_FAIL(SMI_EINVAL, "smi_metric_nll_f32: S=%d n=%d", num_samples, n);
+  if (ws_bytes < smi_metric_workspace_bytes(num_samples, n)) SMI_FAIL(SMI_ENOSPC, "smi_metric_nll_f32: workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  float* col = lpd ? lpd : (float*)((char*)ws + smi_align_up(kSqerrBlocks * sizeof(double), 256));
+  SMI_PROF_BEGIN(st);
+  lse_columns_kernel<<<n, kThreads, 0, st>>>(loglik, num_samples, n, col);
+  SMI_LAUNCH_OK_N("lse_columns_kernel", st);
+  SMI_PROF_BEGIN(st);
+  nll_finish_kernel<<<1, kThreads, 0, st>>>(col, n, out2);
+  SMI_LAUNCH_OK_N("nll_finish_kernel", st);
+  return SMI_OK;
+}
