@@ -102,15 +102,25 @@ class SteinVI:
             return t.contiguous()
         src = arr if isinstance(arr, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(arr))
         slot = self._stage.get(name)
-        if slot is None or slot[0].shape != src.shape or slot[0].dtype != src.dtype:
-            pin = torch.empty(src.shape, dtype=src.dtype, pin_memory=True)
+        if slot is None or slot[0][0].shape != src.shape or slot[0][0].dtype != src.dtype:
+            # two pinned buffers used alternately, each guarded by the event of its last H2D copy:
+            # without a per-step host sync the host runs ahead of the stream and must not overwrite
+            # a staging buffer whose copy has not executed yet
+            pins = [torch.empty(src.shape, dtype=src.dtype, pin_memory=True) for _ in range(2)]
+            evs = [torch.cuda.Event(), torch.cuda.Event()]
             dev = torch.empty(src.shape, dtype=dtype, device=self.device)
             raw = dev if src.dtype == dtype else torch.empty(src.shape, dtype=src.dtype, device=self.device)
-            slot = (pin, raw, dev)
+            slot = [pins, raw, dev, evs, 0, [False, False]]
             self._stage[name] = slot
-        pin, raw, dev = slot
+        pins, raw, dev, evs, turn, used = slot
+        pin = pins[turn]
+        if used[turn]:
+            evs[turn].synchronize()
         pin.copy_(src)
         raw.copy_(pin, non_blocking=True)
+        evs[turn].record()
+        used[turn] = True
+        slot[4] = turn ^ 1
         if raw is not dev:
             dev.copy_(raw)  # dtype conversion (e.g. uint8 pixels -> fp32), on the device
         self.h2d_bytes += src.numel() * src.element_size()
