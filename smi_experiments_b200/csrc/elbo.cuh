@@ -14,7 +14,21 @@
 constexpr int kGuideKT = 64;      // latent indices per CTA tile
 constexpr int kGuideMaxM = 256;   // mixture components supported by the AutoNormal path
 
+// Buffers of the tensor-core classifier path (elbo_cls_tc.cu): K-major fp32 hi / lo operand planes of
+// the two first-layer products, batched over all ELBO draws.
+struct ClsTcWs {
+  bool on;          // the path applies to this (model, minibatch) -- see smi_cls_tc_eligible
+  int Ip, Bp, nit;  // pad32(in_dim), pad32(B), i-tiles of 32
+  float *xh, *xl;   // [B x Ip]           x
+  float *xTh, *xTl; // [in_dim x Bp]      x^T
+  float *Wh, *Wl;   // [(ndraws H) x Ip]  W1^T of every draw: row (n, j), column i
+  float* H1;        // [ndraws x B x H]   act(x W1 + b1)
+  float *dHh, *dHl; // [(ndraws H) x Bp]  dh1^T of every draw
+  double* w1sq;     // [ndraws x nit]     partial sums of W1^2 (prior)
+};
+
 struct ElboWs {
+  ClsTcWs cls;
   int* loc_of;     // [L] latent index -> offset of loc in psi
   int* rho_of;     // [L]
   int* tr_of;      // [L] transform code
@@ -31,7 +45,8 @@ struct ElboWs {
   int nkt;
 };
 
-size_t smi_elbo_carve(SmiArena& ar, ElboWs& w, const SmiModelDesc& md, int m, int S, int nrows);
+size_t smi_elbo_carve(SmiArena& ar, ElboWs& w, const SmiModelDesc& md, int m, int S, int nrows, int B);
+bool smi_cls_tc_eligible(const SmiModelDesc& md, int B);
 
 int smi_guide_prep(const SmiModelDesc& md, const float* psi, int m, ElboWs& w, cudaStream_t st);
 int smi_guide_sample(const SmiModelDesc& md, const float* eps, int m, int S, int row0, int nrows, ElboWs& w,
@@ -47,4 +62,10 @@ int smi_delta_scatter(const SmiModelDesc& md, float tau, int nrows, ElboWs& w, f
 size_t smi_model_smem_bytes(const SmiModelDesc& md, int B);
 int smi_model_logp_grad(const SmiModelDesc& md, const float* Z, const int32_t* idx, const float* x,
                         const void* y, int ndraws, int B, float lik_scale, float* DZ, float* LOGP,
-                        cudaStream_t st);
+                        const ElboWs& w, cudaStream_t st);
+// Classifier BNN with the first-layer products as two batched tcgen05 GEMMs (elbo_cls_tc.cu).
+int smi_cls_tc_logp_grad(const SmiModelDesc& md, const ElboWs& w, const float* Z, const float* x, const int32_t* y,
+                         int ndraws, int B, float lik_scale, float* DZ, float* LOGP, cudaStream_t st);
+// The per-draw part between the two GEMMs (elbo_mlp_cls.cu): layers 2-3 forward and backward.
+int smi_cls_mid_launch(const SmiModelDesc& md, const ClsTcWs& c, const float* Z, const int32_t* y, int ndraws, int B,
+                       float lik_scale, float* DZ, float* LOGP, cudaStream_t st);

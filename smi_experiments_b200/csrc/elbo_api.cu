@@ -16,11 +16,10 @@ static int check_desc(const SmiModelDesc* md) {
 }
 
 SMI_API size_t smi_elbo_grad_workspace_bytes(const SmiModelDesc* md, int m, int S, int B, int nrows) {
-  (void)B;
   if (!md || m < 1 || S < 1 || nrows < 1) return 0;
   SmiArena ar(nullptr, 0);
   ElboWs w;
-  return smi_elbo_carve(ar, w, *md, m, S, nrows) + 512;
+  return smi_elbo_carve(ar, w, *md, m, S, nrows, B) + 512;
 }
 
 SMI_API int smi_elbo_grad_f32(const SmiModelDesc* md, const float* psi, const float* eps, const int32_t* idx,
@@ -37,11 +36,11 @@ SMI_API int smi_elbo_grad_f32(const SmiModelDesc* md, const float* psi, const fl
   cudaStream_t st = (cudaStream_t)stream;
   SmiArena ar(ws, ws_bytes);
   ElboWs w;
-  smi_elbo_carve(ar, w, *md, m, S, nrows);
+  smi_elbo_carve(ar, w, *md, m, S, nrows, B);
   if (md->guide == SMI_GUIDE_DELTA) {
     if (S != 1) SMI_FAIL(SMI_EINVAL, "AutoDelta guides take S = 1 (got %d)", S);
     if ((rc = smi_delta_gather(*md, psi, row0, nrows, w, st))) return rc;
-    if ((rc = smi_model_logp_grad(*md, w.Z, idx, x, y, nrows, B, lik_scale, w.DZ, w.LOGP, st))) return rc;
+    if ((rc = smi_model_logp_grad(*md, w.Z, idx, x, y, nrows, B, lik_scale, w.DZ, w.LOGP, w, st))) return rc;
     return smi_delta_scatter(*md, tau, nrows, w, G, elbo, st);
   }
   if (md->guide != SMI_GUIDE_NORMAL) SMI_FAIL(SMI_EINVAL, "guide=%d", md->guide);
@@ -50,6 +49,6 @@ SMI_API int smi_elbo_grad_f32(const SmiModelDesc* md, const float* psi, const fl
   if ((rc = smi_guide_prep(*md, psi, m, w, st))) return rc;
   if ((rc = smi_guide_sample(*md, eps, m, S, row0, nrows, w, st))) return rc;
   if ((rc = smi_guide_weights(*md, m, S, nrows, w, st))) return rc;
-  if ((rc = smi_model_logp_grad(*md, w.Z, idx, x, y, nrows * S, B, lik_scale, w.DZ, w.LOGP, st))) return rc;
+  if ((rc = smi_model_logp_grad(*md, w.Z, idx, x, y, nrows * S, B, lik_scale, w.DZ, w.LOGP, w, st))) return rc;
   return smi_guide_grad(*md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
 }

@@ -390,7 +390,7 @@ delta_scatter_kernel(const float* __restrict__ DZ, const float* __restrict__ LOG
 // ---- host side ---------------------------------------------------------------------------
 static int nlb_of(int L) { return (L + 255) / 256; }
 
-size_t smi_elbo_carve(SmiArena& ar, ElboWs& w, const SmiModelDesc& md, int m, int S, int nrows) {
+size_t smi_elbo_carve(SmiArena& ar, ElboWs& w, const SmiModelDesc& md, int m, int S, int nrows, int B) {
   const int L = md.latent_dim;
   w.nkt = (L + kGuideKT - 1) / kGuideKT;
   w.loc_of = ar.take<int>(L);
@@ -407,6 +407,22 @@ size_t smi_elbo_carve(SmiArena& ar, ElboWs& w, const SmiModelDesc& md, int m, in
   w.W = ar.take<float>(normal ? (size_t)nrows * S * m : 0);
   w.LOGQ = ar.take<float>((size_t)nrows * S);
   w.LOGP = ar.take<float>((size_t)nrows * S);
+  ClsTcWs& c = w.cls;
+  c.on = smi_cls_tc_eligible(md, B);
+  if (c.on) {
+    const size_t nd = (size_t)nrows * S, H = md.hidden, I = md.in_dim;
+    c.Ip = (md.in_dim + 31) / 32 * 32, c.Bp = (B + 31) / 32 * 32, c.nit = c.Ip / 32;
+    c.xh = ar.take<float>((size_t)B * c.Ip);
+    c.xl = ar.take<float>((size_t)B * c.Ip);
+    c.xTh = ar.take<float>(I * c.Bp);
+    c.xTl = ar.take<float>(I * c.Bp);
+    c.Wh = ar.take<float>(nd * H * c.Ip);
+    c.Wl = ar.take<float>(nd * H * c.Ip);
+    c.H1 = ar.take<float>(nd * B * H);
+    c.dHh = ar.take<float>(nd * H * c.Bp);
+    c.dHl = ar.take<float>(nd * H * c.Bp);
+    c.w1sq = ar.take<double>(nd * c.nit);
+  }
   return ar.off;
 }
 

@@ -435,7 +435,7 @@ int smi_model_cls_logp_grad(const SmiModelDesc& md, const float* Z, const float*
 
 int smi_model_logp_grad(const SmiModelDesc& md, const float* Z, const int32_t* idx, const float* x,
                         const void* y, int ndraws, int B, float lik_scale, float* DZ, float* LOGP,
-                        cudaStream_t st) {
+                        const ElboWs& w, cudaStream_t st) {
   const int L = md.latent_dim;
   if (md.kind == SMI_MODEL_GAUSS) {
     SMI_PROF_BEGIN(st);
@@ -445,6 +445,7 @@ int smi_model_logp_grad(const SmiModelDesc& md, const float* Z, const int32_t* i
   }
   if (md.kind == SMI_MODEL_BNN_CLS) {
     if (idx) SMI_FAIL(SMI_EINVAL, "bnn_cls takes the minibatch pre-sliced (idx must be NULL)");
+    if (w.cls.on) return smi_cls_tc_logp_grad(md, w, Z, x, (const int32_t*)y, ndraws, B, lik_scale, DZ, LOGP, st);
     return smi_model_cls_logp_grad(md, Z, x, (const int32_t*)y, ndraws, B, lik_scale, DZ, LOGP, st);
   }
   if (md.kind != SMI_MODEL_BNN_REG) SMI_FAIL(SMI_EINVAL, "unknown model kind %d", md.kind);

@@ -96,11 +96,21 @@ __device__ __forceinline__ void tile_gemm(int I, int J, int R, const float* __re
   }
 }
 
-template <int ACT>
+// TC = true is the per-draw part of the tensor-core path (elbo_cls_tc.cu): the first-layer forward
+// arrives as H1g (act already applied, written by the EPI_CLS_H1 GEMM) and instead of dW1 the
+// kernel leaves dh1^T as K-major hi / lo planes for the EPI_CLS_DW1 GEMM; sum W1^2 arrives in w1sq.
+struct ClsTcArgs {
+  const float* H1g;
+  float *dHh, *dHl;
+  const double* w1sq;
+  int Bp, nit;
+};
+
+template <int ACT, bool TC>
 __global__ void __launch_bounds__(kThreads)
 bnn_cls_kernel(const float* __restrict__ Z, const float* __restrict__ x, const int32_t* __restrict__ y, int L,
                int I, int H, int O, int B, float lik_scale, ClsOffsets o, float* __restrict__ DZ,
-               float* __restrict__ LOGP) {
+               float* __restrict__ LOGP, ClsTcArgs tc) {
   extern __shared__ __align__(16) float sm[];
   const int H1 = H | 1, O1 = O | 1, KC1 = KC + 1, HP = (H + 3) & ~3;
   float* ws = sm;                   // [KC][HP]   (16-byte aligned rows)
@@ -145,7 +155,14 @@ bnn_cls_kernel(const float* __restrict__ Z, const float* __restrict__ x, const i
 
   // ---- forward layer 1: h1 = act(x W1 + b1), W1 streamed in chunks of KC input rows ----
   zero_acc();
-  for (int k0 = 0; k0 < I; k0 += KC) {
+  if (TC) {
+    const float* hg = tc.H1g + (size_t)n * B * H;
+    for (int t = threadIdx.x; t < B * H; t += blockDim.x) {
+      const int b = t / H;
+      h1[b * H1 + (t - b * H)] = hg[t];
+    }
+  }
+  for (int k0 = 0; !TC && k0 < I; k0 += KC) {
     const int nk = min(KC, I - k0);
     __syncthreads();
     for (int t = threadIdx.x; t < B * KC; t += blockDim.x) {
@@ -159,7 +176,7 @@ bnn_cls_kernel(const float* __restrict__ Z, const float* __restrict__ x, const i
     __syncthreads();
     fwd_chunk(acc, xs, KC1, 1, B, ws, HP, nk, ntj, ntiles);
   }
-  store_act(h1, o.b1);
+  if (!TC) store_act(h1, o.b1);
   // ---- forward layer 2: h2 = act(h1 W2 + b2) ----
   zero_acc();
   for (int k0 = 0; k0 < H; k0 += KC) {
@@ -234,7 +251,20 @@ bnn_cls_kernel(const float* __restrict__ Z, const float* __restrict__ x, const i
     for (int b = 0; b < B; ++b) g += h2[b * H1 + j];
     emit_param(o.b1 + j, g);
   }
-  for (int k0 = 0; k0 < I; k0 += KC) {
+  if (TC) {
+    // dh1^T -> hi / lo planes, row (n, j), column b (zero beyond B): lanes run along b
+    for (int t = threadIdx.x; t < H * tc.Bp; t += blockDim.x) {
+      const int j = t / tc.Bp, b = t - j * tc.Bp;
+      const float v = b < B ? h2[b * H1 + j] : 0.f;
+      const float hi = __uint_as_float(__float_as_uint(v) & 0xFFFFE000u);
+      const size_t e = ((size_t)n * H + j) * tc.Bp + b;
+      tc.dHh[e] = hi;
+      tc.dHl[e] = v - hi;
+    }
+    if (threadIdx.x == 0)
+      for (int it = 0; it < tc.nit; ++it) lprior += tc.w1sq[(size_t)n * tc.nit + it];
+  }
+  for (int k0 = 0; !TC && k0 < I; k0 += KC) {
     const int nk = min(KC, I - k0);
     __syncthreads();
     for (int t = threadIdx.x; t < B * KC; t += blockDim.x) {
@@ -257,9 +287,8 @@ size_t cls_smem_bytes(int H, int O, int B) {
 
 }  // namespace
 
-int smi_model_cls_logp_grad(const SmiModelDesc& md, const float* Z, const float* x, const int32_t* y, int ndraws,
-                            int B, float lik_scale, float* DZ, float* LOGP, cudaStream_t st) {
-  const int I = md.in_dim, H = md.hidden, O = md.out_dim, L = md.latent_dim;
+static int cls_offsets(const SmiModelDesc& md, ClsOffsets& o) {
+  const int I = md.in_dim, H = md.hidden, O = md.out_dim;
   if (md.n_sites != 6) SMI_FAIL(SMI_EINVAL, "bnn_cls expects 6 sites");
   const SmiSite* s = md.sites;
   if (s[0].size != H || s[1].size != I * H || s[2].size != H || s[3].size != H * H || s[4].size != O ||
@@ -267,23 +296,51 @@ int smi_model_cls_logp_grad(const SmiModelDesc& md, const float* Z, const float*
     SMI_FAIL(SMI_EINVAL, "bnn_cls site sizes do not match in=%d hidden=%d out=%d", I, H, O);
   for (int t = 0; t < 6; ++t)
     if (s[t].transform != SMI_T_IDENTITY) SMI_FAIL(SMI_EINVAL, "bnn_cls sites are unconstrained");
-  ClsOffsets o;
   o.b1 = s[0].lat, o.w1 = s[1].lat, o.b2 = s[2].lat, o.w2 = s[3].lat, o.b3 = s[4].lat, o.w3 = s[5].lat;
+  return SMI_OK;
+}
+
+int smi_cls_mid_launch(const SmiModelDesc& md, const ClsTcWs& c, const float* Z, const int32_t* y, int ndraws, int B,
+                       float lik_scale, float* DZ, float* LOGP, cudaStream_t st) {
+  const int I = md.in_dim, H = md.hidden, O = md.out_dim, L = md.latent_dim;
+  ClsOffsets o;
+  if (int rc = cls_offsets(md, o)) return rc;
+  const int HP = (H + 3) & ~3;
+  if (((B + 3) / 4) * (HP / 4) > kSlots * kThreads)
+    SMI_FAIL(SMI_ELIMIT, "bnn_cls: batch %d x hidden %d exceeds the register tiling", B, H);
+  const size_t smem = cls_smem_bytes(H, O, B);
+  if (smem > 220 * 1024) SMI_FAIL(SMI_ELIMIT, "bnn_cls: activations need %zu B of shared memory", smem);
+  ClsTcArgs tc{c.H1, c.dHh, c.dHl, c.w1sq, c.Bp, c.nit};
+  auto kern = md.act == SMI_ACT_RELU ? bnn_cls_kernel<SMI_ACT_RELU, true> : bnn_cls_kernel<SMI_ACT_TANH, true>;
+  SMI_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  SMI_PROF_BEGIN(st);
+  kern<<<ndraws, kThreads, smem, st>>>(Z, nullptr, y, L, I, H, O, B, lik_scale, o, DZ, LOGP, tc);
+  SMI_LAUNCH_OK_N("bnn_cls_mid_kernel", st);
+  return SMI_OK;
+}
+
+int smi_model_cls_logp_grad(const SmiModelDesc& md, const float* Z, const float* x, const int32_t* y, int ndraws,
+                            int B, float lik_scale, float* DZ, float* LOGP, cudaStream_t st) {
+  const int I = md.in_dim, H = md.hidden, O = md.out_dim, L = md.latent_dim;
+  ClsOffsets o;
+  if (int rc = cls_offsets(md, o)) return rc;
   const int HP = (H + 3) & ~3;
   if (((B + 3) / 4) * (HP / 4) > kSlots * kThreads)
     SMI_FAIL(SMI_ELIMIT, "bnn_cls: batch %d x hidden %d exceeds the register tiling", B, H);
   const size_t smem = cls_smem_bytes(H, O, B);
   if (smem > 220 * 1024) SMI_FAIL(SMI_ELIMIT, "bnn_cls: activations need %zu B of shared memory", smem);
   if (md.act == SMI_ACT_RELU) {
-    SMI_CUDA_OK(cudaFuncSetAttribute(bnn_cls_kernel<SMI_ACT_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    SMI_CUDA_OK(cudaFuncSetAttribute(bnn_cls_kernel<SMI_ACT_RELU, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)smem));
     SMI_PROF_BEGIN(st);
-    bnn_cls_kernel<SMI_ACT_RELU><<<ndraws, kThreads, smem, st>>>(Z, x, y, L, I, H, O, B, lik_scale, o, DZ, LOGP);
+    bnn_cls_kernel<SMI_ACT_RELU, false><<<ndraws, kThreads, smem, st>>>(Z, x, y, L, I, H, O, B, lik_scale, o, DZ, LOGP,
+                                                                        ClsTcArgs{});
   } else {
-    SMI_CUDA_OK(cudaFuncSetAttribute(bnn_cls_kernel<SMI_ACT_TANH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    SMI_CUDA_OK(cudaFuncSetAttribute(bnn_cls_kernel<SMI_ACT_TANH, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)smem));
     SMI_PROF_BEGIN(st);
-    bnn_cls_kernel<SMI_ACT_TANH><<<ndraws, kThreads, smem, st>>>(Z, x, y, L, I, H, O, B, lik_scale, o, DZ, LOGP);
+    bnn_cls_kernel<SMI_ACT_TANH, false><<<ndraws, kThreads, smem, st>>>(Z, x, y, L, I, H, O, B, lik_scale, o, DZ, LOGP,
+                                                                        ClsTcArgs{});
   }
   SMI_LAUNCH_OK_N("bnn_cls_kernel", st);
   return SMI_OK;

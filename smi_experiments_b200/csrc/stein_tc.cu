@@ -14,7 +14,7 @@
 #include "common.cuh"
 #include "select.cuh"
 #include "stein_tc.cuh"
-#include "tc_gemm.cuh"
+#include "tc_launch.cuh"
 
 namespace {
 
@@ -133,66 +133,6 @@ __global__ void sumsq_finish_kernel(const double* __restrict__ lpart, int n, dou
   for (int i = threadIdx.x; i < n; i += blockDim.x) t += lpart[i];
   t = block_sum(t, red);
   if (threadIdx.x == 0) *out = t;
-}
-
-// ---- TMA descriptors ----------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
-                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
-                                  CUtensorMapFloatOOBfill);
-
-EncodeTiledFn get_encode() {
-  static EncodeTiledFn fn = nullptr;
-  if (!fn) {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
-        qres != cudaDriverEntryPointSuccess)
-      return nullptr;
-    fn = (EncodeTiledFn)p;
-  }
-  return fn;
-}
-
-// Plane [rows x ld] fp32, K-major; box = 32 x box_rows, SWIZZLE_128B, OOB rows read as zero.
-int make_map(CUtensorMap* map, const float* base, long long rows, long long ld, int box_rows) {
-  EncodeTiledFn enc = get_encode();
-  if (!enc) SMI_FAIL(SMI_ECUDA, "cuTensorMapEncodeTiled entry point not available");
-  cuuint64_t dims[2] = {(cuuint64_t)ld, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(float)};
-  cuuint32_t box[2] = {(cuuint32_t)tc::BK, (cuuint32_t)box_rows};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) SMI_FAIL(SMI_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
-  return SMI_OK;
-}
-
-template <int EPI>
-int launch_gemm(const float* Ah, const float* Al, long long a_rows, const float* Bh, const float* Bl,
-                long long b_rows, long long ldk, tc::GemmArgs ga, cudaStream_t st) {
-  CUtensorMap ma_h, ma_l, mb_h, mb_l;
-  int rc;
-  if ((rc = make_map(&ma_h, Ah, a_rows, ldk, tc::BM))) return rc;
-  if ((rc = make_map(&ma_l, Al, a_rows, ldk, tc::BM))) return rc;
-  if ((rc = make_map(&mb_h, Bh, b_rows, ldk, tc::BN))) return rc;
-  if ((rc = make_map(&mb_l, Bl, b_rows, ldk, tc::BN))) return rc;
-  ga.K = (int)ldk;
-  ga.tiles_m = (ga.M + tc::BM - 1) / tc::BM;
-  ga.tiles_n = (ga.N + tc::BN - 1) / tc::BN;
-  const int ntiles = ga.tiles_m * ga.tiles_n;
-  const int grid = ntiles < smi_num_sms() ? ntiles : smi_num_sms();
-  static bool attr_set[2] = {false, false};
-  if (!attr_set[EPI]) {
-    SMI_CUDA_OK(cudaFuncSetAttribute(tc::gemm3xtf32_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)tc::kSmemBytes));
-    attr_set[EPI] = true;
-  }
-  SMI_PROF_BEGIN(st);
-  tc::gemm3xtf32_kernel<EPI><<<grid, tc::kThreads, tc::kSmemBytes, st>>>(ma_h, ma_l, mb_h, mb_l, ga);
-  SMI_LAUNCH_OK_N("gemm3xtf32_kernel", st);
-  return SMI_OK;
 }
 
 inline int pad32(int v) { return (v + 31) / 32 * 32; }

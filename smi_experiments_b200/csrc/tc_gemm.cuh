@@ -12,6 +12,7 @@
 //   EPI_GRAM : D2[i][j] = max((n_i + n_j) - 2 acc, 0)            (all_pairs_eucl_dist, Gram form)
 //   EPI_FORCE: F[i][k]  = acc + c * rowsum_i * X[i][k],  sum F^2  (force sum + Frobenius norm)
 #pragma once
+#include "../../include/smi.h"
 #include "tc_ptx.cuh"
 
 namespace tc {
@@ -29,7 +30,7 @@ constexpr uint32_t kStageBytes = 2 * kABytes + 2 * kBBytes;  // 96 KB
 constexpr uint32_t kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
 constexpr int kGroupM = 16;  // tile rasterisation: 16 row-tiles share a B panel sweep
 
-enum { EPI_GRAM = 0, EPI_FORCE = 1 };
+enum { EPI_GRAM = 0, EPI_FORCE = 1, EPI_CLS_H1 = 2, EPI_CLS_DW1 = 3 };
 
 struct GemmArgs {
   int M, N, K;          // K already padded to a multiple of BK in the planes
@@ -48,6 +49,13 @@ struct GemmArgs {
   const float* rowsum;  // [M]
   const float* scal;    // scal[1] = c
   double* lpart;        // [gridDim.x] per-CTA sum of F^2
+  // EPI_CLS_H1 / EPI_CLS_DW1: batched classifier-BNN layer products over all ELBO draws (elbo_cls_tc.cu).
+  //   H1 : rows = minibatch row b, cols = (draw n, hidden j);  C[(n * M + b) * hdim + j] = act(acc + Z[n][off_b + j])
+  //   DW1: rows = (draw n, hidden j), cols = input i;          zout[n][off_w + i * hdim + j] = acc - zin[n][off_w + i * hdim + j]
+  const float* zin;     // [ndraws x zld] unconstrained draws
+  float* zout;          // [ndraws x zld] d log p / d u
+  long long zld;
+  int hdim, off_b, off_w, act;
 };
 
 __device__ __forceinline__ void tile_coords(int t, int tiles_m, int tiles_n, int& tm, int& tn) {
@@ -237,6 +245,43 @@ gemm3xtf32_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_con
       const int row = tm * BM + q * 32 + lane;
       const bool row_ok = row < args.M;
       const int colbase = tn * BN + half * kEpiCols;
+      if (EPI == EPI_CLS_H1) {
+        // columns are (draw, hidden unit); hdim % 4 == 0 keeps each float4 inside one draw
+        if (row_ok) {
+#pragma unroll
+          for (int j = 0; j < kEpiCols; j += 4) {
+            const int col = colbase + j;
+            if (col >= args.N) continue;
+            const int n = col / args.hdim, jj = col - n * args.hdim;
+            const float* bias = args.zin + (long long)n * args.zld + args.off_b + jj;
+            float v[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float pre = sum[j + e] + __ldg(bias + e);
+              v[e] = args.act == SMI_ACT_RELU ? fmaxf(pre, 0.f) : tanhf(pre);
+            }
+            *reinterpret_cast<float4*>(args.C + ((long long)n * args.M + row) * args.hdim + jj) =
+                make_float4(v[0], v[1], v[2], v[3]);
+          }
+        }
+        continue;
+      }
+      if (EPI == EPI_CLS_DW1) {
+        // rows are (draw, hidden unit): the 32 lanes of a warp write 32 consecutive floats of dW1[i][:]
+        if (row_ok) {
+          const int n = row / args.hdim, jj = row - n * args.hdim;
+          const long long base = (long long)n * args.zld + args.off_w + jj;
+#pragma unroll
+          for (int j = 0; j < kEpiCols; ++j) {
+            const int col = colbase + j;
+            if (col < args.N) {
+              const long long a = base + (long long)col * args.hdim;
+              args.zout[a] = sum[j] - __ldg(args.zin + a);   // N(0, 1) prior: d/dz (-z^2 / 2)
+            }
+          }
+        }
+        continue;
+      }
       float ra = 0.f;
       if (row_ok) ra = EPI == EPI_GRAM ? args.na[row] : c * args.rowsum[row];
       float* crow = args.C + (long long)row * args.ldc;

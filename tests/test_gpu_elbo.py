@@ -84,7 +84,8 @@ def test_gaussian_target(cuda, guide, m, S, dim):
 
 
 @pytest.mark.parametrize("m,S,B,I,H,O,scale255", [(2, 3, 16, 12, 8, 3, False), (3, 5, 128, 784, 100, 10, False),
-                                                  (2, 2, 128, 784, 100, 10, True), (2, 2, 50, 30, 10, 4, False)])
+                                                  (2, 2, 128, 784, 100, 10, True), (2, 2, 50, 30, 10, 4, False),
+                                                  (3, 4, 40, 70, 20, 5, False), (2, 3, 100, 200, 36, 7, False)])
 def test_mnist_mlp_smi(cuda, m, S, B, I, H, O, scale255):
     from smi_experiments_b200 import models
     pm, om = models.mnist_mlp(I, H, O), omodels.mnist_mlp(I, H, O)
