@@ -17,9 +17,9 @@
 namespace {
 
 constexpr float kLog2Pi = 1.8378770664093453f;
-constexpr int kThreads = 256;
+constexpr int kThreads = 512;
 constexpr int KC = 32;        // chunk of the streamed dimension
-constexpr int kSlots = 4;     // 4 x 4 register tiles per thread in the forward products
+constexpr int kSlots = 2;     // 4 x 4 register tiles per thread in the forward products
 
 struct ClsOffsets {
   int b1, w1, b2, w2, b3, w3;
@@ -63,14 +63,17 @@ __device__ __forceinline__ void fwd_chunk(float (&acc)[kSlots][16], const float*
 template <typename Emit>
 __device__ __forceinline__ void tile_gemm(int I, int J, int R, const float* __restrict__ P, int pi, int pr,
                                           const float* __restrict__ Q, int qr, int qj, Emit emit) {
+  // thread tile = rows i0..i0+3 x columns {jt, jt + ntj, jt + 2 ntj, jt + 3 ntj}: for a fixed column
+  // slot the lanes of a warp read consecutive columns of Q (conflict-free / coalesced), and P is a
+  // broadcast.
   const int nti = (I + 3) >> 2, ntj = (J + 3) >> 2;
   for (int t = threadIdx.x; t < nti * ntj; t += blockDim.x) {
-    const int i0 = (t / ntj) << 2, j0 = (t % ntj) << 2;
+    const int i0 = (t / ntj) << 2, jt = t % ntj;
     int io[4], jo[4];
 #pragma unroll
     for (int a = 0; a < 4; ++a) {
       io[a] = min(i0 + a, I - 1) * pi;
-      jo[a] = min(j0 + a, J - 1) * qj;
+      jo[a] = min(jt + a * ntj, J - 1) * qj;
     }
     float acc[4][4];
 #pragma unroll
@@ -92,7 +95,7 @@ __device__ __forceinline__ void tile_gemm(int I, int J, int R, const float* __re
     for (int a = 0; a < 4; ++a)
 #pragma unroll
       for (int b = 0; b < 4; ++b)
-        if (i0 + a < I && j0 + b < J) emit(i0 + a, j0 + b, acc[a][b]);
+        if (i0 + a < I && jt + b * ntj < J) emit(i0 + a, jt + b * ntj, acc[a][b]);
   }
 }
 
@@ -118,7 +121,7 @@ bnn_cls_kernel(const float* __restrict__ Z, const float* __restrict__ x, const i
   float* h2 = h1 + B * H1;          // [B][H1]   (later: dh1)
   float* dh = h2 + B * H1;          // [B][H1]   dh2
   float* lg = dh + B * H1;          // [B][O1]   logits, then d logits
-  float* xs = lg + B * O1;          // [B][KC1]
+  float* xs = lg + B * O1;          // [B][KC1]   (TC: [H][H1] copy of W2 instead, for the dh1 product)
   __shared__ double red[32];
   const int n = blockIdx.x;
   const float* __restrict__ z = Z + (size_t)n * L;
@@ -160,6 +163,10 @@ bnn_cls_kernel(const float* __restrict__ Z, const float* __restrict__ x, const i
     for (int t = threadIdx.x; t < B * H; t += blockDim.x) {
       const int b = t / H;
       h1[b * H1 + (t - b * H)] = hg[t];
+    }
+    for (int t = threadIdx.x; t < H * H; t += blockDim.x) {
+      const int k = t / H;
+      xs[k * H1 + (t - k * H)] = z[o.w2 + t];     // odd row stride: column reads are conflict-free
     }
   }
   for (int k0 = 0; !TC && k0 < I; k0 += KC) {
@@ -242,8 +249,12 @@ bnn_cls_kernel(const float* __restrict__ Z, const float* __restrict__ x, const i
     emit_param(o.b2 + j, g);
   }
   // dh1[b][k] = act'(h1[b][k]) * sum_j dh2[b][j] W2[k][j]   (W2 read from L2: 4 H^2 bytes)
-  tile_gemm(B, H, H, dh, H1, 1, z + o.w2, 1, H,
-            [&](int b, int k, float v) { h2[b * H1 + k] = v * dact_from_out<ACT>(h1[b * H1 + k]); });
+  if (TC)
+    tile_gemm(B, H, H, dh, H1, 1, xs, 1, H1,
+              [&](int b, int k, float v) { h2[b * H1 + k] = v * dact_from_out<ACT>(h1[b * H1 + k]); });
+  else
+    tile_gemm(B, H, H, dh, H1, 1, z + o.w2, 1, H,
+              [&](int b, int k, float v) { h2[b * H1 + k] = v * dact_from_out<ACT>(h1[b * H1 + k]); });
   __syncthreads();
   // ---- backward: layer 1.  dW1[k][j] = sum_b x[b][k] dh1[b][j], x streamed in row chunks; db1 ----
   for (int j = threadIdx.x; j < H; j += blockDim.x) {
@@ -280,9 +291,10 @@ bnn_cls_kernel(const float* __restrict__ Z, const float* __restrict__ x, const i
     LOGP[n] = (float)(-0.5 * lprior - 0.5 * (double)L * (double)kLog2Pi + (double)lik_scale * ll);
 }
 
-size_t cls_smem_bytes(int H, int O, int B) {
+size_t cls_smem_bytes(int H, int O, int B, bool tc = false) {
   const int H1 = H | 1, O1 = O | 1, HP = (H + 3) & ~3;
-  return ((size_t)KC * HP + (size_t)3 * B * H1 + (size_t)B * O1 + (size_t)B * (KC + 1)) * sizeof(float);
+  const size_t last = tc ? (size_t)H * H1 : (size_t)B * (KC + 1);
+  return ((size_t)KC * HP + (size_t)3 * B * H1 + (size_t)B * O1 + last) * sizeof(float);
 }
 
 }  // namespace
@@ -308,7 +320,7 @@ int smi_cls_mid_launch(const SmiModelDesc& md, const ClsTcWs& c, const float* Z,
   const int HP = (H + 3) & ~3;
   if (((B + 3) / 4) * (HP / 4) > kSlots * kThreads)
     SMI_FAIL(SMI_ELIMIT, "bnn_cls: batch %d x hidden %d exceeds the register tiling", B, H);
-  const size_t smem = cls_smem_bytes(H, O, B);
+  const size_t smem = cls_smem_bytes(H, O, B, true);
   if (smem > 220 * 1024) SMI_FAIL(SMI_ELIMIT, "bnn_cls: activations need %zu B of shared memory", smem);
   ClsTcArgs tc{c.H1, c.dHh, c.dHl, c.w1sq, c.Bp, c.nit};
   auto kern = md.act == SMI_ACT_RELU ? bnn_cls_kernel<SMI_ACT_RELU, true> : bnn_cls_kernel<SMI_ACT_TANH, true>;
