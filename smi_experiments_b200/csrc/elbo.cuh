@@ -38,11 +38,12 @@ struct ElboWs {
   double* logdet_part;  // [m x nkt]
   float* Z;        // [nrows x S x L] unconstrained draws
   float* DZ;       // [nrows x S x L] d log p / d u
-  float* QP;       // [nrows x nkt x S x m] partial quadratic forms
+  float* QP;       // [nrows x nkq x S x m] partial quadratic forms
   float* W;        // [nrows x S x m]
   float* LOGQ;     // [nrows x S]
   float* LOGP;     // [nrows x S]
-  int nkt;
+  int nkt;         // tiles of 64 latents (guide_grad grid)
+  int nkq, ksub;   // QP partials: nkq = ceil(nkt / ksub) groups of ksub tiles (guide_sample grid)
 };
 
 size_t smi_elbo_carve(SmiArena& ar, ElboWs& w, const SmiModelDesc& md, int m, int S, int nrows, int B);

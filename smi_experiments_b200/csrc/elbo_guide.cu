@@ -63,85 +63,141 @@ guide_prep_kernel(const SmiModelDesc md, const float* __restrict__ psi, int m, i
 }
 
 // ---------------------------------------------------------------------------------------
-// Quadratic forms a[s][j] = sum_k ((z_sk - mu_jk) / sigma_jk)^2 over one tile of 64 latents.
-// grid (nkt, nrows); 256 threads = 32 s-groups (4 draws each) x 8 j-groups (4 components each).
+// Quadratic forms a[s][j] = sum_k ((z_sk - mu_jk) / sigma_jk)^2 over KSUB consecutive tiles of 64
+// latents; also writes Z.  grid (nkq, nrows), 256 threads.
+// Thread = (component group tj: 4 components, draw group ts: 4 draws, latent slice ks): when the
+// S x m accumulator block needs fewer than 256 threads (C4: 14 x 3 groups) the 64 latents of a tile
+// are split over KS slices so the CTA stays busy; the slices are summed in a fixed order at the end.
+// KSUB > 1 (fewer, fatter partials for guide_weights) is used only when one pass covers all draws
+// and components (S <= 128, m <= 32).
 // smem: zt[64][128], mt[64][32], it[64][32], columns XOR-swizzled by ((k & 7) << 2).
 __global__ void __launch_bounds__(256)
 guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU, const float* __restrict__ SIG,
                     const float* __restrict__ ISIG, int m, int S, int L, int row0, float* __restrict__ Z,
-                    float* __restrict__ QP, int nkt) {
+                    float* __restrict__ QP, int nkq, int ksub) {
   extern __shared__ float sm[];
   float* zt = sm;                       // [64][128]
   float* mt = zt + kGuideKT * 128;      // [64][32]
   float* it = mt + kGuideKT * 32;       // [64][32]
-  const int kt = blockIdx.x, r = blockIdx.y, i = row0 + r;
-  const int k0 = kt * kGuideKT;
+  const int kq = blockIdx.x, r = blockIdx.y, i = row0 + r;
   // component chunks of JCH = 4 * njg <= 32 columns chosen to divide m evenly (m = 20 -> one chunk
-  // of 20, not a padded 32); thread = (draw group ts < 32, component group tj < njg)
+  // of 20, not a padded 32)
   const int nch = (m + 31) / 32;
   const int njg = (((m + nch - 1) / nch) + 3) >> 2, JCH = njg << 2;
-  const int tj = threadIdx.x % njg, ts = threadIdx.x / njg;
-  const bool lane_on = ts < 32;
+  const int nsg = (min(S, 128) + 3) >> 2;
+  const int nsj = njg * nsg;
+  int KS = 1;
+  while (KS < 8 && 2 * KS * nsj <= (int)blockDim.x) KS <<= 1;
+  const int tj = threadIdx.x % njg, ts = (threadIdx.x / njg) % nsg, ks = threadIdx.x / nsj;
+  const bool lane_on = ks < KS;
+  const int kper = kGuideKT / KS;        // latents of a tile per slice
   for (int sb = 0; sb < S; sb += 128) {
-    __syncthreads();
-    // stage z tile (and write Z): coalesced along k
-    for (int t = threadIdx.x; t < 128 * kGuideKT; t += blockDim.x) {
-      const int sl = t / kGuideKT, kk = t - sl * kGuideKT;
-      const int s = sb + sl, k = k0 + kk;
-      float z = 0.f;
-      if (s < S && k < L) {
-        const size_t e = ((size_t)r * S + s) * L + k;
-        z = fmaf(SIG[(size_t)i * L + k], eps[e], MU[(size_t)i * L + k]);
-        Z[e] = z;
-      }
-      zt[kk * 128 + (sl ^ ((kk & 7) << 2))] = z;
-    }
+    const int Sc = min(128, S - sb);
     for (int jb = 0; jb < m; jb += JCH) {
-      __syncthreads();
-      for (int t = threadIdx.x; t < JCH * kGuideKT; t += blockDim.x) {
-        const int jl = t / kGuideKT, kk = t - jl * kGuideKT;
-        const int j = jb + jl, k = k0 + kk;
-        float mu = 0.f, is = 0.f;  // is = 0 masks padded latents and components
-        if (j < m && jl < JCH && k < L) {
-          mu = MU[(size_t)j * L + k];
-          is = ISIG[(size_t)j * L + k];
-        }
-        const int c = jl ^ ((kk & 7) << 2);
-        mt[kk * 32 + c] = mu;
-        it[kk * 32 + c] = is;
-      }
-      __syncthreads();
-      if (!lane_on) continue;   // (no barrier below this point inside the chunk)
       float acc[4][4];
 #pragma unroll
       for (int a = 0; a < 4; ++a)
 #pragma unroll
         for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+      for (int sub = 0; sub < ksub; ++sub) {
+        const int k0 = (kq * ksub + sub) * kGuideKT;
+        if (k0 >= L) break;
+        __syncthreads();
+        // stage the z tile (and write Z on the first component chunk)
+        if ((L & 1) == 0 && k0 + kGuideKT <= L) {
+          // even L (every AutoNormal layout of the reference's models) keeps (row, k0) 8-byte aligned:
+          // the tile moves as float2 with four independent loads in flight per thread
+          constexpr int kHalf = kGuideKT / 2;
+          const int kk = (threadIdx.x % kHalf) * 2, sl0 = threadIdx.x / kHalf, dsl = blockDim.x / kHalf;
+          const float2 sg2 = *reinterpret_cast<const float2*>(SIG + (size_t)i * L + k0 + kk);
+          const float2 mu2 = *reinterpret_cast<const float2*>(MU + (size_t)i * L + k0 + kk);
+          for (int sl = sl0; sl < Sc; sl += 4 * dsl) {
+            float2 ev[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int s2 = sl + u * dsl;
+              ev[u] = s2 < Sc ? __ldcs(reinterpret_cast<const float2*>(eps + ((size_t)r * S + sb + s2) * L + k0 + kk))
+                              : make_float2(0.f, 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int s2 = sl + u * dsl;
+              if (s2 >= Sc) continue;
+              const float2 z2 = make_float2(fmaf(sg2.x, ev[u].x, mu2.x), fmaf(sg2.y, ev[u].y, mu2.y));
+              if (jb == 0) *reinterpret_cast<float2*>(Z + ((size_t)r * S + sb + s2) * L + k0 + kk) = z2;
+              zt[kk * 128 + (s2 ^ ((kk & 7) << 2))] = z2.x;
+              zt[(kk + 1) * 128 + (s2 ^ (((kk + 1) & 7) << 2))] = z2.y;
+            }
+          }
+        } else {
+          for (int t = threadIdx.x; t < Sc * kGuideKT; t += blockDim.x) {
+            const int sl = t / kGuideKT, kk = t - sl * kGuideKT;
+            const int s = sb + sl, k = k0 + kk;
+            float z = 0.f;
+            if (k < L) {
+              const size_t e = ((size_t)r * S + s) * L + k;
+              z = fmaf(SIG[(size_t)i * L + k], eps[e], MU[(size_t)i * L + k]);
+              if (jb == 0) Z[e] = z;
+            }
+            zt[kk * 128 + (sl ^ ((kk & 7) << 2))] = z;
+          }
+        }
+        for (int t = threadIdx.x; t < JCH * kGuideKT; t += blockDim.x) {
+          const int jl = t / kGuideKT, kk = t - jl * kGuideKT;
+          const int j = jb + jl, k = k0 + kk;
+          float mu = 0.f, is = 0.f;  // is = 0 masks padded latents and components
+          if (j < m && k < L) {
+            mu = MU[(size_t)j * L + k];
+            is = ISIG[(size_t)j * L + k];
+          }
+          const int c = jl ^ ((kk & 7) << 2);
+          mt[kk * 32 + c] = mu;
+          it[kk * 32 + c] = is;
+        }
+        __syncthreads();
+        if (lane_on) {
 #pragma unroll 4
-      for (int kk = 0; kk < kGuideKT; ++kk) {
-        const int sw = (kk & 7) << 2;
-        const float4 z4 = *reinterpret_cast<const float4*>(zt + kk * 128 + ((ts * 4) ^ sw));
-        const float4 m4 = *reinterpret_cast<const float4*>(mt + kk * 32 + ((tj * 4) ^ sw));
-        const float4 i4 = *reinterpret_cast<const float4*>(it + kk * 32 + ((tj * 4) ^ sw));
-        const float zz[4] = {z4.x, z4.y, z4.z, z4.w};
-        const float mm[4] = {m4.x, m4.y, m4.z, m4.w};
-        const float ii[4] = {i4.x, i4.y, i4.z, i4.w};
+          for (int kk = ks * kper; kk < (ks + 1) * kper; ++kk) {
+            const int sw = (kk & 7) << 2;
+            const float4 z4 = *reinterpret_cast<const float4*>(zt + kk * 128 + ((ts * 4) ^ sw));
+            const float4 m4 = *reinterpret_cast<const float4*>(mt + kk * 32 + ((tj * 4) ^ sw));
+            const float4 i4 = *reinterpret_cast<const float4*>(it + kk * 32 + ((tj * 4) ^ sw));
+            const float zz[4] = {z4.x, z4.y, z4.z, z4.w};
+            const float mm[4] = {m4.x, m4.y, m4.z, m4.w};
+            const float ii[4] = {i4.x, i4.y, i4.z, i4.w};
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+              for (int b = 0; b < 4; ++b) {
+                const float df = (zz[a] - mm[b]) * ii[b];
+                acc[a][b] = fmaf(df, df, acc[a][b]);
+              }
+          }
+        }
+      }
+      // ---- sum the latent slices in a fixed order, write the partial ----
+      __syncthreads();
+      float* red = zt;   // [KS][nsj][16]
+      if (lane_on) {
 #pragma unroll
         for (int a = 0; a < 4; ++a)
 #pragma unroll
-          for (int b = 0; b < 4; ++b) {
-            const float df = (zz[a] - mm[b]) * ii[b];
-            acc[a][b] = fmaf(df, df, acc[a][b]);
-          }
+          for (int b = 0; b < 4; ++b) red[((ks * nsj) + ts * njg + tj) * 16 + a * 4 + b] = acc[a][b];
       }
+      __syncthreads();
+      if (ks == 0) {
 #pragma unroll
-      for (int a = 0; a < 4; ++a) {
-        const int s = sb + ts * 4 + a;
-        if (s >= S) continue;
+        for (int a = 0; a < 4; ++a) {
+          const int s = sb + ts * 4 + a;
+          if (s >= S) continue;
 #pragma unroll
-        for (int b = 0; b < 4; ++b) {
-          const int j = jb + tj * 4 + b;
-          if (j < m && tj * 4 + b < JCH) QP[(((size_t)r * nkt + kt) * S + s) * m + j] = acc[a][b];
+          for (int b = 0; b < 4; ++b) {
+            const int j = jb + tj * 4 + b;
+            if (j >= m || tj * 4 + b >= JCH) continue;
+            float v = 0.f;
+            for (int q = 0; q < KS; ++q) v += red[((q * nsj) + ts * njg + tj) * 16 + a * 4 + b];
+            QP[(((size_t)r * nkq + kq) * S + s) * m + j] = v;
+          }
         }
       }
     }
@@ -195,7 +251,9 @@ guide_weights_kernel(const SmiModelDesc md, const float* __restrict__ QP, const 
 }
 
 // ---------------------------------------------------------------------------------------
-// grid (nkt, nrows), 256 threads = 64 latents x 4 draw groups.  MP = padded component count.
+// grid (ceil(L / kGradKT), nrows), 256 threads = 64 latents x 4 draw groups (128 x 2 measured slower
+// at C2: 66 vs 53 us).  MP = padded component count.
+constexpr int kGradKT = 64, kGradSG = 4;
 template <int MP>
 __global__ void __launch_bounds__(256)
 guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, const float* __restrict__ MU,
@@ -206,10 +264,10 @@ guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, 
                   float* __restrict__ elbo) {
   extern __shared__ float sm[];
   float* wt = sm;                        // [S][MP]
-  float* part = wt + (size_t)S * MP;     // [4][64][2]
+  float* part = wt + (size_t)S * MP;     // [kGradSG][kGradKT][2]
   const int kt = blockIdx.x, r = blockIdx.y, i = row0 + r;
-  const int kk = threadIdx.x & 63, sg = threadIdx.x >> 6;
-  const int k = kt * kGuideKT + kk;
+  const int kk = threadIdx.x & (kGradKT - 1), sg = threadIdx.x / kGradKT;
+  const int k = kt * kGradKT + kk;
   for (int t = threadIdx.x; t < S * MP; t += blockDim.x) {
     const int s = t / MP, j = t - s * MP;
     wt[t] = j < m ? W[((size_t)r * S + s) * m + j] : 0.f;
@@ -231,7 +289,7 @@ guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, 
     const float mu_i = MU[(size_t)i * L + k], sg_i = SIG[(size_t)i * L + k], is_i = ISIG[(size_t)i * L + k];
     const float jac = tr_of[k] == SMI_T_EXP ? 1.f : 0.f;
 #pragma unroll 4
-    for (int s = sg; s < S; s += 4) {
+    for (int s = sg; s < S; s += kGradSG) {
       const size_t e = ((size_t)r * S + s) * L + k;
       const float ep = __ldg(eps + e);
       const float z = fmaf(sg_i, ep, mu_i);
@@ -244,15 +302,15 @@ guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, 
       gs += du * ep - wi * (ep * ep - 1.f) * is_i;
     }
   }
-  part[(sg * 64 + kk) * 2] = gl;
-  part[(sg * 64 + kk) * 2 + 1] = gs;
+  part[(sg * kGradKT + kk) * 2] = gl;
+  part[(sg * kGradKT + kk) * 2 + 1] = gs;
   __syncthreads();
   if (sg == 0 && k < L) {
     float a = 0.f, b = 0.f;
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {
-      a += part[(g * 64 + kk) * 2];
-      b += part[(g * 64 + kk) * 2 + 1];
+    for (int g = 0; g < kGradSG; ++g) {
+      a += part[(g * kGradKT + kk) * 2];
+      b += part[(g * kGradKT + kk) * 2 + 1];
     }
     const float inv = 1.f / (float)S;
     G[(size_t)r * d + loc_of[k]] = a * inv;
@@ -393,6 +451,14 @@ static int nlb_of(int L) { return (L + 255) / 256; }
 size_t smi_elbo_carve(SmiArena& ar, ElboWs& w, const SmiModelDesc& md, int m, int S, int nrows, int B) {
   const int L = md.latent_dim;
   w.nkt = (L + kGuideKT - 1) / kGuideKT;
+  // fatter QP partials when one pass covers all draws and components: aim at ~16 CTAs per SM
+  w.ksub = 1;
+  if (S <= 128 && m <= 32) {
+    const long long ctas = (long long)w.nkt * nrows;
+    w.ksub = (int)(ctas / 2400);
+    w.ksub = w.ksub < 1 ? 1 : (w.ksub > 8 ? 8 : w.ksub);
+  }
+  w.nkq = (w.nkt + w.ksub - 1) / w.ksub;
   w.loc_of = ar.take<int>(L);
   w.rho_of = ar.take<int>(L);
   w.tr_of = ar.take<int>(L);
@@ -403,7 +469,7 @@ size_t smi_elbo_carve(SmiArena& ar, ElboWs& w, const SmiModelDesc& md, int m, in
   w.logdet_part = ar.take<double>(normal ? (size_t)m * nlb_of(L) : 0);
   w.Z = ar.take<float>((size_t)nrows * S * L);
   w.DZ = ar.take<float>((size_t)nrows * S * L);
-  w.QP = ar.take<float>(normal ? (size_t)nrows * w.nkt * S * m : 0);
+  w.QP = ar.take<float>(normal ? (size_t)nrows * w.nkq * S * m : 0);
   w.W = ar.take<float>(normal ? (size_t)nrows * S * m : 0);
   w.LOGQ = ar.take<float>((size_t)nrows * S);
   w.LOGP = ar.take<float>((size_t)nrows * S);
@@ -443,10 +509,10 @@ int smi_guide_sample(const SmiModelDesc& md, const float* eps, int m, int S, int
     SMI_CUDA_OK(cudaFuncSetAttribute(guide_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     set = true;
   }
-  dim3 grid(w.nkt, nrows);
+  dim3 grid(w.nkq, nrows);
   SMI_PROF_BEGIN(st);
   guide_sample_kernel<<<grid, 256, smem, st>>>(eps, w.MU, w.SIG, w.ISIG, m, S, md.latent_dim, row0, w.Z, w.QP,
-                                               w.nkt);
+                                               w.nkq, w.ksub);
   SMI_LAUNCH_OK_N("guide_sample_kernel", st);
   return SMI_OK;
 }
@@ -455,7 +521,7 @@ int smi_guide_weights(const SmiModelDesc& md, int m, int S, int nrows, ElboWs& w
   const int warps = nrows * S;
   SMI_PROF_BEGIN(st);
   guide_weights_kernel<<<(warps + 7) / 8, 256, 0, st>>>(md, w.QP, w.logdet_part, nlb_of(md.latent_dim), w.Z, m, S,
-                                                        nrows, w.nkt, w.W, w.LOGQ);
+                                                        nrows, w.nkq, w.W, w.LOGQ);
   SMI_LAUNCH_OK_N("guide_weights_kernel", st);
   return SMI_OK;
 }
@@ -463,11 +529,11 @@ int smi_guide_weights(const SmiModelDesc& md, int m, int S, int nrows, ElboWs& w
 template <int MP>
 static int launch_grad(const SmiModelDesc& md, const float* psi, const float* eps, int m, int S, float tau,
                        int row0, int nrows, ElboWs& w, float* G, float* elbo, cudaStream_t st) {
-  const size_t smem = ((size_t)S * MP + 4 * 64 * 2) * sizeof(float);
+  const size_t smem = ((size_t)S * MP + kGradSG * kGradKT * 2) * sizeof(float);
   if (smem > 200 * 1024) SMI_FAIL(SMI_ELIMIT, "guide_grad: S * m too large for shared memory");
   if (smem > 48 * 1024)
     SMI_CUDA_OK(cudaFuncSetAttribute(guide_grad_kernel<MP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dim3 grid(w.nkt, nrows);
+  dim3 grid((md.latent_dim + kGradKT - 1) / kGradKT, nrows);
   SMI_PROF_BEGIN(st);
   guide_grad_kernel<MP><<<grid, 256, smem, st>>>(psi, eps, w.MU, w.SIG, w.ISIG, w.W, w.DZ, w.LOGP, w.LOGQ,
                                                  w.loc_of, w.rho_of, w.tr_of, m, S, md.latent_dim,

@@ -112,14 +112,41 @@ __global__ void __launch_bounds__(1024) stein_small_finish(FinishArgs a) {
   __shared__ float s_h;
   const int np = pairs_of(m);
   // (a) deterministic reduction of the chunk partials, in double
+  // Q threads per pair, each over the chunks c = q mod Q in order, then the Q partials in order:
+  // with few pairs (m = 10: 55) and many chunks (d = 179 220) one thread per pair left the CTA idle.
+  const int Q = min(max((int)blockDim.x / np, 1), 16);
+  double* dpart = reinterpret_cast<double*>(((uintptr_t)(srt + P) + 7) & ~(uintptr_t)7);   // [Q][np][2]
+  if (Q > 1) {
+    const int q = threadIdx.x / np, p = threadIdx.x - q * np;
+    if (q < Q) {
+      double g = 0.0, s = 0.0;
+      const float2* src = reinterpret_cast<const float2*>(a.partial) + p;
+#pragma unroll 4
+      for (int c = q; c < a.nchunk; c += Q) {
+        const float2 v = src[(size_t)c * np];
+        g += (double)v.x;
+        s += (double)v.y;
+      }
+      dpart[((size_t)q * np + p) * 2] = g;
+      dpart[((size_t)q * np + p) * 2 + 1] = s;
+    }
+    __syncthreads();
+  }
   for (int p = threadIdx.x; p < np; p += blockDim.x) {  // one thread per pair, fixed order
     double g = 0.0, s = 0.0;
-    const float2* src = reinterpret_cast<const float2*>(a.partial) + p;
+    if (Q > 1) {
+      for (int q = 0; q < Q; ++q) {
+        g += dpart[((size_t)q * np + p) * 2];
+        s += dpart[((size_t)q * np + p) * 2 + 1];
+      }
+    } else {
+      const float2* src = reinterpret_cast<const float2*>(a.partial) + p;
 #pragma unroll 8
-    for (int c = 0; c < a.nchunk; ++c) {  // independent loads: the unrolled batch hides the L2 latency
-      const float2 v = src[(size_t)c * np];
-      g += (double)v.x;
-      s += (double)v.y;
+      for (int c = 0; c < a.nchunk; ++c) {  // independent loads: the unrolled batch hides the L2 latency
+        const float2 v = src[(size_t)c * np];
+        g += (double)v.x;
+        s += (double)v.y;
+      }
     }
     // decode p -> (i, j), i <= j
     int i = 0, rem = p;
@@ -293,11 +320,13 @@ int smi_stein_small_run(const float* X, const float* G, int m, int d, float c_at
   fa.counter = counter;
   int P = 1;
   while (P < m * m) P <<= 1;
-  const size_t fsm = ((size_t)2 * m * m + P) * sizeof(float);
+  const int fthreads = 1024, fnp = m * (m + 1) / 2;
+  const int fQ = fthreads / fnp < 1 ? 1 : (fthreads / fnp > 16 ? 16 : fthreads / fnp);
+  const size_t fsm = ((size_t)2 * m * m + P) * sizeof(float) + 8 + (fQ > 1 ? (size_t)fQ * fnp * 2 * sizeof(double) : 0);
   if (fsm > 40 * 1024)
-    SMI_CUDA_OK(cudaFuncSetAttribute(stein_small_finish, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    SMI_CUDA_OK(cudaFuncSetAttribute(stein_small_finish, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
   SMI_PROF_BEGIN(st);
-  stein_small_finish<<<1, m <= 16 ? 256 : 1024, fsm, st>>>(fa);
+  stein_small_finish<<<1, fthreads, fsm, st>>>(fa);
   SMI_LAUNCH_OK_N("stein_small_finish", st);
   if (dist_only) return SMI_OK;
 
