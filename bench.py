@@ -210,6 +210,50 @@ def bench_stein_sweep(torch, smi, dev, m, d, reps, flush, pk):
     return out
 
 
+def bench_other_configs(torch, smi, dev, flush):
+    """The other BASELINE.json configs (parity-test cases) timed the same
+    way as `value` (graph replay, L2 flushed between steps, CUDA events): context, not bench lines."""
+    out = {}
+
+    def timed(name, eng, state, args, kwargs, steps):
+        for _ in range(4):
+            state, loss = eng.update(state, *args, **kwargs)
+        torch.cuda.synchronize()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        for a, b in evs:
+            flush()
+            a.record()
+            state, loss = eng.update(state, *args, **kwargs)
+            b.record()
+        torch.cuda.synchronize()
+        ms = float(np.mean([a.elapsed_time(b) for a, b in evs]))
+        out[name] = dict(ms_per_step=ms, steps_per_s=1e3 / ms, loss=float(loss))
+
+    rng = np.random.default_rng(0)
+    model = smi.reg_1d_bnn(50)
+    eng = smi.SteinVI(model, smi.AutoNormal(model), smi.Adam(1e-3), smi.RBFKernel(), num_stein_particles=5,
+                      num_elbo_particles=100)
+    x = torch.linspace(-1.5, 1.7, 40, device=dev)
+    y = torch.sin(x)
+    timed("C1 sine BNN 1x50 hidden, SMI 5 particles, 100 draws", eng, eng.init(smi.PRNGKey(0), x, y), (x, y), {}, 20)
+    model = smi.GaussianTarget(1000)
+    eng = smi.SVGD(model, smi.Adam(0.05), smi.RBFKernel(), num_stein_particles=20,
+                   guide_kwargs={"init_loc_fn": smi.init_to_uniform(radius=2.0)})
+    timed("C3 Gaussian d=1000, SVGD 20 particles", eng, eng.init(smi.PRNGKey(2)), (), {}, 20)
+    eng = smi.SteinVI(model, smi.AutoNormal(model, init_loc_fn=smi.init_to_uniform(radius=2.0)), smi.Adagrad(0.05),
+                      smi.RBFKernel(), num_stein_particles=20, num_elbo_particles=100)
+    timed("C3 Gaussian d=1000, SMI 20 particles, 100 draws", eng, eng.init(smi.PRNGKey(2)), (), {}, 20)
+    model = smi.mnist_mlp()
+    eng = smi.SteinVI(model, smi.AutoNormal(model, init_loc_fn=smi.init_to_uniform(radius=0.05)), smi.Adagrad(0.8),
+                      smi.RBFKernel(), num_stein_particles=10, num_elbo_particles=55)
+    xb = torch.from_numpy(rng.integers(0, 256, (128, 784)).astype(np.float32) / 255.0).to(dev)
+    yb = torch.from_numpy(rng.integers(0, 10, 128).astype(np.int32)).to(dev)
+    st = eng.init(smi.PRNGKey(4), xb, yb, n=60000, batch_size=128)
+    timed("C4 MNIST-shape MLP 784-100-100-10, SMI 10 particles, 55 draws, batch 128", eng, st, (xb, yb),
+          dict(n=60000, batch_size=128), 10)
+    return out
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -311,9 +355,12 @@ def run_gpu(args):
             flop = 3.0 * 2.0 * (B * I * H + B * H * H + B * H) * m_local * S
             tf32_peak = 1100.0 * pk["bf16"] / 2250.0
             roof = dict(kernel=dom_name, bound="tensor", achieved=flop / dom_avg_ms / 1e9, peak=tf32_peak / 3.0,
-                        unit="TFLOP/s", frac=(flop / dom_avg_ms / 1e9) / (tf32_peak / 3.0), traffic=None,
+                        unit="TFLOP/s", frac=(flop / dom_avg_ms / 1e9) / (tf32_peak / 3.0),
+                        traffic=27312384 if world == 1 else None,   # dram read + write bytes per launch, ncu capture
+                        traffic_source="profiles/r01c_ncu_bnn_reg_mma_kernel_C2.txt",
                         algorithmic_flop=flop, peak_source=pk["src"],
-                        note="fp32 CUDA-core kernel measured against the 3xTF32 tensor roofline the north star names")
+                        note="warp-level mma.sync 3xTF32 kernel (one CTA per ELBO draw, per-draw weights) against the "
+                             "tcgen05 3xTF32 roofline the north star names: peak = 1100 x measured bf16 / 2250 / 3")
         else:
             d_ = eng.layout.particle_dim
             L_ = eng.layout.latent_dim
@@ -342,6 +389,8 @@ def run_gpu(args):
             sw = bench_sharded_force(args.sweep_m, 10000, args.sweep_reps, flush, pk)
         if rank == 0:
             line["stein_force"] = sw
+    if rank == 0 and world == 1 and not args.no_configs:
+        line["other_configs"] = bench_other_configs(torch, smi, dev, flush)
     # ---- CPU baseline (rank 0, N = 1 only): bounded sample of the same workload ----
     if rank == 0 and world == 1 and not args.no_cpu:
         step, cores = cpu_step_runner(os.cpu_count())
@@ -369,6 +418,7 @@ def main():
     ap.add_argument("--sweep-reps", type=int, default=3)
     ap.add_argument("--no-sweep", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-configs", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -237,6 +237,19 @@ def bench_sharded_force(m, d, reps, flush, pk):
         F, loss, h = unit()
         b.record()
     torch.cuda.synchronize()
+    # per-kernel durations of one more unit on this rank (libsmi's event profiler; untimed)
+    lib = _lib.load()
+    lib.smi_profile(1)
+    unit()
+    torch.cuda.synchronize()
+    lib.smi_profile(0)
+    import ctypes as C
+    buf = C.create_string_buffer(1 << 16)
+    lib.smi_profile_report(buf, len(buf))
+    kern = {}
+    for ln in buf.value.decode().splitlines():
+        nm, cnt, tms = ln.split()
+        kern[nm] = dict(launches=int(cnt), ms_per_step=float(tms))
     ms = torch.tensor([float(np.mean([a.elapsed_time(b) for a, b in evs]))], dtype=torch.float64, device=dev)
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms = float(ms)
@@ -246,7 +259,7 @@ def bench_sharded_force(m, d, reps, flush, pk):
     nv_bytes = 2.0 * (world - 1) / world * m * d * 4.0          # received per rank per step
     t_comm = nv_bytes / 770e9 * 1e3
     t_flop = W / world / (tf32_peak / 3.0 * 1e12) * 1e3
-    return dict(m=m, d=d, ms=ms, gflops=W / ms / 1e6, flop_per_step=W, loss=float(loss), h=float(h),
+    return dict(m=m, d=d, ms=ms, gflops=W / ms / 1e6, flop_per_step=W, loss=float(loss), h=float(h), kernels=kern,
                 roofline=dict(bound="tensor", achieved=W / ms / 1e9, peak=peak, unit="TFLOP/s",
                               frac=(W / ms / 1e9) / peak, traffic=None,
                               nvlink_bytes_per_rank=nv_bytes, t_comm_ms_at_770GBs=t_comm, t_flop_ms=t_flop,
