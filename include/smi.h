@@ -190,6 +190,20 @@ int smi_elbo_grad_f32(const SmiModelDesc* md, const float* psi, const float* eps
                       float lik_scale, float tau, int row0, int nrows, float* G, float* elbo,
                       void* ws, size_t ws_bytes, void* stream);
 
+/* As smi_elbo_grad_f32 with the loss temperature read from device memory at execution time (so a
+ * captured CUDA graph follows a schedule), and the ASVGD schedule itself (numpyro
+ * ASVGD._cyclical_annealing; reference src/methods/asvgd.py:4-27, src/engine_run.py:16-24):
+ *   *tau = cyc(t) / m,  t = *step - step0,
+ *   cyc(t) = (1 - last) (((t - 1) mod cycle_len + 1) / norm)^trans_speed + last,
+ *   norm = (num_steps + 1) / num_cycles, cycle_len = num_steps / num_cycles (integer),
+ *   last = min(t / ((num_cycles - 1) cycle_len), 1) (integer division; 1 when num_cycles = 1).      */
+int smi_elbo_grad_tau_f32(const SmiModelDesc* md, const float* psi, const float* eps,
+                          const int32_t* idx, const float* x, const void* y, int m, int S, int B,
+                          float lik_scale, const float* tau_dev, int row0, int nrows, float* G,
+                          float* elbo, void* ws, size_t ws_bytes, void* stream);
+int smi_asvgd_tau_f32(const int32_t* step, int step0, int num_steps, int num_cycles, int trans_speed,
+                      int m, float* tau, void* stream);
+
 /* ---- Counter PRNG (row a9): threefry2x32 key chain of one update on the device.
  *   key_in  : device uint32[2] state key.  key_out : device uint32[2] next state key (must not
  *   alias key_in; may be NULL).  n_total > 0 declares a data plate (it consumes one subkey even

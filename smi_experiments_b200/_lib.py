@@ -75,6 +75,8 @@ PROTOTYPES = {
     "smi_adagrad_f32": (_I, [_P, _P, _P, _P, _F, _P, _I, _D, _D, _Z, _P]),
     "smi_elbo_grad_workspace_bytes": (_Z, [_MD, _I, _I, _I, _I]),
     "smi_elbo_grad_f32": (_I, [_MD, _P, _P, _P, _P, _P, _I, _I, _I, _F, _F, _I, _I, _P, _P, _P, _Z, _P]),
+    "smi_elbo_grad_tau_f32": (_I, [_MD, _P, _P, _P, _P, _P, _I, _I, _I, _F, _P, _I, _I, _P, _P, _P, _Z, _P]),
+    "smi_asvgd_tau_f32": (_I, [_P, _I, _I, _I, _I, _I, _P, _P]),
     "smi_prng_step_f32": (_I, [_MD, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
     "smi_prng_split": (_I, [_P, _I, _P, _P]),
     "smi_prng_uniform_f32": (_I, [_P, _Z, _F, _F, _P, _P]),

@@ -54,9 +54,9 @@ int smi_guide_sample(const SmiModelDesc& md, const float* eps, int m, int S, int
                      cudaStream_t st);
 int smi_guide_weights(const SmiModelDesc& md, int m, int S, int nrows, ElboWs& w, cudaStream_t st);
 int smi_guide_grad(const SmiModelDesc& md, const float* psi, const float* eps, int m, int S, float tau,
-                   int row0, int nrows, ElboWs& w, float* G, float* elbo, cudaStream_t st);
+                   const float* tau_dev, int row0, int nrows, ElboWs& w, float* G, float* elbo, cudaStream_t st);
 int smi_delta_gather(const SmiModelDesc& md, const float* psi, int row0, int nrows, ElboWs& w, cudaStream_t st);
-int smi_delta_scatter(const SmiModelDesc& md, float tau, int nrows, ElboWs& w, float* G, float* elbo,
+int smi_delta_scatter(const SmiModelDesc& md, float tau, const float* tau_dev, int nrows, ElboWs& w, float* G, float* elbo,
                       cudaStream_t st);
 
 // Model kernels: Z (ndraws x L, unconstrained) -> DZ = d log p / d u, LOGP.

@@ -22,10 +22,10 @@ SMI_API size_t smi_elbo_grad_workspace_bytes(const SmiModelDesc* md, int m, int 
   return smi_elbo_carve(ar, w, *md, m, S, nrows, B) + 512;
 }
 
-SMI_API int smi_elbo_grad_f32(const SmiModelDesc* md, const float* psi, const float* eps, const int32_t* idx,
-                              const float* x, const void* y, int m, int S, int B, float lik_scale, float tau,
-                              int row0, int nrows, float* G, float* elbo, void* ws, size_t ws_bytes,
-                              void* stream) {
+static int elbo_grad_impl(const SmiModelDesc* md, const float* psi, const float* eps, const int32_t* idx,
+                          const float* x, const void* y, int m, int S, int B, float lik_scale, float tau,
+                          const float* tau_dev, int row0, int nrows, float* G, float* elbo, void* ws,
+                          size_t ws_bytes, void* stream) {
   int rc = check_desc(md);
   if (rc) return rc;
   if (!psi || !G || !ws) SMI_FAIL(SMI_EINVAL, "smi_elbo_grad_f32: null pointer");
@@ -41,7 +41,7 @@ SMI_API int smi_elbo_grad_f32(const SmiModelDesc* md, const float* psi, const fl
     if (S != 1) SMI_FAIL(SMI_EINVAL, "AutoDelta guides take S = 1 (got %d)", S);
     if ((rc = smi_delta_gather(*md, psi, row0, nrows, w, st))) return rc;
     if ((rc = smi_model_logp_grad(*md, w.Z, idx, x, y, nrows, B, lik_scale, w.DZ, w.LOGP, w, st))) return rc;
-    return smi_delta_scatter(*md, tau, nrows, w, G, elbo, st);
+    return smi_delta_scatter(*md, tau, tau_dev, nrows, w, G, elbo, st);
   }
   if (md->guide != SMI_GUIDE_NORMAL) SMI_FAIL(SMI_EINVAL, "guide=%d", md->guide);
   if (!eps) SMI_FAIL(SMI_EINVAL, "AutoNormal guides need eps");
@@ -50,5 +50,51 @@ SMI_API int smi_elbo_grad_f32(const SmiModelDesc* md, const float* psi, const fl
   if ((rc = smi_guide_sample(*md, eps, m, S, row0, nrows, w, st))) return rc;
   if ((rc = smi_guide_weights(*md, m, S, nrows, w, st))) return rc;
   if ((rc = smi_model_logp_grad(*md, w.Z, idx, x, y, nrows * S, B, lik_scale, w.DZ, w.LOGP, w, st))) return rc;
-  return smi_guide_grad(*md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
+  return smi_guide_grad(*md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+}
+
+SMI_API int smi_elbo_grad_f32(const SmiModelDesc* md, const float* psi, const float* eps, const int32_t* idx,
+                              const float* x, const void* y, int m, int S, int B, float lik_scale, float tau,
+                              int row0, int nrows, float* G, float* elbo, void* ws, size_t ws_bytes,
+                              void* stream) {
+  return elbo_grad_impl(md, psi, eps, idx, x, y, m, S, B, lik_scale, tau, nullptr, row0, nrows, G, elbo, ws, ws_bytes,
+                        stream);
+}
+
+SMI_API int smi_elbo_grad_tau_f32(const SmiModelDesc* md, const float* psi, const float* eps, const int32_t* idx,
+                                  const float* x, const void* y, int m, int S, int B, float lik_scale,
+                                  const float* tau_dev, int row0, int nrows, float* G, float* elbo, void* ws,
+                                  size_t ws_bytes, void* stream) {
+  if (!tau_dev) SMI_FAIL(SMI_EINVAL, "smi_elbo_grad_tau_f32: null temperature pointer");
+  return elbo_grad_impl(md, psi, eps, idx, x, y, m, S, B, lik_scale, 1.f, tau_dev, row0, nrows, G, elbo, ws, ws_bytes,
+                        stream);
+}
+
+// ASVGD's cyclical annealing on the device (numpyro ASVGD._cyclical_annealing, mirrored at reference
+// src/engine_run.py:16-24): tau = cyc(t) / m with t = *step - step0, evaluated in double like the host
+// schedule so a CUDA-graph replay of the step needs no host scalar.
+__global__ void asvgd_tau_kernel(const int32_t* __restrict__ step, int step0, int num_steps, int num_cycles,
+                                 int trans_speed, int m, float* __restrict__ tau) {
+  const long long t = (long long)*step - step0;
+  const double norm = (double)(num_steps + 1) / (double)num_cycles;
+  const int cycle_len = num_steps / num_cycles;
+  const long long last_start = (long long)(num_cycles - 1) * cycle_len;
+  const double last = last_start > 0 ? (double)(t / last_start < 1 ? t / last_start : 1) : 1.0;
+  double v = last;
+  if (last < 1.0 && cycle_len > 0) {
+    long long r = (t - 1) % cycle_len;   // Python's modulo: non-negative
+    if (r < 0) r += cycle_len;
+    v = (1.0 - last) * pow(((double)r + 1.0) / norm, (double)trans_speed) + last;
+  }
+  *tau = (float)(v / (double)m);
+}
+
+SMI_API int smi_asvgd_tau_f32(const int32_t* step, int step0, int num_steps, int num_cycles, int trans_speed, int m,
+                              float* tau, void* stream) {
+  if (!step || !tau) SMI_FAIL(SMI_EINVAL, "smi_asvgd_tau_f32: null pointer");
+  if (num_steps < 1 || num_cycles < 1 || m < 1) SMI_FAIL(SMI_EINVAL, "smi_asvgd_tau_f32: bad schedule");
+  SMI_PROF_BEGIN((cudaStream_t)stream);
+  asvgd_tau_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step, step0, num_steps, num_cycles, trans_speed, m, tau);
+  SMI_LAUNCH_OK_N("asvgd_tau_kernel", (cudaStream_t)stream);
+  return SMI_OK;
 }

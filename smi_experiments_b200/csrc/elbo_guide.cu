@@ -260,8 +260,9 @@ guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, 
                   const float* __restrict__ SIG, const float* __restrict__ ISIG, const float* __restrict__ W,
                   const float* __restrict__ DZ, const float* __restrict__ LOGP, const float* __restrict__ LOGQ,
                   const int* __restrict__ loc_of, const int* __restrict__ rho_of, const int* __restrict__ tr_of,
-                  int m, int S, int L, int d, float tau, int row0, float* __restrict__ G,
-                  float* __restrict__ elbo) {
+                  int m, int S, int L, int d, float tau_host, const float* __restrict__ tau_dev, int row0,
+                  float* __restrict__ G, float* __restrict__ elbo) {
+  const float tau = tau_dev ? *tau_dev : tau_host;   // device-side schedule (ASVGD) when given
   extern __shared__ float sm[];
   float* wt = sm;                        // [S][MP]
   float* part = wt + (size_t)S * MP;     // [kGradSG][kGradKT][2]
@@ -335,8 +336,9 @@ guide_grad_big_kernel(const float* __restrict__ psi, const float* __restrict__ e
                       const float* __restrict__ SIG, const float* __restrict__ ISIG, const float* __restrict__ W,
                       const float* __restrict__ DZ, const float* __restrict__ LOGP, const float* __restrict__ LOGQ,
                       const int* __restrict__ loc_of, const int* __restrict__ rho_of, const int* __restrict__ tr_of,
-                      int m, int S, int L, int d, float tau, int row0, float* __restrict__ G,
-                      float* __restrict__ elbo) {
+                      int m, int S, int L, int d, float tau_host, const float* __restrict__ tau_dev, int row0,
+                      float* __restrict__ G, float* __restrict__ elbo) {
+  const float tau = tau_dev ? *tau_dev : tau_host;
   extern __shared__ float sm[];
   float* wt = sm;                                   // [S][m] (+ kBigJC floats of slack)
   float* part = wt + (size_t)S * m + kBigJC;        // [4][64][2]
@@ -437,7 +439,9 @@ delta_gather_kernel(const SmiModelDesc md, const float* __restrict__ psi, int ro
 
 __global__ void __launch_bounds__(256)
 delta_scatter_kernel(const float* __restrict__ DZ, const float* __restrict__ LOGP, const int* __restrict__ loc_of,
-                     int L, int d, float tau, float* __restrict__ G, float* __restrict__ elbo) {
+                     int L, int d, float tau_host, const float* __restrict__ tau_dev, float* __restrict__ G,
+                     float* __restrict__ elbo) {
+  const float tau = tau_dev ? *tau_dev : tau_host;
   const int k = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
   if (k < L) G[(size_t)r * d + loc_of[k]] = tau * DZ[(size_t)r * L + k];
   if (k == 0 && elbo) elbo[r] = tau * LOGP[r];
@@ -528,7 +532,7 @@ int smi_guide_weights(const SmiModelDesc& md, int m, int S, int nrows, ElboWs& w
 
 template <int MP>
 static int launch_grad(const SmiModelDesc& md, const float* psi, const float* eps, int m, int S, float tau,
-                       int row0, int nrows, ElboWs& w, float* G, float* elbo, cudaStream_t st) {
+                       const float* tau_dev, int row0, int nrows, ElboWs& w, float* G, float* elbo, cudaStream_t st) {
   const size_t smem = ((size_t)S * MP + kGradSG * kGradKT * 2) * sizeof(float);
   if (smem > 200 * 1024) SMI_FAIL(SMI_ELIMIT, "guide_grad: S * m too large for shared memory");
   if (smem > 48 * 1024)
@@ -537,27 +541,27 @@ static int launch_grad(const SmiModelDesc& md, const float* psi, const float* ep
   SMI_PROF_BEGIN(st);
   guide_grad_kernel<MP><<<grid, 256, smem, st>>>(psi, eps, w.MU, w.SIG, w.ISIG, w.W, w.DZ, w.LOGP, w.LOGQ,
                                                  w.loc_of, w.rho_of, w.tr_of, m, S, md.latent_dim,
-                                                 md.particle_dim, tau, row0, G, elbo);
+                                                 md.particle_dim, tau, tau_dev, row0, G, elbo);
   SMI_LAUNCH_OK_N("guide_grad_kernel", st);
   return SMI_OK;
 }
 
 int smi_guide_grad(const SmiModelDesc& md, const float* psi, const float* eps, int m, int S, float tau,
-                   int row0, int nrows, ElboWs& w, float* G, float* elbo, cudaStream_t st) {
-  if (m <= 4) return launch_grad<4>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
-  if (m <= 8) return launch_grad<8>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
-  if (m <= 12) return launch_grad<12>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
-  if (m <= 16) return launch_grad<16>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
-  if (m <= 20) return launch_grad<20>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
-  if (m <= 24) return launch_grad<24>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
-  if (m <= 32) return launch_grad<32>(md, psi, eps, m, S, tau, row0, nrows, w, G, elbo, st);
+                   const float* tau_dev, int row0, int nrows, ElboWs& w, float* G, float* elbo, cudaStream_t st) {
+  if (m <= 4) return launch_grad<4>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+  if (m <= 8) return launch_grad<8>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+  if (m <= 12) return launch_grad<12>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+  if (m <= 16) return launch_grad<16>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+  if (m <= 20) return launch_grad<20>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+  if (m <= 24) return launch_grad<24>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+  if (m <= 32) return launch_grad<32>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
   const size_t smem = ((size_t)S * m + kBigJC + 4 * 64 * 2) * sizeof(float);
   if (smem > 220 * 1024) SMI_FAIL(SMI_ELIMIT, "guide_grad: S * m = %d x %d too large for shared memory", S, m);
   SMI_CUDA_OK(cudaFuncSetAttribute(guide_grad_big_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid(w.nkt, nrows);
   SMI_PROF_BEGIN(st);
   guide_grad_big_kernel<<<grid, 256, smem, st>>>(psi, eps, w.MU, w.SIG, w.ISIG, w.W, w.DZ, w.LOGP, w.LOGQ, w.loc_of,
-                                                 w.rho_of, w.tr_of, m, S, md.latent_dim, md.particle_dim, tau, row0,
+                                                 w.rho_of, w.tr_of, m, S, md.latent_dim, md.particle_dim, tau, tau_dev, row0,
                                                  G, elbo);
   SMI_LAUNCH_OK_N("guide_grad_big_kernel", st);
   return SMI_OK;
@@ -571,11 +575,11 @@ int smi_delta_gather(const SmiModelDesc& md, const float* psi, int row0, int nro
   return SMI_OK;
 }
 
-int smi_delta_scatter(const SmiModelDesc& md, float tau, int nrows, ElboWs& w, float* G, float* elbo,
+int smi_delta_scatter(const SmiModelDesc& md, float tau, const float* tau_dev, int nrows, ElboWs& w, float* G, float* elbo,
                       cudaStream_t st) {
   dim3 grid(nlb_of(md.latent_dim), nrows);
   SMI_PROF_BEGIN(st);
-  delta_scatter_kernel<<<grid, 256, 0, st>>>(w.DZ, w.LOGP, w.loc_of, md.latent_dim, md.particle_dim, tau, G, elbo);
+  delta_scatter_kernel<<<grid, 256, 0, st>>>(w.DZ, w.LOGP, w.loc_of, md.latent_dim, md.particle_dim, tau, tau_dev, G, elbo);
   SMI_LAUNCH_OK_N("delta_scatter_kernel", st);
   return SMI_OK;
 }

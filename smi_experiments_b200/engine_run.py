@@ -27,8 +27,7 @@ def setup_run(engine, dataset, compat_b3=False, seed=None):
         total = num_epochs * steps_per_epoch
         anneal = isinstance(engine, ASVGD) and not compat_b3
         if anneal:
-            engine._cyc = ASVGD._cyclical_annealing(num_epochs, engine.num_cycles, engine.trans_speed)
-            engine._t = 0
+            engine._begin_schedule(num_epochs)     # src/engine_run.py:17-19: the schedule length is num_epochs
         state, losses0 = init_state, []
         ring = torch.zeros(max(total, 1), dtype=torch.float32, device=engine.device)
         engine._ring = ring
@@ -53,7 +52,7 @@ def setup_run(engine, dataset, compat_b3=False, seed=None):
             engine._ring = None
             engine._graph = None
             if anneal:
-                engine._cyc = None
+                engine._end_schedule()
         return Result(engine.get_params(state), state, losses)
 
     return run

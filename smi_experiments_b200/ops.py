@@ -141,9 +141,21 @@ def elbo_grad(md, psi, eps, idx, x, y, S, B, lik_scale=1.0, tau=1.0, row0=0, nro
         elbo = torch.empty(nrows, dtype=torch.float32, device=psi.device)
     nbytes = load().smi_elbo_grad_workspace_bytes(C.byref(md), m, S, B, nrows)
     w = ws.get(nbytes, psi.device) if ws is not None else _ws("elbo", nbytes, psi.device)
-    call("smi_elbo_grad_f32", C.byref(md), _ptr(psi), _ptr(eps), _ptr(idx), _ptr(x), _ptr(y), m, S, B,
-         lik_scale, tau, row0, nrows, _ptr(G), _ptr(elbo), _ptr(w), w.numel(), _stream())
+    if isinstance(tau, torch.Tensor):      # device-side temperature (ASVGD schedule inside a CUDA graph)
+        _need_cuda(tau)
+        call("smi_elbo_grad_tau_f32", C.byref(md), _ptr(psi), _ptr(eps), _ptr(idx), _ptr(x), _ptr(y), m, S, B,
+             lik_scale, _ptr(tau), row0, nrows, _ptr(G), _ptr(elbo), _ptr(w), w.numel(), _stream())
+    else:
+        call("smi_elbo_grad_f32", C.byref(md), _ptr(psi), _ptr(eps), _ptr(idx), _ptr(x), _ptr(y), m, S, B,
+             lik_scale, tau, row0, nrows, _ptr(G), _ptr(elbo), _ptr(w), w.numel(), _stream())
     return G, elbo
+
+
+def asvgd_tau(step, step0, num_steps, num_cycles, trans_speed, m, out):
+    """out[0] = cyc(step - step0) / m on the device (ASVGD._cyclical_annealing).  row a10."""
+    _need_cuda(step, out)
+    call("smi_asvgd_tau_f32", _ptr(step), int(step0), int(num_steps), int(num_cycles), int(trans_speed), int(m),
+         _ptr(out), _stream())
 
 
 def prng_step(md, key_in, key_out, m, S, n_total=0, B=0, row0=0, nrows=None, eps=None, idx=None):

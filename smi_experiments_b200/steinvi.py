@@ -376,8 +376,7 @@ class ASVGD(SVGD):
                          **static_kwargs)
         self.num_cycles = int(num_cycles)
         self.trans_speed = int(trans_speed)
-        self._cyc = None
-        self._t = 0
+        self._sched = None
 
     @staticmethod
     def _cyclical_annealing(num_steps, num_cycles, trans_speed):
@@ -392,23 +391,31 @@ class ASVGD(SVGD):
 
         return cycle_fn
 
-    def _graphable(self):
-        return False  # tau changes every step (host scalar)
+    # The schedule runs on the device (smi_asvgd_tau_f32 reads the step counter), so the annealed
+    # step is CUDA-graph replayable like every other engine: no host scalar changes between steps.
+    def _begin_schedule(self, num_steps):
+        self._sched = dict(T=int(num_steps), step0=None)
+        self._tau_dev = torch.zeros(1, dtype=torch.float32, device=self.device)
+        self._graph = self._warm_sig = None
+
+    def _end_schedule(self):
+        self._sched = None
+        self._graph = self._warm_sig = None
 
     def _tau(self):
-        if self._cyc is None:
+        sched = getattr(self, "_sched", None)
+        if sched is None:
             return self.loss_temperature
-        return self._cyc(self._t) / float(self.num_stein_particles)
-
-    def update(self, state, *args, **kwargs):
-        out = super().update(state, *args, **kwargs)
-        self._t += 1
-        return out
+        step = self._state.optim_state.step
+        if sched["step0"] is None:
+            sched["step0"] = int(step.item())
+        ops.asvgd_tau(step, sched["step0"], sched["T"], self.num_cycles, self.trans_speed,
+                      self.num_stein_particles, self._tau_dev)
+        return self._tau_dev
 
     def run(self, rng_key, num_steps, *args, **kwargs):
-        self._cyc = ASVGD._cyclical_annealing(num_steps, self.num_cycles, self.trans_speed)
-        self._t = 0
+        self._begin_schedule(num_steps)
         try:
             return super().run(rng_key, num_steps, *args, **kwargs)
         finally:
-            self._cyc = None
+            self._end_schedule()

@@ -192,3 +192,44 @@ def test_setup_run_tuple(cuda):
     assert float(collect(info)) > 0 and l0 > 0
     assert int(extract_state(info).optim_state.step.item()) == 1
     assert isinstance(diagnostic(info), str)
+
+
+def test_asvgd_device_schedule_matches_host_formula(cuda):
+    """smi_asvgd_tau_f32 against ASVGD._cyclical_annealing (numpyro; mirrored at src/engine_run.py:16-24)."""
+    import smi_experiments_b200 as smi
+    from smi_experiments_b200 import ops
+    step = torch.zeros(1, dtype=torch.int32, device=cuda)
+    tau = torch.zeros(1, device=cuda)
+    for T, Cc, p, m, step0 in ((8, 2, 3, 5, 0), (100, 10, 10, 20, 7), (15000, 10, 10, 5, 0), (9, 1, 2, 3, 2)):
+        cyc = smi.ASVGD._cyclical_annealing(T, Cc, p)
+        for t in sorted(set([0, 1, 2, T // 2, T - 1, T, T + 3] + list(range(0, T + 1, max(T // 17, 1))))):
+            step.fill_(step0 + t)
+            ops.asvgd_tau(step, step0, T, Cc, p, m, tau)
+            want = np.float32(cyc(t) / float(m))
+            got = float(tau.item())
+            assert abs(got - want) <= 1e-6 * max(abs(want), 1e-30), (T, Cc, p, t, got, want)
+
+
+def test_asvgd_graph_run_matches_host_scheduled_eager_loop(cuda):
+    """ASVGD.run with the schedule on the device (CUDA-graph replay) == an eager loop that sets
+    loss_temperature = cyc(t) / m on the host before every update (the reference's body_fn)."""
+    import smi_experiments_b200 as smi
+    x = np.linspace(-1, 1, 40).astype(np.float32)
+    y = np.sin(3 * x).astype(np.float32)
+    T = 12
+
+    def mk(graph):
+        model = smi.reg_1d_bnn(5)
+        return smi.ASVGD(model, smi.Adam(1e-2), smi.RBFKernel(), num_stein_particles=5, num_cycles=3, trans_speed=2,
+                         use_cuda_graph=graph)
+    res = mk(True).run(smi.PRNGKey(0), T, x, y, progress_bar=False)
+    eng = mk(False)
+    cyc = smi.ASVGD._cyclical_annealing(T, 3, 2)
+    st = eng.init(smi.PRNGKey(0), x, y)
+    losses = []
+    for t in range(T):
+        eng.loss_temperature = cyc(t) / 5.0
+        st, l = eng.update(st, x, y)
+        losses.append(float(l))
+    np.testing.assert_allclose(res.losses.cpu().numpy(), np.asarray(losses, np.float32), rtol=2e-6)
+    np.testing.assert_allclose(res.state.optim_state.x.cpu().numpy(), st.optim_state.x.cpu().numpy(), rtol=1e-5, atol=1e-7)
