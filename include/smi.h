@@ -271,6 +271,14 @@ int smi_metric_rmse_f32(const float* y_loc, const float* y, int num_samples, int
 int smi_metric_nll_f32(const float* loglik, int num_samples, int n, float* out2, float* lpd, void* ws,
                        size_t ws_bytes, void* stream);
 
+/* Classification metrics of the reference (src/metrics.py:17-160, 270-321: nll_fn, acc_fn, brier_fn, ece_fn,
+ * mce_fn, conf_fn) per posterior draw.  logits (S, n, C) fp32; y (n) true labels; ypred (S, n) the sampled
+ * "y" site or NULL (then acc and conf are NaN); bins <= 128 (the reference uses 100).
+ * out6 (S, 6) = {nll, acc, brier, ece, mce, conf}.  ece / mce restate binned_conf_acc including its
+ * treatment of empty bins.                                                                      */
+int smi_metric_classification_f32(const float* logits, const int32_t* y, const int32_t* ypred, int num_samples,
+                                  int n, int num_classes, int bins, float* out6, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -77,3 +77,54 @@ def nll_reg(loglik):
 
 def lppd(loglik):
     return float(lpd(loglik).sum())
+
+
+# ---- classification metrics: literal numpy transcription of reference src/metrics.py ----------
+def _softmax(l):
+    e = np.exp(l - l.max(-1, keepdims=True))
+    return e / e.sum(-1, keepdims=True)
+
+
+def binned_conf_acc(logits, targets, bins=100):
+    """src/metrics.py:270-321, statement by statement (jnp gather clamps out-of-range indices;
+    jnp.histogram edges = linspace(0, 1, bins + 1) in float32, last bin right-closed)."""
+    confs_all = _softmax(np.asarray(logits, np.float64))
+    preds = confs_all.argmax(-1)
+    confs = confs_all.max(-1)
+    accs = preds == targets
+    idx = np.argsort(confs, kind="stable")
+    confs, accs = confs[idx], accs[idx]
+    edges = (np.arange(bins + 1, dtype=np.float32) / np.float32(bins)).astype(np.float64)
+    counts, _ = np.histogram(confs, bins=edges)
+    counts = counts.astype(int)
+
+    def compute_bins_mean(arr, counts):
+        bins_end = counts.cumsum()
+        bins_end = np.where(counts > 0, bins_end - 1, bins_end)
+        cs = arr.cumsum()
+        bin_cumsum = cs[np.clip(bins_end, 0, len(cs) - 1)]
+        prev = np.concatenate([np.array([0], cs.dtype), bin_cumsum[:-1]])
+        bin_sum = bin_cumsum - prev
+        return np.where(counts > 0, bin_sum / np.maximum(counts, 1), bin_sum)
+
+    return compute_bins_mean(confs, counts), compute_bins_mean(accs.astype(np.int64), counts)
+
+
+def classification_metrics(logits, y, ypred=None, bins=100):
+    """(P, 6) array {nll, acc, brier, ece, mce, conf} per posterior draw (nll_fn, acc_fn, brier_fn,
+    ece_fn, mce_fn, conf_fn of src/metrics.py:17-160); acc / conf need the sampled y site."""
+    logits = np.asarray(logits, np.float64)
+    P, n, C = logits.shape
+    out = np.full((P, 6), np.nan)
+    for p in range(P):
+        sm = _softmax(logits[p])
+        lsm = np.log(sm)
+        out[p, 0] = -lsm[np.arange(n), y].mean()
+        out[p, 2] = ((sm - np.eye(C)[y]) ** 2).sum(1).mean()
+        mc, ma = binned_conf_acc(logits[p], y, bins)
+        out[p, 3] = np.abs(mc - ma).mean()
+        out[p, 4] = np.abs(mc - ma).max()
+        if ypred is not None:
+            out[p, 1] = (y == ypred[p]).mean()
+            out[p, 5] = np.exp(lsm[np.arange(n), ypred[p]]).mean()
+    return out

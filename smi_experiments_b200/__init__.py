@@ -10,6 +10,7 @@ from . import _lib, models, ops  # noqa: F401
 from .kernels import RBFKernel  # noqa: F401
 from .models import (AutoDelta, AutoNormal, BNNClassifier, BNNRegression, GaussianTarget,  # noqa: F401
                      init_to_uniform, mnist_mlp, reg_1d_bnn, uci_bnn)
+from .predictive import classification_metrics  # noqa: F401
 from .predictive import MixtureGuidePredictive, Predictive, lppd_fn, nll_reg_fn, rmse_fn  # noqa: F401
 from .optim import Adagrad, Adam  # noqa: F401
 from .early_stop import OnlineEarlyStop  # noqa: F401

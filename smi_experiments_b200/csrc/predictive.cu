@@ -257,3 +257,119 @@ SMI_API int smi_metric_nll_f32(const float* loglik, int num_samples, int n, floa
   SMI_LAUNCH_OK_N("nll_finish_kernel", st);
   return SMI_OK;
 }
+
+// ---- classification metrics (reference src/metrics.py:17-160, 270-321) ----------------------------
+// One CTA per posterior draw p over logits[p] (n x C) and the true labels:
+//   out[p] = {nll, acc, brier, ece, mce, conf}
+//   nll   = -mean_i log softmax(l_i)[y_i]                               (nll_fn)
+//   acc   = mean_i [y_i == ypred_pi]      ypred = the sampled "y" site  (acc_fn)
+//   brier = mean_i sum_c (softmax(l_i)_c - 1[c == y_i])^2               (brier_fn)
+//   conf  = mean_i softmax(l_i)[ypred_pi]                               (conf_fn)
+//   ece / mce = mean / max over 100 bins of |mean conf - mean acc| with conf = max_c softmax, acc =
+//   [argmax == y] (ece_fn / mce_fn over binned_conf_acc).  binned_conf_acc's cumulative-sum
+//   bookkeeping is restated INCLUDING its behaviour on empty bins (an empty bin reports the first
+//   sorted element of the next occupied bin, which that bin then loses; trailing empty bins report 0):
+//   with T_k the sum over bins <= k and f_k the first sorted element after bin k,
+//   cum_k = T_k + (c_k == 0 ? f_k : 0), bin_sum_k = cum_k - cum_{k-1}, mean_k = c_k ? bin_sum_k / c_k : bin_sum_k.
+constexpr int kBinsMax = 128;
+
+__global__ void __launch_bounds__(kThreads)
+cls_metrics_kernel(const float* __restrict__ logits, const int32_t* __restrict__ y, const int32_t* __restrict__ ypred,
+                   int n, int C, int bins, float* __restrict__ out) {
+  __shared__ double red[32];
+  __shared__ unsigned int cnt[kBinsMax];
+  __shared__ unsigned int accs[kBinsMax];
+  __shared__ double csum[kBinsMax];
+  __shared__ unsigned long long first[kBinsMax];   // min over the bin of (conf bits, row, acc bit)
+  const int p = blockIdx.x;
+  const float* lg = logits + (size_t)p * n * C;
+  for (int k = threadIdx.x; k < bins; k += blockDim.x) {
+    cnt[k] = 0u, accs[k] = 0u, csum[k] = 0.0, first[k] = ~0ull;
+  }
+  __syncthreads();
+  double s_nll = 0.0, s_acc = 0.0, s_brier = 0.0, s_conf = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const float* l = lg + (size_t)i * C;
+    float mx = -INFINITY;
+    int am = 0;
+    for (int c = 0; c < C; ++c) {
+      const float v = l[c];
+      if (v > mx) mx = v, am = c;      // first maximum, as argmax
+    }
+    float se = 0.f;
+    for (int c = 0; c < C; ++c) se += expf(l[c] - mx);
+    const float lse = mx + logf(se);
+    const int yi = y[i];
+    s_nll += (double)(l[yi] - lse);
+    float br = 0.f, pmax = 0.f;
+    for (int c = 0; c < C; ++c) {
+      const float pc = expf(l[c] - mx) / se;      // nn.softmax
+      const float df = pc - (c == yi ? 1.f : 0.f);
+      br = fmaf(df, df, br);
+      pmax = fmaxf(pmax, pc);
+    }
+    s_brier += (double)br;
+    if (ypred) {
+      const int yp = ypred[(size_t)p * n + i];
+      s_acc += yp == yi ? 1.0 : 0.0;
+      s_conf += (double)expf(l[yp] - lse);
+    }
+    // histogram(confs, bins, range=(0, 1)): edges k / bins in float32, right edge of the last bin closed
+    int k = (int)(pmax * (float)bins);
+    k = k < 0 ? 0 : (k > bins - 1 ? bins - 1 : k);
+    while (k > 0 && pmax < __fdiv_rn((float)k, (float)bins)) --k;
+    while (k < bins - 1 && pmax >= __fdiv_rn((float)(k + 1), (float)bins)) ++k;
+    const unsigned int a = am == yi ? 1u : 0u;
+    atomicAdd(&cnt[k], 1u);
+    atomicAdd(&accs[k], a);
+    atomicAdd(&csum[k], (double)pmax);
+    atomicMin(&first[k], ((unsigned long long)__float_as_uint(pmax) << 32) | ((unsigned long long)i << 1) | a);
+  }
+  s_nll = block_sum(s_nll, red);
+  s_acc = block_sum(s_acc, red);
+  s_brier = block_sum(s_brier, red);
+  s_conf = block_sum(s_conf, red);     // (block_sum's barriers also publish the bins)
+  if (threadIdx.x == 0) {
+    double Tc = 0.0, prev_c = 0.0, ece = 0.0, mce = 0.0;
+    unsigned long long Ta = 0ull;
+    double prev_a = 0.0;
+    for (int k = 0; k < bins; ++k) {
+      Tc += csum[k];
+      Ta += accs[k];
+      double cum_c = Tc, cum_a = (double)Ta;
+      if (cnt[k] == 0u) {
+        int k2 = k + 1;
+        while (k2 < bins && cnt[k2] == 0u) ++k2;
+        if (k2 < bins) {
+          cum_c += (double)__uint_as_float((unsigned int)(first[k2] >> 32));
+          cum_a += (double)(first[k2] & 1ull);
+        }
+      }
+      double mc = cum_c - prev_c, ma = cum_a - prev_a;
+      if (cnt[k] > 0u) mc /= (double)cnt[k], ma /= (double)cnt[k];
+      prev_c = cum_c, prev_a = cum_a;
+      const double gap = fabs(mc - ma);
+      ece += gap;
+      mce = fmax(mce, gap);
+    }
+    float* o = out + (size_t)p * 6;
+    o[0] = (float)(-s_nll / (double)n);
+    o[1] = ypred ? (float)(s_acc / (double)n) : nanf("");
+    o[2] = (float)(s_brier / (double)n);
+    o[3] = (float)(ece / (double)bins);
+    o[4] = (float)mce;
+    o[5] = ypred ? (float)(s_conf / (double)n) : nanf("");
+  }
+}
+
+SMI_API int smi_metric_classification_f32(const float* logits, const int32_t* y, const int32_t* ypred, int num_samples,
+                                          int n, int num_classes, int bins, float* out6, void* stream) {
+  if (!logits || !y || !out6) SMI_FAIL(SMI_EINVAL, "smi_metric_classification_f32: null pointer");
+  if (num_samples < 1 || n < 1 || num_classes < 1) SMI_FAIL(SMI_EINVAL, "smi_metric_classification_f32: bad shape");
+  if (bins < 1 || bins > kBinsMax) SMI_FAIL(SMI_ELIMIT, "smi_metric_classification_f32: bins must be in [1, %d]", kBinsMax);
+  cudaStream_t st = (cudaStream_t)stream;
+  SMI_PROF_BEGIN(st);
+  cls_metrics_kernel<<<num_samples, kThreads, 0, st>>>(logits, y, ypred, n, num_classes, bins, out6);
+  SMI_LAUNCH_OK_N("cls_metrics_kernel", st);
+  return SMI_OK;
+}

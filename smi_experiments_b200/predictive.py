@@ -116,3 +116,25 @@ def lppd_fn(posterior_samples, model=None, xs=None, ys=None, batch_ndims=1):
     if ll is None:
         raise ValueError("call the predictive with y to get log-likelihoods")
     return _nll(ll)[1]
+
+
+def classification_metrics(posterior_samples, y, bins=100):
+    """{"nll", "acc", "brier", "ece", "mce", "conf"}: per-draw device vectors, the six metrics of
+    INDIST_EVAL_METRICS (src/constants.py:26-33; src/metrics.py:17-160) from ``posterior_samples["logits"]``
+    (S, n, C) and, for acc / conf, the sampled ``posterior_samples["y"]`` (S, n)."""
+    logits = torch.as_tensor(posterior_samples["logits"], dtype=torch.float32)
+    if not logits.is_cuda:
+        logits = logits.cuda()
+    logits = logits.contiguous()
+    if logits.dim() == 4:           # flatten_post_dim (src/metrics.py:324-345)
+        logits = logits.reshape(-1, *logits.shape[2:])
+    S, n, C = logits.shape
+    dev = logits.device
+    yd = torch.as_tensor(y).to(dev).to(torch.int32).contiguous()
+    yp = posterior_samples.get("y")
+    if yp is not None:
+        yp = torch.as_tensor(yp).to(dev).to(torch.int32).reshape(S, n).contiguous()
+    out = torch.empty(S, 6, device=dev)
+    _lib.call("smi_metric_classification_f32", ops._ptr(logits), ops._ptr(yd), ops._ptr(yp), S, n, C, int(bins),
+              ops._ptr(out), ops._stream())
+    return {k: out[:, i] for i, k in enumerate(("nll", "acc", "brier", "ece", "mce", "conf"))}

@@ -106,3 +106,22 @@ def test_metrics_at_reference_size_against_torch(cuda):
     assert abs(float(smi.lppd_fn(out)) - float(lpd.sum())) <= 1e-6 * abs(float(lpd.sum()))
     counts = torch.bincount(out["_assign"].long(), minlength=20).cpu().numpy()
     assert counts.sum() == 5000 and counts.min() > 150          # uniform over the 20 components
+
+
+@pytest.mark.parametrize("P,n,C,scale", [(3, 7, 4, 0.3), (5, 400, 10, 2.0), (2, 10000, 10, 4.0)])
+def test_classification_metrics_match_oracle(cuda, P, n, C, scale):
+    """nll / acc / brier / ece / mce / conf (src/metrics.py:17-160) incl. binned_conf_acc's empty-bin
+    behaviour; 10000 x 10 is the MNIST test-set shape."""
+    import smi_experiments_b200 as smi
+    rng = np.random.default_rng(n + C)
+    logits = (rng.standard_normal((P, n, C)) * scale).astype(np.float32)
+    y = rng.integers(0, C, n).astype(np.int32)
+    ypred = rng.integers(0, C, (P, n)).astype(np.int32)
+    got = smi.classification_metrics({"logits": torch.from_numpy(logits).to(cuda), "y": torch.from_numpy(ypred)}, y)
+    ref = op.classification_metrics(logits.astype(np.float64), y, ypred)
+    for i, k in enumerate(("nll", "acc", "brier", "ece", "mce", "conf")):
+        g = got[k].cpu().numpy().astype(np.float64)
+        assert np.all(np.abs(g - ref[:, i]) <= TOL * np.maximum(np.abs(ref[:, i]), 1e-2)), (k, g, ref[:, i])
+    # without the sampled y site: acc / conf undefined, the rest unchanged
+    got2 = smi.classification_metrics({"logits": torch.from_numpy(logits).to(cuda)}, y)
+    assert torch.isnan(got2["acc"]).all() and torch.equal(got2["ece"], got["ece"])

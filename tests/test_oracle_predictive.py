@@ -59,3 +59,38 @@ def test_delta_guide_is_one_draw_per_particle():
         u = psi[:, r["loc"]:r["loc"] + r["size"]]
         want = np.exp(u) if r["transform"] == om.T_EXP else u
         assert np.allclose(o["latents"][:, r["lat"]:r["lat"] + r["size"]], want)
+
+
+def test_binned_conf_acc_transcription_and_closed_form():
+    """The literal transcription of binned_conf_acc (src/metrics.py:270-321) agrees with the per-bin
+    closed form the device kernel uses: plain bin means for occupied bins that follow an occupied bin,
+    and the cumulative-sum artefacts around empty bins."""
+    rng = np.random.default_rng(0)
+    for n, C, scale in ((50, 3, 1.0), (400, 10, 3.0), (7, 4, 0.2)):
+        logits = rng.standard_normal((n, C)) * scale
+        y = rng.integers(0, C, n)
+        mc, ma = op.binned_conf_acc(logits, y, 100)
+        sm = np.exp(logits - logits.max(-1, keepdims=True))
+        sm /= sm.sum(-1, keepdims=True)
+        conf, acc = sm.max(-1), (sm.argmax(-1) == y).astype(float)
+        edges = (np.arange(101, dtype=np.float32) / np.float32(100)).astype(np.float64)
+        k = np.clip(np.searchsorted(edges, conf, side="right") - 1, 0, 99)
+        order = np.lexsort((np.arange(n), conf))
+        T_c = T_a = prev_c = prev_a = 0.0
+        for b in range(100):
+            sel = k == b
+            T_c, T_a = T_c + conf[sel].sum(), T_a + acc[sel].sum()
+            cum_c, cum_a = T_c, T_a
+            if not sel.any():
+                later = [i for i in order if k[i] > b]
+                if later:
+                    cum_c, cum_a = cum_c + conf[later[0]], cum_a + acc[later[0]]
+            want_c, want_a = cum_c - prev_c, cum_a - prev_a
+            if sel.any():
+                want_c, want_a = want_c / sel.sum(), want_a / sel.sum()
+            prev_c, prev_a = cum_c, cum_a
+            assert abs(mc[b] - want_c) < 1e-9 and abs(ma[b] - want_a) < 1e-9, (n, b)
+    # all rows in one bin and correct: perfectly calibrated except for the empty-bin artefact before it
+    logits = np.tile(np.array([[10.0, 0.0, 0.0]]), (20, 1))
+    m = op.classification_metrics(logits[None], np.zeros(20, int), np.zeros((1, 20), int))
+    assert abs(m[0, 1] - 1.0) < 1e-12 and m[0, 0] < 1e-3 and m[0, 2] < 1e-6
