@@ -279,6 +279,23 @@ int smi_metric_nll_f32(const float* loglik, int num_samples, int n, float* out2,
 int smi_metric_classification_f32(const float* logits, const int32_t* y, const int32_t* ypred, int num_samples,
                                   int n, int num_classes, int bins, float* out6, void* stream);
 
+/* Posterior-predictive draws for the classifier BNN (reference src/models/mlp.py:14-65 under
+ * MixtureGuidePredictive / Predictive, src/metrics.py:216-237; experiments/img_classifier.py:126-150):
+ *   smi_predictive_latents_f32 : latents (S, L) constrained draws of any model + assign (S), the guide half
+ *                                (same key chain as smi_predictive_reg_f32);
+ *   smi_predictive_cls_layer1  : h1 (S, n, H) = act(x W1_s + b1_s) as ONE stacked tcgen05 3xTF32 GEMM
+ *                                (M = n data rows, N = S x H, K = in_dim);
+ *   smi_predictive_cls_head    : logits (S, n, O) and the Categorical draw y (S, n) int32 (may be NULL),
+ *                                y = argmax_o(logits + Gumbel noise) as jax.random.categorical.           */
+int smi_predictive_latents_f32(const SmiModelDesc* md, const float* psi, int m, const uint32_t* key,
+                               int num_samples, int32_t* assign, float* latents, void* stream);
+size_t smi_predictive_cls_layer1_workspace_bytes(const SmiModelDesc* md, int num_samples, int n);
+int smi_predictive_cls_layer1_f32(const SmiModelDesc* md, const float* latents, int num_samples, const float* x,
+                                  int n, float* h1, void* ws, size_t ws_bytes, void* stream);
+int smi_predictive_cls_head_f32(const SmiModelDesc* md, const float* latents, const float* h1,
+                                const uint32_t* key, int num_samples, int n, float* logits, int32_t* y_draw,
+                                void* stream);
+
 #ifdef __cplusplus
 }
 #endif

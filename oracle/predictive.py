@@ -128,3 +128,39 @@ def classification_metrics(logits, y, ypred=None, bins=100):
             out[p, 1] = (y == ypred[p]).mean()
             out[p, 5] = np.exp(lsm[np.arange(n), ypred[p]]).mean()
     return out
+
+
+def predictive_cls(spec, psi, key, num_samples, x, guide="normal", dtype=np.float64):
+    """Classifier counterpart of predictive_reg (reference src/models/mlp.py:14-65 under
+    MixtureGuidePredictive): dict(assign, latents (S, L), logits (S, n, O), y (S, n)).
+    y = argmax(logits + Gumbel), Gumbel = -log(-log(uniform(key_s, (n, O), minval=tiny)))
+    (jax.random.categorical, as numpyro's Categorical.sample draws)."""
+    rows, L, d = models.layout(spec, guide)
+    psi = np.asarray(psi, dtype)
+    m, S, n = psi.shape[0], int(num_samples), x.shape[0]
+    ka, kg, km = prng.split(np.asarray(key, np.uint32), 3)
+    assign = (prng.randint_bits_to_index(prng.random_bits(ka, S), m) if guide == "normal"
+              else (np.arange(S) % m).astype(np.int32))
+    dkeys, nkeys = prng.split(kg, S), prng.split(km, S)
+    lat = np.zeros((S, L), dtype)
+    for s in range(S):
+        kk = dkeys[s]
+        p = psi[assign[s]]
+        for r in rows:
+            kk, sub = prng.split(kk, 2)
+            u = p[r["loc"]:r["loc"] + r["size"]]
+            if guide == "normal":
+                u = u + softplus(p[r["rho"]:r["rho"] + r["size"]]) * prng.normal(sub, r["size"]).astype(dtype)
+            lat[s, r["lat"]:r["lat"] + r["size"]] = u
+    tdt = torch.float64 if dtype == np.float64 else torch.float32
+    xb = torch.from_numpy(np.asarray(x, dtype).reshape(n, -1)).to(tdt)[None].expand(S, n, -1)
+    logits = models.forward(spec, torch.from_numpy(lat).to(tdt), xb).numpy()
+    O = logits.shape[-1]
+    tiny = np.float32(1.17549435e-38)
+    y = np.zeros((S, n), np.int32)
+    for s in range(S):
+        f = prng.bits_to_unit_float(prng.random_bits(nkeys[s], n * O)).astype(np.float32)
+        u = np.maximum(tiny, f + tiny).astype(np.float64)
+        g = -np.log(-np.log(u)).reshape(n, O)
+        y[s] = np.argmax(logits[s] + g, axis=-1)
+    return dict(assign=assign, latents=lat, logits=logits, y=y)

@@ -89,6 +89,10 @@ PROTOTYPES = {
     "smi_predictive_reg_f32": (_I, [_MD, _P, _I, _P, _I, _P, _I, _P, _P, _P, _P, _P, _P, _P]),
     "smi_metric_workspace_bytes": (_Z, [_I, _I]),
     "smi_metric_rmse_f32": (_I, [_P, _P, _I, _I, _P, _P, _Z, _P]),
+    "smi_predictive_latents_f32": (_I, [_MD, _P, _I, _P, _I, _P, _P, _P]),
+    "smi_predictive_cls_layer1_workspace_bytes": (_Z, [_MD, _I, _I]),
+    "smi_predictive_cls_layer1_f32": (_I, [_MD, _P, _I, _P, _I, _P, _P, _Z, _P]),
+    "smi_predictive_cls_head_f32": (_I, [_MD, _P, _P, _P, _I, _I, _P, _P, _P]),
     "smi_metric_classification_f32": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _P]),
     "smi_metric_nll_f32": (_I, [_P, _I, _I, _P, _P, _P, _Z, _P]),
 }

@@ -47,7 +47,7 @@ cls_xsplit_kernel(const float* __restrict__ x, int B, int I, int Ip, int Bp, flo
   __syncthreads();
   for (int r = ty; r < 32; r += 8) {
     const int i = i0 + r, b = b0 + tx;
-    if (i < I && b < Bp) {
+    if (xTh && i < I && b < Bp) {
       float hi, lo;
       split2(tile[tx][r], hi, lo);   // zero beyond B
       xTh[(size_t)i * Bp + b] = hi;
@@ -137,4 +137,62 @@ int smi_cls_tc_logp_grad(const SmiModelDesc& md, const ElboWs& w, const float* Z
       return rc;
   }
   return SMI_OK;
+}
+
+// ---- first layer of the classifier for posterior-predictive draws ---------------
+// h1[s][r][j] = act(sum_i x[r][i] W1_s[i][j] + b1_s[j]) for S draws of the latents and n data rows: the
+// same stacked forward GEMM as above with M = n (e.g. the 10 000 MNIST test rows).
+static void pred_carve(SmiArena& ar, int S, int n, int I, int H, float*& xh, float*& xl, float*& Wh, float*& Wl,
+                       double*& w1sq, int& Ip) {
+  Ip = (I + 31) / 32 * 32;
+  xh = ar.take<float>((size_t)n * Ip);
+  xl = ar.take<float>((size_t)n * Ip);
+  Wh = ar.take<float>((size_t)S * H * Ip);
+  Wl = ar.take<float>((size_t)S * H * Ip);
+  w1sq = ar.take<double>((size_t)S * (Ip / 32));
+}
+
+SMI_API size_t smi_predictive_cls_layer1_workspace_bytes(const SmiModelDesc* md, int num_samples, int n) {
+  if (!md || num_samples < 1 || n < 1) return 0;
+  SmiArena ar(nullptr, 0);
+  float *a, *b, *c, *d;
+  double* e;
+  int Ip;
+  pred_carve(ar, num_samples, n, md->in_dim, md->hidden, a, b, c, d, e, Ip);
+  return ar.off + 512;
+}
+
+SMI_API int smi_predictive_cls_layer1_f32(const SmiModelDesc* md, const float* latents, int num_samples, const float* x,
+                                          int n, float* h1, void* ws, size_t ws_bytes, void* stream) {
+  if (!md || !latents || !x || !h1 || !ws) SMI_FAIL(SMI_EINVAL, "smi_predictive_cls_layer1_f32: null pointer");
+  if (md->kind != SMI_MODEL_BNN_CLS || md->n_sites != 6) SMI_FAIL(SMI_EINVAL, "smi_predictive_cls_layer1_f32: classifier BNN only");
+  if (md->hidden % 4 != 0) SMI_FAIL(SMI_ELIMIT, "smi_predictive_cls_layer1_f32: hidden width must be a multiple of 4");
+  if (ws_bytes < smi_predictive_cls_layer1_workspace_bytes(md, num_samples, n))
+    SMI_FAIL(SMI_ENOSPC, "smi_predictive_cls_layer1_f32: workspace too small");
+  const int I = md->in_dim, H = md->hidden, S = num_samples;
+  if ((long long)S * H > 0x7fffffffLL / 2) SMI_FAIL(SMI_ELIMIT, "smi_predictive_cls_layer1_f32: %d draws x %d hidden units", S, H);
+  cudaStream_t st = (cudaStream_t)stream;
+  SmiArena ar(ws, ws_bytes);
+  float *xh, *xl, *Wh, *Wl;
+  double* w1sq;
+  int Ip;
+  pred_carve(ar, S, n, I, H, xh, xl, Wh, Wl, w1sq, Ip);
+  {
+    dim3 grid(Ip / 32, (n + 31) / 32);
+    SMI_PROF_BEGIN(st);
+    cls_xsplit_kernel<<<grid, 256, 0, st>>>(x, n, I, Ip, 0, xh, xl, nullptr, nullptr);
+    SMI_LAUNCH_OK_N("cls_xsplit_kernel", st);
+  }
+  {
+    dim3 grid(Ip / 32, S);
+    SMI_PROF_BEGIN(st);
+    cls_w1t_kernel<<<grid, 256, 0, st>>>(latents, (long long)md->latent_dim, md->sites[1].lat, I, H, Ip, Wh, Wl, w1sq);
+    SMI_LAUNCH_OK_N("cls_w1t_kernel", st);
+  }
+  tc::GemmArgs ga{};
+  ga.M = n, ga.N = S * H;
+  ga.C = h1, ga.ldc = 0;
+  ga.zin = latents, ga.zout = nullptr, ga.zld = md->latent_dim, ga.hdim = H, ga.off_b = md->sites[0].lat,
+  ga.off_w = md->sites[1].lat, ga.act = md->act;
+  return launch_gemm<tc::EPI_CLS_H1>(xh, xl, n, Wh, Wl, (long long)S * H, Ip, ga, st);
 }

@@ -373,3 +373,138 @@ SMI_API int smi_metric_classification_f32(const float* logits, const int32_t* y,
   SMI_LAUNCH_OK_N("cls_metrics_kernel", st);
   return SMI_OK;
 }
+
+// ---- predictive draws of the latents for any model (the guide half of MixtureGuidePredictive) ----
+// grid (ceil(L / 2048), S): latents[s][k] = T(loc_a[k] + softplus(rho_a[k]) eps), same key chain as
+// predictive_reg_kernel; every CTA of a draw walks the (short) chain itself.
+__global__ void __launch_bounds__(kThreads)
+predictive_latents_kernel(const SmiModelDesc md, const float* __restrict__ psi, int m, const uint32_t* __restrict__ key,
+                          int S, int32_t* __restrict__ assign, float* __restrict__ latents) {
+  __shared__ Key site_key[SMI_MAX_SITES];
+  __shared__ int s_a;
+  const int s = blockIdx.y, L = md.latent_dim, d = md.particle_dim;
+  const bool delta = md.guide == SMI_GUIDE_DELTA;
+  if (threadIdx.x == 0) {
+    const Key k0 = {key[0], key[1]};
+    const Key ka = split_at(k0, 0), kg = split_at(k0, 1);
+    s_a = delta ? s % m : (int)(((unsigned long long)bits_at(ka, (uint32_t)s) * (unsigned long long)m) >> 32);
+    Key kk = split_at(kg, (uint32_t)s);
+    for (int t = 0; t < md.n_sites; ++t) {
+      site_key[t] = split_at(kk, 1);
+      kk = split_at(kk, 0);
+    }
+    if (assign && blockIdx.x == 0) assign[s] = s_a;
+  }
+  __syncthreads();
+  const float* p = psi + (size_t)s_a * d;
+  const int k0 = blockIdx.x * 2048, k1 = min(L, k0 + 2048);
+  for (int k = k0 + threadIdx.x; k < k1; k += blockDim.x) {
+    int t = 0;
+    while (t + 1 < md.n_sites && k >= md.sites[t + 1].lat) ++t;
+    const SmiSite st = md.sites[t];
+    const int q = k - st.lat;
+    float u = p[st.loc + q];
+    if (!delta) u = fmaf(softplus_f(p[st.rho + q]), normal_from_bits(bits_at(site_key[t], (uint32_t)q)), u);
+    latents[(size_t)s * L + k] = st.transform == SMI_T_EXP ? expf(u) : u;
+  }
+}
+
+SMI_API int smi_predictive_latents_f32(const SmiModelDesc* md, const float* psi, int m, const uint32_t* key,
+                                       int num_samples, int32_t* assign, float* latents, void* stream) {
+  if (!md || !psi || !key || !latents) SMI_FAIL(SMI_EINVAL, "smi_predictive_latents_f32: null pointer");
+  if (m < 1 || num_samples < 1) SMI_FAIL(SMI_EINVAL, "smi_predictive_latents_f32: m=%d S=%d", m, num_samples);
+  dim3 grid((md->latent_dim + 2047) / 2048, num_samples);
+  SMI_PROF_BEGIN((cudaStream_t)stream);
+  predictive_latents_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(*md, psi, m, key, num_samples, assign, latents);
+  SMI_LAUNCH_OK_N("predictive_latents_kernel", (cudaStream_t)stream);
+  return SMI_OK;
+}
+
+// ---- classifier head: layers 2-3 and the Categorical draw, given h1 = act(x W1 + b1) ----------------
+// grid (row blocks, S), 256 threads: W2, b2, W3, b3 of the draw in smem, one warp per data row.
+//   logits[s][r][o] = b3 + act(h1 W2 + b2) W3;   y[s][r] = argmax_o (logits + Gumbel), the Gumbel noise
+//   -log(-log(u)), u = uniform(split(model key, S)[s], (n, O), minval = tiny)   (jax.random.categorical)
+template <int ACT>
+__global__ void __launch_bounds__(kThreads)
+cls_head_kernel(const float* __restrict__ Zl, long long L, int off_b2, int off_w2, int off_b3, int off_w3,
+                const float* __restrict__ H1, int n, int H, int O, const uint32_t* __restrict__ key, int S,
+                float* __restrict__ logits, int32_t* __restrict__ ydraw, int rows_per_block) {
+  extern __shared__ float sm[];
+  float* W2 = sm;                 // [H][H]
+  float* W3 = W2 + H * H;         // [H][O]
+  float* b2 = W3 + H * O;         // [H]
+  float* b3 = b2 + H;             // [O]
+  float* hb = b3 + ((O + 3) & ~3);  // [warps][2 H]
+  __shared__ Key noise_key;
+  const int s = blockIdx.y;
+  const float* z = Zl + (size_t)s * L;
+  for (int t = threadIdx.x; t < H * H; t += blockDim.x) W2[t] = z[off_w2 + t];
+  for (int t = threadIdx.x; t < H * O; t += blockDim.x) W3[t] = z[off_w3 + t];
+  for (int t = threadIdx.x; t < H; t += blockDim.x) b2[t] = z[off_b2 + t];
+  for (int t = threadIdx.x; t < O; t += blockDim.x) b3[t] = z[off_b3 + t];
+  if (threadIdx.x == 0) {
+    const Key k0 = {key[0], key[1]};
+    noise_key = split_at(split_at(k0, 2), (uint32_t)s);
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  float* h1 = hb + warp * 2 * H;
+  float* h2 = h1 + H;
+  const int r0 = blockIdx.x * rows_per_block, r1 = min(n, r0 + rows_per_block);
+  for (int r = r0 + warp; r < r1; r += nw) {
+    const float* hr = H1 + ((size_t)s * n + r) * H;
+    for (int j = lane; j < H; j += 32) h1[j] = hr[j];
+    __syncwarp();
+    for (int j = lane; j < H; j += 32) {
+      float a = b2[j];
+      for (int k = 0; k < H; ++k) a = fmaf(h1[k], W2[k * H + j], a);
+      h2[j] = act_f<ACT>(a);
+    }
+    __syncwarp();
+    float best = -INFINITY;
+    int arg = 0;
+    if (lane < O) {
+      float a = b3[lane];
+      for (int j = 0; j < H; ++j) a = fmaf(h2[j], W3[j * O + lane], a);
+      logits[((size_t)s * n + r) * O + lane] = a;
+      if (ydraw) {
+        const uint32_t bits = bits_at(noise_key, (uint32_t)(r * O + lane));
+        const float f = __uint_as_float((bits >> 9) | 0x3F800000u) - 1.0f;
+        const float u = fmaxf(1.17549435e-38f, f + 1.17549435e-38f);
+        best = a - logf(-logf(u));
+        arg = lane;
+      }
+    }
+    if (ydraw) {   // first maximum over the classes
+      for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+        if (ob > best || (ob == best && oa < arg)) best = ob, arg = oa;
+      }
+      if (lane == 0) ydraw[(size_t)s * n + r] = arg;
+    }
+    __syncwarp();
+  }
+}
+
+SMI_API int smi_predictive_cls_head_f32(const SmiModelDesc* md, const float* latents, const float* h1,
+                                        const uint32_t* key, int num_samples, int n, float* logits, int32_t* y_draw,
+                                        void* stream) {
+  if (!md || !latents || !h1 || !key || !logits) SMI_FAIL(SMI_EINVAL, "smi_predictive_cls_head_f32: null pointer");
+  if (md->kind != SMI_MODEL_BNN_CLS || md->n_sites != 6) SMI_FAIL(SMI_EINVAL, "smi_predictive_cls_head_f32: classifier BNN only");
+  const int H = md->hidden, O = md->out_dim;
+  if (O > 32) SMI_FAIL(SMI_ELIMIT, "smi_predictive_cls_head_f32: at most 32 classes");
+  const size_t smem = ((size_t)H * H + (size_t)H * O + H + ((O + 3) & ~3) + (size_t)(kThreads / 32) * 2 * H) * sizeof(float);
+  if (smem > 200 * 1024) SMI_FAIL(SMI_ELIMIT, "smi_predictive_cls_head_f32: hidden %d exceeds shared memory", H);
+  auto kern = md->act == SMI_ACT_RELU ? cls_head_kernel<SMI_ACT_RELU> : cls_head_kernel<SMI_ACT_TANH>;
+  if (smem > 48 * 1024) SMI_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int rows_per_block = 256;
+  dim3 grid((n + rows_per_block - 1) / rows_per_block, num_samples);
+  cudaStream_t st = (cudaStream_t)stream;
+  SMI_PROF_BEGIN(st);
+  kern<<<grid, kThreads, smem, st>>>(latents, (long long)md->latent_dim, md->sites[2].lat, md->sites[3].lat,
+                                     md->sites[4].lat, md->sites[5].lat, h1, n, H, O, key, num_samples, logits, y_draw,
+                                     rows_per_block);
+  SMI_LAUNCH_OK_N("cls_head_kernel", st);
+  return SMI_OK;
+}

@@ -20,8 +20,8 @@ class MixtureGuidePredictive:
     leading ``num_samples`` axis.  ``params`` is ``engine.get_params(state)`` (or the state)."""
 
     def __init__(self, model, guide, params, num_samples=1, return_sites=None, guide_sites=None, device=None):
-        if not isinstance(model, models.BNNRegression):
-            raise NotImplementedError("predictive draws are implemented for the regression BNN descriptors")
+        if not isinstance(model, (models.BNNRegression, models.BNNClassifier)):
+            raise NotImplementedError("predictive draws are implemented for the BNN descriptors")
         self.model, self.guide, self.num_samples = model, guide, int(num_samples)
         self.return_sites = list(return_sites) if return_sites is not None else None
         self.guide_sites = guide_sites
@@ -46,7 +46,41 @@ class MixtureGuidePredictive:
             psi[:, off:off + site.size] = v
         return psi
 
+    def _call_classifier(self, rng_key, x):
+        """logits (S, n, O) and the Categorical draw y (S, n): latents by threefry, first layer as one
+        stacked tcgen05 GEMM over all draws, layers 2-3 + Gumbel-argmax per draw."""
+        dev = self.device
+        x = torch.as_tensor(x)
+        x = x.to(dev).reshape(x.shape[0], -1).to(torch.float32).contiguous()
+        n, L, H, O = x.shape[0], self.layout.latent_dim, self.model.hidden, self.model.out_dim
+        S = self.psi.shape[0] if self.guide.kind == _lib.GUIDE_DELTA else self.num_samples
+        key = _key_tensor(rng_key, dev)
+        lat = torch.empty(S, L, device=dev)
+        assign = torch.empty(S, dtype=torch.int32, device=dev)
+        _lib.call("smi_predictive_latents_f32", C.byref(self.md), ops._ptr(self.psi), self.psi.shape[0],
+                  ops._ptr(key), S, ops._ptr(assign), ops._ptr(lat), ops._stream())
+        nbytes = _lib.load().smi_predictive_cls_layer1_workspace_bytes(C.byref(self.md), S, n)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        h1 = torch.empty(S, n, H, device=dev)
+        _lib.call("smi_predictive_cls_layer1_f32", C.byref(self.md), ops._ptr(lat), S, ops._ptr(x), n, ops._ptr(h1),
+                  ops._ptr(ws), ws.numel(), ops._stream())
+        logits = torch.empty(S, n, O, device=dev)
+        yd = torch.empty(S, n, dtype=torch.int32, device=dev)
+        _lib.call("smi_predictive_cls_head_f32", C.byref(self.md), ops._ptr(lat), ops._ptr(h1), ops._ptr(key), S, n,
+                  ops._ptr(logits), ops._ptr(yd), ops._stream())
+        res = {"logits": logits, "y": yd}
+        off = 0
+        for site in self.model.sites():
+            res[site.name] = lat[:, off:off + site.size].reshape((S,) + tuple(site.shape))
+            off += site.size
+        if self.return_sites is not None:
+            res = {k: v for k, v in res.items() if k in self.return_sites}
+        res["_assign"] = assign
+        return res
+
     def __call__(self, rng_key, x, y=None, subsample=None, **_ignored):
+        if isinstance(self.model, models.BNNClassifier):
+            return self._call_classifier(rng_key, x)
         dev = self.device
         x = torch.as_tensor(x, dtype=torch.float32).to(dev).reshape(len(x), -1).contiguous()
         n, S, L = x.shape[0], self.num_samples, self.layout.latent_dim

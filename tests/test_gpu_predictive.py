@@ -125,3 +125,46 @@ def test_classification_metrics_match_oracle(cuda, P, n, C, scale):
     # without the sampled y site: acc / conf undefined, the rest unchanged
     got2 = smi.classification_metrics({"logits": torch.from_numpy(logits).to(cuda)}, y)
     assert torch.isnan(got2["acc"]).all() and torch.equal(got2["ece"], got["ece"])
+
+
+@pytest.mark.parametrize("I,H,O,S,n,m", [(12, 8, 3, 5, 37, 3), (70, 20, 5, 4, 300, 2), (784, 100, 10, 3, 130, 2)])
+def test_classifier_predictive_matches_oracle(cuda, I, H, O, S, n, m):
+    """logits through the stacked tcgen05 first-layer GEMM + per-draw head; y by Gumbel-max.  Integer
+    outputs (assign, y) bit-exact wherever the winning margin exceeds the fp32 logit error."""
+    import smi_experiments_b200 as smi
+    model, spec = smi.mnist_mlp(I, H, O), om.mnist_mlp(I, H, O)
+    guide = smi.AutoNormal(model)
+    psi = _particles(smi, model, guide, m, 7)
+
+    class St:
+        class optim_state:
+            pass
+    St.optim_state.x = psi
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal((n, I)).astype(np.float32)
+    out = smi.MixtureGuidePredictive(model, guide, St, num_samples=S, return_sites=["logits", "y"])(smi.PRNGKey(9), x)
+    ref = op.predictive_cls(spec, psi.numpy().astype(np.float64), [0, 9], S, x.astype(np.float64))
+    assert np.array_equal(out["_assign"].cpu().numpy(), ref["assign"])
+    lg = out["logits"].cpu().numpy()
+    assert lg.shape == (S, n, O) and rel(lg, ref["logits"]) <= TOL
+    # Gumbel-max draw: recompute the float64 perturbed scores; rows whose top-2 margin is above 1e-4 must agree
+    yg = out["y"].cpu().numpy()
+    assert yg.shape == (S, n) and yg.dtype == np.int32
+    from oracle import prng as oprng
+    km = oprng.split(np.asarray([0, 9], np.uint32), 3)[2]
+    nk = oprng.split(km, S)
+    tiny = np.float32(1.17549435e-38)
+    for s in range(S):
+        f = oprng.bits_to_unit_float(oprng.random_bits(nk[s], n * O)).astype(np.float32)
+        g = -np.log(-np.log(np.maximum(tiny, f + tiny).astype(np.float64))).reshape(n, O)
+        sc = ref["logits"][s] + g
+        top2 = np.sort(sc, -1)[:, -2:]
+        clear = (top2[:, 1] - top2[:, 0]) > 1e-4
+        assert clear.mean() > 0.99
+        assert np.array_equal(yg[s][clear], ref["y"][s][clear])
+    # metrics straight from the predictive output
+    y_true = rng.integers(0, O, n).astype(np.int32)
+    met = smi.classification_metrics(out, y_true)
+    refm = op.classification_metrics(lg.astype(np.float64), y_true, yg)
+    for i, k in enumerate(("nll", "acc", "brier", "ece", "mce", "conf")):
+        assert np.all(np.abs(met[k].cpu().numpy() - refm[:, i]) <= 1e-5 * np.maximum(np.abs(refm[:, i]), 1e-2)), k

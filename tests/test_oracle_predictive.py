@@ -94,3 +94,22 @@ def test_binned_conf_acc_transcription_and_closed_form():
     logits = np.tile(np.array([[10.0, 0.0, 0.0]]), (20, 1))
     m = op.classification_metrics(logits[None], np.zeros(20, int), np.zeros((1, 20), int))
     assert abs(m[0, 1] - 1.0) < 1e-12 and m[0, 0] < 1e-3 and m[0, 2] < 1e-6
+
+
+def test_classifier_predictive_oracle_sanity():
+    spec = om.mnist_mlp(12, 8, 3)
+    rows, L, d = om.layout(spec, "normal")
+    rng = np.random.default_rng(1)
+    psi = rng.normal(size=(4, d)) * 0.3
+    for r in rows:
+        psi[:, r["rho"]:r["rho"] + r["size"]] = np.log(np.expm1(0.05))
+    x = rng.normal(size=(200, 12))
+    o = op.predictive_cls(spec, psi, [0, 3], 6, x)
+    assert o["logits"].shape == (6, 200, 3) and o["y"].shape == (6, 200) and o["y"].min() >= 0 and o["y"].max() <= 2
+    # the Gumbel-max draw follows softmax(logits): agreement with argmax well above chance, below 1
+    agree = (o["y"] == o["logits"].argmax(-1)).mean()
+    sm = np.exp(o["logits"] - o["logits"].max(-1, keepdims=True))
+    sm /= sm.sum(-1, keepdims=True)
+    assert abs(agree - sm.max(-1).mean()) < 0.06
+    o2 = op.predictive_cls(spec, psi, [0, 3], 6, x)
+    assert np.array_equal(o["y"], o2["y"]) and np.array_equal(o["logits"], o2["logits"])
