@@ -11,8 +11,10 @@
 // row-chunks for dW1 = x^T dh1.  fp32 FMA register tiles (4 x 4 per thread); every output is
 // written exactly once, in a fixed summation order.
 #include <math.h>
+#include <stdlib.h>
 
 #include "elbo.cuh"
+#include "mma_tiles.cuh"
 
 namespace {
 
@@ -291,6 +293,217 @@ bnn_cls_kernel(const float* __restrict__ Z, const float* __restrict__ x, const i
     LOGP[n] = (float)(-0.5 * lprior - 0.5 * (double)L * (double)kLog2Pi + (double)lik_scale * ll);
 }
 
+// ---------------------------------------------------------------------------------------
+// Per-draw part of the tensor-core path with the three H x H products on the warp-level 3xTF32
+// tiles of mma_tiles.cuh (same scheme as the regression kernel, elbo_bnn_mma.cu):
+//   h2  = act(h1 W2 + b2)           PT = h1^T [k][b],  Q = W2 [k][j]
+//   dW2 = h1^T dh2                  PT = h1   [b][k],  Q = dh2 [b][j]
+//   dh1 = (dh2 W2^T) act'(h1)       PT = dh2^T [j][b], Q = W2 [k][j] read as [output][reduction]
+// One copy of W2, h1 (-> dh1 in place), h2 (-> dh2 in place) and one transposed buffer (h1^T, then
+// dh2^T): 212 KB at 128 x 100.  The O-wide output layer stays on fp32 FMA.
+struct ClsMmaPlan {
+  int BR, HR, BP, HP, O1;
+  int W2s, h1s, hT, h2s, lg, total;
+  __host__ __device__ ClsMmaPlan(int B, int H, int O) {
+    BR = mma3::up8(B), HR = mma3::up8(H), BP = mma3::stride8(B), HP = mma3::stride8(H), O1 = O | 1;
+    int o = 0;
+    W2s = o, o += HR * HP;
+    h1s = o, o += BR * HP + 16;    // + slack: M tiles of dW2 read up to 15 columns past H
+    hT = o, o += HR * BP + 16;
+    h2s = o, o += BR * HP + 16;
+    lg = o, o += B * O1;
+    total = (o + 3) & ~3;
+  }
+};
+
+template <int ACT>
+__global__ void __launch_bounds__(kThreads, 1)
+bnn_cls_mid_mma_kernel(const float* __restrict__ Z, const int32_t* __restrict__ y, int L, int H, int O, int B,
+                       float lik_scale, ClsOffsets o, float* __restrict__ DZ, float* __restrict__ LOGP, ClsTcArgs tc) {
+  extern __shared__ __align__(16) float sm[];
+  const ClsMmaPlan pl(B, H, O);
+  const int BR = pl.BR, HR = pl.HR, BP = pl.BP, HP = pl.HP, O1 = pl.O1;
+  float* W2s = sm + pl.W2s;
+  float* h1s = sm + pl.h1s;
+  float* hT = sm + pl.hT;
+  float* h2s = sm + pl.h2s;
+  float* lg = sm + pl.lg;
+  __shared__ double red[32];
+  const int n = blockIdx.x;
+  const float* __restrict__ z = Z + (size_t)n * L;
+  float* __restrict__ dz = DZ + (size_t)n * L;
+  double lprior = 0.0;
+  auto emit_param = [&](int k, float g) {
+    const float t = z[k];
+    dz[k] = g - t;
+    lprior += (double)(t * t);
+  };
+  // reduction-side padding must be exact zeros
+  for (int t = threadIdx.x; t < pl.total / 4; t += blockDim.x)
+    reinterpret_cast<float4*>(sm)[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+  __syncthreads();
+  {
+    // one warp per row: coalesced global reads, conflict-free stores, no integer division
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    // one CTA per SM: the 91 KB of h1 and W2 arrive latency-bound unless every thread keeps several
+    // independent loads in flight (8 x float4 / 8 x float per trip)
+    const float4* hg4 = reinterpret_cast<const float4*>(tc.H1g + (size_t)n * B * H);   // H % 4 == 0: 16-byte rows
+    const int nq = (B * H) >> 2;
+    for (int base = 0; base < nq; base += 8 * (int)blockDim.x) {
+      float4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int q = base + u * (int)blockDim.x + (int)threadIdx.x;
+        v[u] = q < nq ? __ldcs(hg4 + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int q = base + u * (int)blockDim.x + (int)threadIdx.x;
+        if (q < nq) {
+          const int e = q << 2, b = e / H, k = e - b * H;
+          *reinterpret_cast<float4*>(h1s + b * HP + k) = v[u];
+        }
+      }
+    }
+    for (int base = 0; base < H * H; base += 8 * (int)blockDim.x) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int q = base + u * (int)blockDim.x + (int)threadIdx.x;
+        v[u] = q < H * H ? z[o.w2 + q] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int q = base + u * (int)blockDim.x + (int)threadIdx.x;
+        if (q < H * H) {
+          const int k = q / H;
+          W2s[k * HP + (q - k * H)] = v[u];
+        }
+      }
+    }
+    __syncthreads();
+    // h1^T through shared memory, a warp moving 8 k x 4 b per instruction: with both row pitches = 8
+    // mod 32 words the read is conflict-free and the store 2-way (a plain transpose is 8-way)
+    const int kl = lane & 7, bl = lane >> 3;
+    const int nkt = (H + 7) >> 3, nbt = (B + 3) >> 2;
+    for (int t = warp; t < nkt * nbt; t += nw) {
+      const int k = (t / nbt) * 8 + kl, b = (t % nbt) * 4 + bl;
+      if (k < H && b < B) hT[k * BP + b] = h1s[b * HP + k];
+    }
+  }
+  __syncthreads();
+  // ---- forward layer 2 ----
+  mma3::mma_gemm_bal<5>(B, H, HR, hT, BP, W2s, HP, [&](int b, int j, float v0, float v1) {
+    if (b >= B) return;
+    const float a0 = j < H ? act_f<ACT>(v0 + z[o.b2 + j]) : 0.f;
+    const float a1 = j + 1 < H ? act_f<ACT>(v1 + z[o.b2 + j + 1]) : 0.f;
+    *reinterpret_cast<float2*>(h2s + b * HP + j) = make_float2(a0, a1);
+  });
+  __syncthreads();
+  // ---- output layer, log-softmax, d logits ----
+  for (int t = threadIdx.x; t < B * O; t += blockDim.x) {
+    const int b = t / O, c = t - b * O;
+    float v4[4] = {z[o.b3 + c], 0.f, 0.f, 0.f};     // four independent chains: the loop is latency-bound
+    int j = 0;
+    for (; j + 4 <= H; j += 4) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v4[u] = fmaf(h2s[b * HP + j + u], z[o.w3 + (j + u) * O + c], v4[u]);
+    }
+    for (; j < H; ++j) v4[0] = fmaf(h2s[b * HP + j], z[o.w3 + j * O + c], v4[0]);
+    lg[b * O1 + c] = (v4[0] + v4[1]) + (v4[2] + v4[3]);
+  }
+  __syncthreads();
+  double ll = 0.0;
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    float mx = -INFINITY;
+    for (int c = 0; c < O; ++c) mx = fmaxf(mx, lg[b * O1 + c]);
+    float se = 0.f;
+    for (int c = 0; c < O; ++c) se += expf(lg[b * O1 + c] - mx);
+    const float lse = mx + logf(se);
+    const int yb = y[b];
+    ll += (double)(lg[b * O1 + yb] - lse);
+    for (int c = 0; c < O; ++c) {
+      const float p = expf(lg[b * O1 + c] - lse);
+      lg[b * O1 + c] = lik_scale * ((c == yb ? 1.f : 0.f) - p);
+    }
+  }
+  ll = block_sum(ll, red);  // barriers inside publish d logits
+  __syncthreads();
+  // ---- backward: output layer; dh2 in place and transposed (h1^T is dead) ----
+  for (int t = threadIdx.x; t < H * O; t += blockDim.x) {
+    const int j = t / O, c = t - j * O;
+    float g4[4] = {0.f, 0.f, 0.f, 0.f};
+    int b = 0;
+    for (; b + 4 <= B; b += 4) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) g4[u] = fmaf(h2s[(b + u) * HP + j], lg[(b + u) * O1 + c], g4[u]);
+    }
+    for (; b < B; ++b) g4[0] = fmaf(h2s[b * HP + j], lg[b * O1 + c], g4[0]);
+    emit_param(o.w3 + t, (g4[0] + g4[1]) + (g4[2] + g4[3]));
+  }
+  for (int c = threadIdx.x; c < O; c += blockDim.x) {
+    float g = 0.f;
+    for (int b = 0; b < B; ++b) g += lg[b * O1 + c];
+    emit_param(o.b3 + c, g);
+  }
+  __syncthreads();
+  {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    const int jl = lane & 7, bl = lane >> 3;       // 8 j x 4 b per warp: h2 access conflict-free, dh2^T store 2-way
+    const int njt = (H + 7) >> 3, nbt = (B + 3) >> 2;
+    for (int t = warp; t < njt * nbt; t += nw) {
+      const int j = (t / nbt) * 8 + jl, b = (t % nbt) * 4 + bl;
+      if (j < H && b < B) {
+        float g = 0.f;
+        for (int c = 0; c < O; ++c) g = fmaf(lg[b * O1 + c], z[o.w3 + j * O + c], g);
+        const float v = g * dact_from_out<ACT>(h2s[b * HP + j]);
+        h2s[b * HP + j] = v;
+        hT[j * BP + b] = v;
+      }
+    }
+  }
+  __syncthreads();
+  // ---- backward: layer 2 ----
+  mma3::mma_gemm_bal<5>(H, H, BR, h1s, HP, h2s, HP, [&](int k, int j, float v0, float v1) {
+    if (k >= H) return;
+    if (j < H) emit_param(o.w2 + k * H + j, v0);
+    if (j + 1 < H) emit_param(o.w2 + k * H + j + 1, v1);
+  });
+  for (int j = threadIdx.x; j < H; j += blockDim.x) {
+    float g = 0.f;
+    for (int b = 0; b < B; ++b) g += h2s[b * HP + j];
+    emit_param(o.b2 + j, g);
+  }
+  __syncthreads();
+  mma3::mma_gemm_bal<5, true>(B, H, HR, hT, BP, W2s, HP, [&](int b, int k, float v0, float v1) {
+    if (b >= B) return;
+    const float2 h = *reinterpret_cast<const float2*>(h1s + b * HP + k);
+    const float d0 = k < H ? v0 * dact_from_out<ACT>(h.x) : 0.f;
+    const float d1 = k + 1 < H ? v1 * dact_from_out<ACT>(h.y) : 0.f;
+    *reinterpret_cast<float2*>(h1s + b * HP + k) = make_float2(d0, d1);
+  });
+  __syncthreads();
+  // ---- layer 1: db1, dh1^T planes for the dW1 GEMM, prior of W1 ----
+  for (int j = threadIdx.x; j < H; j += blockDim.x) {
+    float g = 0.f;
+    for (int b = 0; b < B; ++b) g += h1s[b * HP + j];
+    emit_param(o.b1 + j, g);
+  }
+  for (int t = threadIdx.x; t < H * tc.Bp; t += blockDim.x) {
+    const int j = t / tc.Bp, b = t - j * tc.Bp;
+    const float v = b < B ? h1s[b * HP + j] : 0.f;
+    const float hi = __uint_as_float(__float_as_uint(v) & 0xFFFFE000u);
+    const size_t e = ((size_t)n * H + j) * tc.Bp + b;
+    tc.dHh[e] = hi;
+    tc.dHl[e] = v - hi;
+  }
+  if (threadIdx.x == 0)
+    for (int it = 0; it < tc.nit; ++it) lprior += tc.w1sq[(size_t)n * tc.nit + it];
+  lprior = block_sum(lprior, red);
+  if (threadIdx.x == 0)
+    LOGP[n] = (float)(-0.5 * lprior - 0.5 * (double)L * (double)kLog2Pi + (double)lik_scale * ll);
+}
+
 size_t cls_smem_bytes(int H, int O, int B, bool tc = false) {
   const int H1 = H | 1, O1 = O | 1, HP = (H + 3) & ~3;
   const size_t last = tc ? (size_t)H * H1 : (size_t)B * (KC + 1);
@@ -320,6 +533,19 @@ int smi_cls_mid_launch(const SmiModelDesc& md, const ClsTcWs& c, const float* Z,
   const int HP = (H + 3) & ~3;
   if (((B + 3) / 4) * (HP / 4) > kSlots * kThreads)
     SMI_FAIL(SMI_ELIMIT, "bnn_cls: batch %d x hidden %d exceeds the register tiling", B, H);
+  ClsTcArgs tcm{c.H1, c.dHh, c.dHl, c.w1sq, c.Bp, c.nit};
+  {  // warp-level tensor-core tiles when one draw fits in shared memory (SMI_CLS_MID_FMA=1: the FMA kernel)
+    static const bool use_fma = getenv("SMI_CLS_MID_FMA") != nullptr;
+    const size_t msm = (size_t)ClsMmaPlan(B, H, O).total * sizeof(float);
+    if (!use_fma && msm <= 224 * 1024) {
+      auto km = md.act == SMI_ACT_RELU ? bnn_cls_mid_mma_kernel<SMI_ACT_RELU> : bnn_cls_mid_mma_kernel<SMI_ACT_TANH>;
+      SMI_CUDA_OK(cudaFuncSetAttribute(km, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msm));
+      SMI_PROF_BEGIN(st);
+      km<<<ndraws, kThreads, msm, st>>>(Z, y, L, H, O, B, lik_scale, o, DZ, LOGP, tcm);
+      SMI_LAUNCH_OK_N("bnn_cls_mid_mma_kernel", st);
+      return SMI_OK;
+    }
+  }
   const size_t smem = cls_smem_bytes(H, O, B, true);
   if (smem > 220 * 1024) SMI_FAIL(SMI_ELIMIT, "bnn_cls: activations need %zu B of shared memory", smem);
   ClsTcArgs tc{c.H1, c.dHh, c.dHl, c.w1sq, c.Bp, c.nit};
