@@ -289,18 +289,33 @@ guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, 
     }
     const float mu_i = MU[(size_t)i * L + k], sg_i = SIG[(size_t)i * L + k], is_i = ISIG[(size_t)i * L + k];
     const float jac = tr_of[k] == SMI_T_EXP ? 1.f : 0.f;
-#pragma unroll 4
-    for (int s = sg; s < S; s += kGradSG) {
-      const size_t e = ((size_t)r * S + s) * L + k;
-      const float ep = __ldg(eps + e);
-      const float z = fmaf(sg_i, ep, mu_i);
-      float T = 0.f;
+    // batches of 8 draws: the 16 global loads are issued before any of them is consumed (the kernel
+    // is HBM-latency bound: ncu long-scoreboard stall 7 per issue with the loads left to the compiler)
+    constexpr int kBatch = 8;
+    for (int s0 = sg; s0 < S; s0 += kGradSG * kBatch) {
+      float epv[kBatch], dzv[kBatch];
 #pragma unroll
-      for (int j = 0; j < MP; ++j) T = fmaf(wt[s * MP + j] * (z - mu[j]), q[j], T);
-      const float du = fmaf(tau, __ldg(DZ + e), T) + jac;
-      const float wi = wt[s * MP + i];
-      gl += du - wi * ep * is_i;
-      gs += du * ep - wi * (ep * ep - 1.f) * is_i;
+      for (int u = 0; u < kBatch; ++u) {
+        const int s = s0 + u * kGradSG;
+        const size_t e = ((size_t)r * S + min(s, S - 1)) * L + k;
+        epv[u] = __ldcs(eps + e);
+        dzv[u] = __ldcs(DZ + e);
+      }
+#pragma unroll
+      for (int u = 0; u < kBatch; ++u) {
+        const int s = s0 + u * kGradSG;
+        if (s < S) {
+          const float ep = epv[u];
+          const float z = fmaf(sg_i, ep, mu_i);
+          float T = 0.f;
+#pragma unroll
+          for (int j = 0; j < MP; ++j) T = fmaf(wt[s * MP + j] * (z - mu[j]), q[j], T);
+          const float du = fmaf(tau, dzv[u], T) + jac;
+          const float wi = wt[s * MP + i];
+          gl += du - wi * ep * is_i;
+          gs += du * ep - wi * (ep * ep - 1.f) * is_i;
+        }
+      }
     }
   }
   part[(sg * kGradKT + kk) * 2] = gl;
