@@ -20,6 +20,7 @@
 // and each activation is kept in two layouts ([b][j] and [j][b]) because it is an output-side
 // operand of one product and a reduction-side operand of another.
 #include <math.h>
+#include <stdlib.h>
 
 #include "elbo.cuh"
 #include "mma_tiles.cuh"
@@ -289,6 +290,242 @@ bnn_reg_mma_kernel(const float* __restrict__ Z, const int32_t* __restrict__ idx,
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// Single-copy variant: every operand lives in shared memory once ([b][i] / [k][j] / [b][j]); the
+// products in which it is the transposed operand read it through the [output][reduction]
+// fragment gathers of mma_tiles.cuh (2-way bank conflicts).  74 KB per draw instead of 113 KB:
+// three 8-warp CTAs per SM instead of two 12-warp ones.  Measured on B200: a lone CTA of the kernel
+// above takes 25 us, two per SM 34 us -- each CTA is latency-bound (barrier-separated phases), so the
+// number of co-resident draws, not the MMA pipe, sets the throughput.
+constexpr int kThreads3 = 256;
+
+struct Mma3Plan {
+  int BR, HR, IR, HP, IP;
+  int xs, hA, hB, W2p, W1p, b1, b2, w3, yb, dout, total;
+  __host__ __device__ Mma3Plan(int B, int I, int H) {
+    BR = up8(B), HR = up8(H), IR = up8(I + 1);
+    HP = stride8(H + 1), IP = stride8(I + 1);
+    int o = 0;
+    // order: an M tile of a transposed-A product may read up to 8 rows past BR -> into the next buffer
+    xs = o, o += BR * IP;         // x[b][i], column I = 1
+    hA = o, o += BR * HP;         // h1[b][k] (column H = 1), later dh1
+    hB = o, o += BR * HP;         // h2[b][j], then dh2 in place
+    W2p = o, o += HR * HP;        // W2[k][j]
+    W1p = o, o += IR * HP;        // W1[i][j]
+    b1 = o, o += HP;
+    b2 = o, o += HP;
+    w3 = o, o += HP;
+    yb = o, o += BR;
+    dout = o, o += BR;
+    total = (o + 3) & ~3;
+  }
+};
+
+template <int ACT>
+__global__ void __launch_bounds__(kThreads3, 3)
+bnn_reg_mma3_kernel(const float* __restrict__ Z, const int32_t* __restrict__ idx, const float* __restrict__ x,
+                    const float* __restrict__ y, int L, int I, int H, int B, int noise, float sigma,
+                    float lik_scale, MmaOffsets o, float* __restrict__ DZ, float* __restrict__ LOGP) {
+  extern __shared__ __align__(16) float sm[];
+  const Mma3Plan pl(B, I, H);
+  const int HP = pl.HP, IP = pl.IP, BR = pl.BR, HR = pl.HR, IR = pl.IR;
+  float* xs = sm + pl.xs;
+  float* hA = sm + pl.hA;
+  float* hB = sm + pl.hB;
+  float* W2p = sm + pl.W2p;
+  float* W1p = sm + pl.W1p;
+  float* b1 = sm + pl.b1;
+  float* b2 = sm + pl.b2;
+  float* w3 = sm + pl.w3;
+  float* yb = sm + pl.yb;
+  float* dout = sm + pl.dout;
+  __shared__ double red[32];
+  __shared__ float s_prec_grad;
+  const int n = blockIdx.x;
+  const float* __restrict__ z = Z + (size_t)n * L;
+  float* __restrict__ dz = DZ + (size_t)n * L;
+  const bool gamma = noise == SMI_NOISE_GAMMA_PREC;
+
+  for (int t = threadIdx.x; t < pl.total / 4; t += blockDim.x)
+    reinterpret_cast<float4*>(sm)[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+  __syncthreads();
+
+  // ---- stage the draw ----
+  double lprior = 0.0;
+  {
+    const int ntj = (H + 3) >> 2, nti = (I + 3) >> 2, ntk = (H + 3) >> 2;
+    for (int t = threadIdx.x; t < nti * ntj + ntk * ntj; t += blockDim.x) {
+      const bool second = t >= nti * ntj;
+      const int tt = second ? t - nti * ntj : t;
+      const int r0 = (tt / ntj) << 2, j0 = (tt % ntj) << 2;
+      const int rows = second ? H : I;
+      const float* src = z + (second ? o.w2 : o.w1);
+      float v[4][4], ss = 0.f;
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          v[a][c] = (r0 + a < rows && j0 + c < H) ? src[(r0 + a) * H + j0 + c] : 0.f;
+          ss = fmaf(v[a][c], v[a][c], ss);
+        }
+      lprior += (double)ss;
+      float* dst = second ? W2p : W1p;
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+        if (r0 + a < rows) *reinterpret_cast<float4*>(dst + (r0 + a) * HP + j0) = make_float4(v[a][0], v[a][1], v[a][2], v[a][3]);
+    }
+  }
+  for (int j = threadIdx.x; j < H; j += blockDim.x) {
+    const float v1 = z[o.b1 + j], v2 = z[o.b2 + j], v3 = z[o.w3 + j];
+    lprior += (double)(v1 * v1) + (double)(v2 * v2) + (double)(v3 * v3);
+    b1[j] = v1, b2[j] = v2, w3[j] = v3;
+  }
+  {
+    const int nci = IP >> 2;
+    for (int t = threadIdx.x; t < B * nci; t += blockDim.x) {
+      const int b = t / nci, i0 = (t - b * nci) << 2;
+      const int row = idx ? idx[(size_t)n * B + b] : b;
+      float v[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int i = i0 + c;
+        v[c] = i < I ? __ldg(x + (size_t)row * I + i) : (i == I ? 1.f : 0.f);   // column I: ones (bias gradient)
+      }
+      *reinterpret_cast<float4*>(xs + b * IP + i0) = make_float4(v[0], v[1], v[2], v[3]);
+      if (i0 == 0) yb[b] = y[row];
+    }
+  }
+  const float b3 = z[o.b3];
+  const float prec = gamma ? expf(z[o.prec]) : 1.f / (sigma * sigma);
+  __syncthreads();
+
+  // ---- forward 1: h1 = act(x W1 + b1) -> hA [b][j] (column H = 1);  A = x read as [m][r] ----
+  mma_gemm_bal<5, false, true>(B, H + 1, IR, xs, IP, W1p, HP, [&](int b, int j, float v0, float v1) {
+    if (b >= BR) return;
+    const bool live = b < B;
+    const float h0 = live ? (j < H ? act_f<ACT>(v0 + b1[j]) : (j == H ? 1.f : 0.f)) : 0.f;
+    const float h1v = live ? (j + 1 < H ? act_f<ACT>(v1 + b1[j + 1]) : (j + 1 == H ? 1.f : 0.f)) : 0.f;
+    *reinterpret_cast<float2*>(hA + b * HP + j) = make_float2(h0, h1v);
+  });
+  __syncthreads();
+  // ---- forward 2: h2 = act(h1 W2 + b2) -> hB [b][j];  A = h1 read as [m][r] ----
+  mma_gemm_bal<5, false, true>(B, H, HR, hA, HP, W2p, HP, [&](int b, int j, float v0, float v1) {
+    if (b >= BR) return;
+    const bool live = b < B;
+    const float h0 = (live && j < H) ? act_f<ACT>(v0 + b2[j]) : 0.f;
+    const float h1v = (live && j + 1 < H) ? act_f<ACT>(v1 + b2[j + 1]) : 0.f;
+    *reinterpret_cast<float2*>(hB + b * HP + j) = make_float2(h0, h1v);
+  });
+  __syncthreads();
+  // ---- output layer: four lanes per row, residuals ----
+  double ll = 0.0;
+  {
+    const int q = threadIdx.x & 3;
+    for (int b = threadIdx.x >> 2; b < BR; b += blockDim.x >> 2) {   // BR: keeps the quad shuffles convergent
+      float out = 0.f;
+      if (b < B) {
+        const float4* hr = reinterpret_cast<const float4*>(hB + b * HP);
+        const float4* wr = reinterpret_cast<const float4*>(w3);
+        for (int c = q; c < (HP >> 2); c += 4) {   // padded columns of w3 are zero
+          const float4 h4 = hr[c], w4 = wr[c];
+          out = fmaf(h4.x, w4.x, out);
+          out = fmaf(h4.y, w4.y, out);
+          out = fmaf(h4.z, w4.z, out);
+          out = fmaf(h4.w, w4.w, out);
+        }
+      }
+      out += __shfl_xor_sync(0xffffffffu, out, 1);
+      out += __shfl_xor_sync(0xffffffffu, out, 2);
+      if (q == 0 && b < B) {
+        out += b3;
+        const float r = yb[b] - out;
+        dout[b] = lik_scale * prec * r;
+        ll += (double)(-0.5f * prec * r * r);
+        yb[b] = r;  // keep the residual for d/d prec
+      }
+    }
+  }
+  ll = block_sum(ll, red);  // (its barriers publish dout / yb)
+  double lp_const = 0.0;
+  if (threadIdx.x == 0) lp_const = (double)B * (0.5 * (double)logf(prec) - 0.5 * (double)kLog2Pi);
+  __syncthreads();
+  // ---- backward: output layer ----
+  for (int j = threadIdx.x; j < H; j += blockDim.x) {
+    float g = 0.f;
+    for (int b = 0; b < B; ++b) g = fmaf(dout[b], hB[b * HP + j], g);
+    dz[o.w3 + j] = g - w3[j];
+  }
+  if (threadIdx.x == blockDim.x - 1) {
+    float g = 0.f;
+    for (int b = 0; b < B; ++b) g += dout[b];
+    dz[o.b3] = g - b3;
+    if (gamma) {
+      float gp = 0.f;
+      for (int b = 0; b < B; ++b) gp += -0.5f * yb[b] * yb[b] + 0.5f / prec;
+      s_prec_grad = lik_scale * gp;
+    }
+  }
+  __syncthreads();
+  // dh2 = dout w3 act'(h2), in place (hB); lanes along j
+  for (int t = threadIdx.x; t < BR * (HP >> 2); t += blockDim.x) {
+    const int b = t / (HP >> 2), j0 = (t - b * (HP >> 2)) << 2;
+    const float4 w4 = *reinterpret_cast<const float4*>(w3 + j0);
+    const float4 h4 = *reinterpret_cast<const float4*>(hB + b * HP + j0);
+    const float dv = dout[b];   // 0 for padded rows
+    const float wv[4] = {w4.x, w4.y, w4.z, w4.w}, hv[4] = {h4.x, h4.y, h4.z, h4.w};
+    float v[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) v[c] = (j0 + c < H) ? dv * wv[c] * dact_from_out<ACT>(hv[c]) : 0.f;
+    *reinterpret_cast<float4*>(hB + b * HP + j0) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+  __syncthreads();
+  // ---- layer 2: [dW2; db2] = [h1, 1]^T dh2 ----
+  mma_gemm_bal<4>(H + 1, H, BR, hA, HP, hB, HP, [&](int k, int j, float v0, float v1) {
+    if (k > H) return;
+    if (j < H) {
+      if (k < H) dz[o.w2 + k * H + j] = v0 - W2p[k * HP + j];
+      else dz[o.b2 + j] = v0 - b2[j];
+    }
+    if (j + 1 < H) {
+      if (k < H) dz[o.w2 + k * H + j + 1] = v1 - W2p[k * HP + j + 1];
+      else dz[o.b2 + j + 1] = v1 - b2[j + 1];
+    }
+  });
+  __syncthreads();
+  // ---- dh1 = (dh2 W2^T) act'(h1), over h1;  A = dh2 read as [m][r], B = W2 read as [n][r] ----
+  mma_gemm_bal<5, true, true>(B, H, HR, hB, HP, W2p, HP, [&](int b, int k, float v0, float v1) {
+    if (b >= BR) return;
+    const float2 h = *reinterpret_cast<const float2*>(hA + b * HP + k);
+    const bool live = b < B;
+    const float d0 = (live && k < H) ? v0 * dact_from_out<ACT>(h.x) : 0.f;
+    const float d1 = (live && k + 1 < H) ? v1 * dact_from_out<ACT>(h.y) : 0.f;
+    *reinterpret_cast<float2*>(hA + b * HP + k) = make_float2(d0, d1);
+  });
+  __syncthreads();
+  // ---- layer 1: [dW1; db1] = [x, 1]^T dh1 ----
+  mma_gemm<1>(I + 1, H, BR, xs, IP, hA, HP, [&](int i, int j, float v0, float v1) {
+    if (i > I) return;
+    if (j < H) {
+      if (i < I) dz[o.w1 + i * H + j] = v0 - W1p[i * HP + j];
+      else dz[o.b1 + j] = v0 - b1[j];
+    }
+    if (j + 1 < H) {
+      if (i < I) dz[o.w1 + i * H + j + 1] = v1 - W1p[i * HP + j + 1];
+      else dz[o.b1 + j + 1] = v1 - b1[j + 1];
+    }
+  });
+  // ---- priors, precision site, log p ----
+  lprior = block_sum(lprior, red);
+  if (threadIdx.x == 0) {
+    double lp = -0.5 * lprior - 0.5 * (double)(L - (gamma ? 1 : 0)) * (double)kLog2Pi - 0.5 * (double)(b3 * b3);
+    if (gamma) {
+      lp += (double)(logf(0.1f) - 0.1f * prec);           // Gamma(1, rate 0.1)
+      dz[o.prec] = (s_prec_grad - 0.1f) * prec;           // d theta / d u = theta
+    }
+    LOGP[n] = (float)(lp + (double)lik_scale * (ll + lp_const));
+  }
+}
+
 }  // namespace
 
 size_t smi_bnn_reg_mma_smem_bytes(int I, int H, int B) { return (size_t)MmaPlan(B, I, H).total * sizeof(float); }
@@ -298,6 +535,20 @@ int smi_bnn_reg_mma_launch(const SmiModelDesc& md, const float* Z, const int32_t
                            int ndraws, int B, float lik_scale, const int* off7, float* DZ, float* LOGP,
                            cudaStream_t st) {
   const int I = md.in_dim, H = md.hidden, L = md.latent_dim;
+  {  // single-copy variant: three CTAs per SM when a draw fits in a third of the shared memory
+    static const bool two = getenv("SMI_BNN_MMA2") != nullptr;   // comparison runs against the two-copy kernel
+    const size_t smem3 = (size_t)Mma3Plan(B, I, H).total * sizeof(float);
+    if (!two && smem3 <= 75 * 1024) {
+      MmaOffsets o3;
+      o3.prec = off7[0], o3.w1 = off7[1], o3.b1 = off7[2], o3.w2 = off7[3], o3.b2 = off7[4], o3.w3 = off7[5], o3.b3 = off7[6];
+      auto k3 = md.act == SMI_ACT_RELU ? bnn_reg_mma3_kernel<SMI_ACT_RELU> : bnn_reg_mma3_kernel<SMI_ACT_TANH>;
+      SMI_CUDA_OK(cudaFuncSetAttribute(k3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
+      SMI_PROF_BEGIN(st);
+      k3<<<ndraws, kThreads3, smem3, st>>>(Z, idx, x, y, L, I, H, B, md.noise, md.sigma, lik_scale, o3, DZ, LOGP);
+      SMI_LAUNCH_OK_N("bnn_reg_mma_kernel", st);
+      return SMI_OK;
+    }
+  }
   const size_t smem = smi_bnn_reg_mma_smem_bytes(I, H, B);
   if (smem > 220 * 1024) SMI_FAIL(SMI_ELIMIT, "bnn_reg: network + minibatch need %zu B of shared memory", smem);
   MmaOffsets o;

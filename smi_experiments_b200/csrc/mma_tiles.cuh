@@ -126,22 +126,24 @@ __device__ __forceinline__ void mma_gemm(int M, int N, int R8, const float* __re
 // BMR = true: Q is stored [output n][reduction r] instead (the same buffer then serves a product in
 // which it is the transposed operand, e.g. dh1 = dh2 W2^T with W2 kept as [k][j]); its fragment
 // gather is 2-way bank conflicted with the stride8 row pitch.
-template <int NTMAX, bool BMR = false>
+// AMR = true: likewise PT is stored [output m][reduction r].
+template <int NTMAX, bool BMR = false, bool AMR = false>
 __device__ __forceinline__ void mma_unit_rt(float (&acc)[NTMAX][4], int nv, int R8, const float* __restrict__ PT,
                                             int ps, int m0, const float* __restrict__ Q, int qs, int n0) {
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-  const float* pa = PT + t * ps + m0 + g;
+  const float* pa = AMR ? PT + (m0 + g) * ps + t : PT + t * ps + m0 + g;
+  const int a8 = AMR ? 8 * ps : 8, a4 = AMR ? 4 : 4 * ps, astep = AMR ? 8 : 8 * ps;
   const float* pb = BMR ? Q + (n0 + g) * qs + t : Q + t * qs + n0 + g;
-  const int ps4 = 4 * ps, qs4 = BMR ? 4 : 4 * qs;
+  const int qs4 = BMR ? 4 : 4 * qs;
   const int nstep = BMR ? 8 * qs : 8;      // next 8-column tile
   const int kstep = BMR ? 8 : 8 * qs;      // next K step
 #pragma unroll 2
   for (int k0 = 0; k0 < R8; k0 += 8) {
     uint32_t ah[4], al[4];
     split_tf32(pa[0], ah[0], al[0]);
-    split_tf32(pa[8], ah[1], al[1]);
-    split_tf32(pa[ps4], ah[2], al[2]);
-    split_tf32(pa[ps4 + 8], ah[3], al[3]);
+    split_tf32(pa[a8], ah[1], al[1]);
+    split_tf32(pa[a4], ah[2], al[2]);
+    split_tf32(pa[a4 + a8], ah[3], al[3]);
 #pragma unroll
     for (int u = 0; u < NTMAX; ++u) {
       if (u < nv) {
@@ -153,7 +155,7 @@ __device__ __forceinline__ void mma_unit_rt(float (&acc)[NTMAX][4], int nv, int 
         mma_tf32(acc[u], ah, bh);
       }
     }
-    pa += 8 * ps;
+    pa += astep;
     pb += kstep;
   }
 }
@@ -161,7 +163,7 @@ __device__ __forceinline__ void mma_unit_rt(float (&acc)[NTMAX][4], int nv, int 
 // Whole product with the (16-row, 8-column) output tiles dealt evenly to the warps: warp w owns
 // tiles [w P / kWarps, (w + 1) P / kWarps) in row-major tile order, cut at tile-row boundaries
 // (7 x 7 tiles over 12 warps: 4 or 5 tiles each instead of 8 for the slowest warp).
-template <int NTMAX, bool BMR = false, typename Emit>
+template <int NTMAX, bool BMR = false, bool AMR = false, typename Emit>
 __device__ __forceinline__ void mma_gemm_bal(int M, int N, int R8, const float* __restrict__ PT, int ps,
                                              const float* __restrict__ Q, int qs, Emit emit) {
   const int ntm = (M + 15) >> 4, ntn = (N + 7) >> 3, P = ntm * ntn;
@@ -176,7 +178,7 @@ __device__ __forceinline__ void mma_gemm_bal(int M, int N, int R8, const float* 
     float acc[NTMAX][4];
 #pragma unroll
     for (int a = 0; a < NTMAX; ++a) acc[a][0] = acc[a][1] = acc[a][2] = acc[a][3] = 0.f;
-    mma_unit_rt<NTMAX, BMR>(acc, nv, R8, PT, ps, m0, Q, qs, n0);
+    mma_unit_rt<NTMAX, BMR, AMR>(acc, nv, R8, PT, ps, m0, Q, qs, n0);
 #pragma unroll
     for (int a = 0; a < NTMAX; ++a) {
       if (a < nv) {
