@@ -38,7 +38,8 @@ def _compile(src, force, verbose):
     if (not force and os.path.exists(obj)
             and os.path.getmtime(obj) > max(os.path.getmtime(sp), _newest_header())):
         return obj, ""
-    cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", sp, "-o", obj]
+    extra = os.environ.get("SMI_NVCC_EXTRA", "").split()   # e.g. -DSMI_STEIN_TRACE for the phase trace
+    cmd = [NVCC] + FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", sp, "-o", obj]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed for %s:\n%s\n%s" % (src, r.stdout, r.stderr))

@@ -10,10 +10,14 @@
 //               reference's kernel does), row sums
 //   3. force  : F = c_att K G + c (rowsum(K) * X - K X), c = 2 alpha/(h m); |F|_F
 // HBM traffic: X is read twice and G once, F written once: 16 m d bytes.
+#include <cooperative_groups.h>
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "stein_small.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -253,6 +257,359 @@ stein_small_force(const float* __restrict__ X, const float* __restrict__ G, int 
   }
 }
 
+
+// ---------------------------------------------------------------------------------------
+// One-launch variant for particle sets that fit the shared memory of one thread-block cluster
+// (2 m d floats over CS CTAs: every SMI config of the reference's regression experiments).  CTA r
+// of the cluster keeps its column chunk of X (and of G) in shared memory for the whole kernel:
+//   pairs   : per-CTA partial |x_i - x_j|^2 in double, published in its own shared memory
+//   cluster.sync; every CTA sums the CS partials through DSMEM in rank order (so all CTAs hold the
+//   same bits), finds the median by rank counting (bitonic sort above 1024 distances), K, row sums
+//   force   : from the resident chunk; per-CTA |F|^2 partial -> cluster.sync -> CTA 0 writes the loss
+// X and G are read from HBM once, F written once (12 m d bytes); the three launches, their
+// workspace round trips and two kernel boundaries (~ 40 us at C2) collapse into ~ 10 us.
+struct FusedArgs {
+  const float* X;
+  const float* G;
+  int m, d, dcp, nsplit;
+  float c_att, alpha;
+  int rank_lo, rank_hi;
+  float factor, h_fixed;
+  float* F;
+  float* loss;
+  float* h_out;
+};
+
+constexpr int kFusedThreads = 1024;
+// words of the count / sort scratch for np pair values
+__host__ __device__ inline int fused_cnt_words(int np) {
+  const int np4 = (np + 3) & ~3;
+  if (np < 1) return 0;
+  const int nsl = np <= 512 ? max(1, min(8, kFusedThreads / np)) : 1;
+  return max(2 * np4, nsl * np4);
+}
+
+#ifdef SMI_STEIN_TRACE
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define TR(i) do { if (threadIdx.x == 0) tr[i] = gtimer(); } while (0)
+#else
+#define TR(i) do { } while (0)
+#endif
+
+__global__ void __launch_bounds__(kFusedThreads, 1) stein_cluster_kernel(FusedArgs a) {
+  cg::cluster_group cluster = cg::this_cluster();
+  const int CS = (int)cluster.num_blocks(), rk = (int)cluster.block_rank();
+  extern __shared__ __align__(16) unsigned char smraw[];
+  const int m = a.m, d = a.d, dcp = a.dcp;
+  const int np = m * (m - 1) / 2, np4 = (np + 3) & ~3, mp4 = (m + 3) & ~3;
+  const int nb = mp4 >> 2, nbp = nb * (nb + 1) / 2;
+  double* lossp = reinterpret_cast<double*>(smraw);           // [CS]   (CTA 0's copy is the one read)
+  float* xs = reinterpret_cast<float*>(lossp + ((CS + 1) & ~1));   // [m][dcp], 16-byte aligned
+  float* ys = xs + (size_t)m * dcp;                           // [m][dcp]
+  float* pall = ys + (size_t)m * dcp;                         // [CS][np4]: slot r written by CTA r
+  float* pv = pall + (size_t)CS * np4;                        // [np4] pair distances, +inf padded
+  float* sq = pv + np4;                                       // [np4] squared pair distances
+  float* kt = sq + np4;                                       // [m][mp4] kernel matrix, zero padded
+  float* rs = kt + (size_t)m * mp4;                           // [mp4]
+  float* psp = rs + mp4;                                      // [nsplit][nbp][16] column-split partials
+  int* cnt = reinterpret_cast<int*>(psp + (size_t)a.nsplit * nbp * 16);   // count slices / sort scratch
+  unsigned char* pi = reinterpret_cast<unsigned char*>(cnt + fused_cnt_words(np));    // [np] row of pair p
+  unsigned char* pj = pi + np4;                                           // [np] column of pair p
+  __shared__ double red[32];
+  __shared__ float s_med[2];
+  const int k0 = rk * dcp;
+  const int len = max(0, min(dcp, d - k0));
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, nw = blockDim.x >> 5;
+#ifdef SMI_STEIN_TRACE
+  __shared__ unsigned long long tr[12];
+#endif
+  TR(0);
+  // every CTA of the cluster must be running before its shared memory is written remotely: arrive
+  // now, wait just before the first remote store (split-phase, so the wait is free by then)
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+
+  // ---- stage the chunk (rows zero-padded up to dcp), all loads of a batch in flight together ----
+  if ((d & 1) == 0) {
+    const int h2 = dcp >> 1, n2 = m * h2;
+    for (int t0 = tid; t0 < n2; t0 += 4 * blockDim.x) {
+      float2 xv[4], gv[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int t = t0 + u * blockDim.x;
+        xv[u] = gv[u] = make_float2(0.f, 0.f);
+        if (t < n2) {
+          const int i = t / h2, k = (t - i * h2) * 2;
+          if (k < len) {
+            const size_t e = (size_t)i * d + k0 + k;
+            xv[u] = __ldg(reinterpret_cast<const float2*>(a.X + e));
+            gv[u] = __ldg(reinterpret_cast<const float2*>(a.G + e));
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int t = t0 + u * blockDim.x;
+        if (t < n2) {
+          reinterpret_cast<float2*>(xs)[t] = xv[u];
+          reinterpret_cast<float2*>(ys)[t] = gv[u];
+        }
+      }
+    }
+  } else {
+#pragma unroll 4
+    for (int t = tid; t < m * dcp; t += blockDim.x) {
+      const int i = t / dcp, k = t - i * dcp;
+      const size_t e = (size_t)i * d + k0 + k;
+      xs[t] = k < len ? __ldg(a.X + e) : 0.f;
+      ys[t] = k < len ? __ldg(a.G + e) : 0.f;
+    }
+  }
+  for (int i = tid; i < m; i += blockDim.x) {   // pair p of row i starts at i (m - 1) - i (i - 1) / 2
+    const int base = i * (m - 1) - (i * (i - 1)) / 2;
+    for (int j = i + 1; j < m; ++j) {
+      pi[base + j - i - 1] = (unsigned char)i;
+      pj[base + j - i - 1] = (unsigned char)j;
+    }
+  }
+  if (tid < 2) s_med[tid] = 0.f;
+  __syncthreads();
+  TR(1);
+  // ---- squared differences: warp = (4 x 4 block of particle pairs, column split); every row of
+  //      the block is read once per 16 pairs (shared-memory bandwidth bound the one-pair-per-warp form)
+  {
+    const int nsplit = a.nsplit;
+    const int cper = (((dcp + nsplit - 1) / nsplit) + 31) & ~31;
+    for (int item = w; item < nbp * nsplit; item += nw) {
+      const int bp = item % nbp, sp = item / nbp;
+      int bi = 0, rem = bp;
+      while (rem >= nb - bi) {
+        rem -= nb - bi;
+        ++bi;
+      }
+      const int bj = bi + rem;
+      const float* xi[4];
+      const float* xj[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        xi[u] = xs + min(4 * bi + u, m - 1) * dcp;
+        xj[u] = xs + min(4 * bj + u, m - 1) * dcp;
+      }
+      float acc[4][4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int v = 0; v < 4; ++v) acc[u][v] = 0.f;
+      const int kend = min(dcp, (sp + 1) * cper);
+      for (int k = sp * cper + lane; k < kend; k += 32) {
+        float av[4], bv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          av[u] = xi[u][k];
+          bv[u] = xj[u][k];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+          for (int v = 0; v < 4; ++v) {
+            const float df = av[u] - bv[v];
+            acc[u][v] = fmaf(df, df, acc[u][v]);
+          }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          const float s = warp_sum(acc[u][v]);
+          if (lane == 0) psp[((size_t)sp * nbp + bp) * 16 + u * 4 + v] = s;
+        }
+    }
+  }
+  __syncthreads();
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+  // sum the column splits in order; publish this CTA's partial in slot rk of every CTA of the cluster
+  for (int p = tid; p < np; p += blockDim.x) {
+    const int i = pi[p], j = pj[p];
+    const int bi = i >> 2, bj = j >> 2;
+    const int bp = bi * nb - (bi * (bi - 1)) / 2 + (bj - bi);
+    const int e = (i & 3) * 4 + (j & 3);
+    float s = 0.f;
+    for (int sp = 0; sp < a.nsplit; ++sp) s += psp[((size_t)sp * nbp + bp) * 16 + e];
+    for (int r = 0; r < CS; ++r) *cluster.map_shared_rank(pall + (size_t)rk * np4 + p, r) = s;
+  }
+  TR(2);
+  cluster.sync();
+  TR(3);
+  for (int p = tid; p < np4; p += blockDim.x) {
+    float v = INFINITY, s2 = 0.f;
+    if (p < np) {
+      double s = 0.0;
+      for (int r = 0; r < CS; ++r) s += (double)pall[(size_t)r * np4 + p];
+      s2 = (float)s;
+      v = sqrtf(s2);
+    }
+    sq[p] = s2;
+    pv[p] = v;
+  }
+  __syncthreads();
+  TR(4);
+  // ---- median of the m*m distances = m zeros (diagonal) + every pair distance twice.  Rank
+  //      counting over the pair values: v_p sits at ranks [cl, cle) of the sorted multiset ----
+  float h;
+  if (a.h_fixed > 0.f || m == 1) {
+    h = m == 1 && !(a.h_fixed > 0.f) ? 1.0f : a.h_fixed;
+  } else {
+    if (np <= 512) {
+      // thread = (candidate p, slice of the pair values); packed counts (lt | eq << 16) per slice,
+      // summed by the candidate's thread
+      const int nsl = max(1, min(8, (int)blockDim.x / np));
+      const int nq4 = np4 >> 2, qper = (nq4 + nsl - 1) / nsl;
+      for (int t = tid; t < np * nsl; t += blockDim.x) {
+        const int sl = t / np, p = t - sl * np;
+        const float v = pv[p];
+        int c2 = 0;
+        const int qe = min(nq4, (sl + 1) * qper);
+        for (int q = sl * qper; q < qe; ++q) {
+          const float4 u = *reinterpret_cast<const float4*>(pv + 4 * q);
+          c2 += (u.x < v) + (u.y < v) + (u.z < v) + (u.w < v);
+          c2 += ((u.x == v) + (u.y == v) + (u.z == v) + (u.w == v)) << 16;
+        }
+        cnt[sl * np4 + p] = c2;
+      }
+      __syncthreads();
+      for (int p = tid; p < np; p += blockDim.x) {
+        int c2 = 0;
+        for (int sl = 0; sl < nsl; ++sl) c2 += cnt[sl * np4 + p];
+        const float v = pv[p];
+        const int cl = 2 * (c2 & 0xffff) + (v > 0.f ? m : 0);
+        const int cle = cl + 2 * (c2 >> 16) + (v > 0.f ? 0 : m);
+        if (cl <= a.rank_lo && a.rank_lo < cle) s_med[0] = v;   // equal values: same-value writes
+        if (cl <= a.rank_hi && a.rank_hi < cle) s_med[1] = v;
+      }
+    } else {
+      // sorted pair values: rank r of the multiset is 0 for r < m, else sorted[(r - m) / 2]
+      float* srt = reinterpret_cast<float*>(cnt);   // [P2] (the host sizes cnt for it)
+      int P2 = 1;
+      while (P2 < np) P2 <<= 1;
+      for (int t = tid; t < P2; t += blockDim.x) srt[t] = t < np ? pv[t] : INFINITY;
+      __syncthreads();
+      bitonic_sort_smem(srt, P2);
+      if (tid == 0) {
+        s_med[0] = a.rank_lo < m ? 0.f : srt[(a.rank_lo - m) >> 1];
+        s_med[1] = a.rank_hi < m ? 0.f : srt[(a.rank_hi - m) >> 1];
+      }
+    }
+    __syncthreads();
+    const float med = (s_med[0] + s_med[1]) * 0.5f;
+    h = __fadd_rn(__fmul_rn(__fmul_rn(med, med), a.factor), 1.1920929e-07f);
+  }
+  TR(5);
+  const float c = (2.0f * a.alpha) / (h * (float)m);
+  for (int t = tid; t < m * mp4; t += blockDim.x) {
+    const int i = t / mp4, j = t - i * mp4;
+    float kv = 0.f;
+    if (j < m) {
+      if (i == j) {
+        kv = 1.0f;   // expf(-0 / h)
+      } else {
+        const int lo = min(i, j), hi = max(i, j);
+        kv = expf(-sq[lo * (m - 1) - (lo * (lo - 1)) / 2 + hi - lo - 1] / h);
+      }
+    }
+    kt[t] = kv;
+  }
+  // y_j = c_att g_j - c (x_j - x_0), in place over the staged G
+  {
+    const int nq = dcp >> 2;
+    for (int t = tid; t < m * nq; t += blockDim.x) {
+      const int q = t % nq;
+      const float4 g = reinterpret_cast<const float4*>(ys)[t];
+      const float4 x = reinterpret_cast<const float4*>(xs)[t];
+      const float4 x0 = reinterpret_cast<const float4*>(xs)[q];
+      reinterpret_cast<float4*>(ys)[t] =
+          make_float4(a.c_att * g.x - c * (x.x - x0.x), a.c_att * g.y - c * (x.y - x0.y),
+                      a.c_att * g.z - c * (x.z - x0.z), a.c_att * g.w - c * (x.w - x0.w));
+    }
+  }
+  __syncthreads();
+  for (int i = tid; i < mp4; i += blockDim.x) {
+    double r = 0.0;
+    if (i < m)
+      for (int j = 0; j < m; ++j) r += (double)kt[i * mp4 + j];
+    rs[i] = (float)r;
+  }
+  if (rk == 0 && tid == 0 && a.h_out) *a.h_out = h;
+  __syncthreads();
+  TR(6);
+  // ---- force: item = (4 particles, 4 consecutive columns); K is symmetric, so the four K_ij of a
+  //      block row are one broadcast float4 of row j ----
+  double fsq = 0.0;
+  {
+    const int nq = dcp >> 2;
+    for (int t = tid; t < nb * nq; t += blockDim.x) {
+      const int ib = t / nq, q = t - ib * nq;
+      float acc[4][4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int v = 0; v < 4; ++v) acc[u][v] = 0.f;
+#pragma unroll 4
+      for (int j = 0; j < m; ++j) {
+        const float4 k4 = *reinterpret_cast<const float4*>(kt + j * mp4 + 4 * ib);
+        const float4 y = *reinterpret_cast<const float4*>(ys + j * dcp + 4 * q);
+        const float kk[4] = {k4.x, k4.y, k4.z, k4.w};
+        const float yy[4] = {y.x, y.y, y.z, y.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+          for (int v = 0; v < 4; ++v) acc[u][v] = fmaf(kk[u], yy[v], acc[u][v]);
+      }
+      const float4 x0 = *reinterpret_cast<const float4*>(xs + 4 * q);
+      const float x0v[4] = {x0.x, x0.y, x0.z, x0.w};
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = 4 * ib + u;
+        if (i >= m) break;
+        const float cr = c * rs[i];
+        const float4 xi = *reinterpret_cast<const float4*>(xs + i * dcp + 4 * q);
+        const float xv[4] = {xi.x, xi.y, xi.z, xi.w};
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          const int k = 4 * q + v;
+          if (k < len) {
+            const float f = fmaf(cr, xv[v] - x0v[v], acc[u][v]);
+            if (a.F) a.F[(size_t)i * d + k0 + k] = f;
+            fsq += (double)f * (double)f;
+          }
+        }
+      }
+    }
+  }
+  TR(7);
+  const double bs = block_sum(fsq, red);
+  if (tid == 0) *cluster.map_shared_rank(lossp + rk, 0) = bs;
+  TR(8);
+  cluster.sync();
+  TR(9);
+  if (rk == 0 && tid == 0 && a.loss) {
+    double t = 0.0;
+    for (int r = 0; r < CS; ++r) t += lossp[r];
+    *a.loss = (float)sqrt(t);
+  }
+#ifdef SMI_STEIN_TRACE
+  if (tid == 0 && (rk == 0 || rk == CS - 1)) {
+    tr[10] = gtimer();
+    printf("stein_cluster rk %d: %d %d %d %d %d %d %d %d %d %d  total %d ns\n", rk, (int)(tr[1] - tr[0]),
+           (int)(tr[2] - tr[1]), (int)(tr[3] - tr[2]), (int)(tr[4] - tr[3]), (int)(tr[5] - tr[4]), (int)(tr[6] - tr[5]),
+           (int)(tr[7] - tr[6]), (int)(tr[8] - tr[7]), (int)(tr[9] - tr[8]), (int)(tr[10] - tr[9]),
+           (int)(tr[10] - tr[0]));
+  }
+#endif
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------
@@ -260,7 +617,10 @@ static int small_dc(int m) { return m <= 32 ? 128 : 64; }
 static int small_nchunk(int m, int d) { return (d + small_dc(m) - 1) / small_dc(m); }
 static int force_blocks(int d) { return (d + kForceThreads - 1) / kForceThreads; }
 
+static int fused_cluster_size(int m, int d);
+
 size_t smi_stein_small_workspace_bytes(int m, int d) {
+  (void)fused_cluster_size(m, d);  // device queries happen here, outside any stream capture
   size_t b = 0;
   b += smi_align_up((size_t)small_nchunk(m, d) * pairs_of(m) * 2 * sizeof(float), 256);
   b += smi_align_up((size_t)m * m * sizeof(float), 256);      // K
@@ -282,11 +642,102 @@ void smi_median_ranks(long long n, int mode, long long* lo, long long* hi) {
   }
 }
 
+// Cluster size and per-CTA shared memory of the one-launch variant; 0 when the set does not fit.
+static int fused_dcp(int d, int cs) { return ((d + cs - 1) / cs + 3) & ~3; }
+static int fused_nsplit(int m, int dcp) {
+  const int nb = (m + 3) / 4, nbp = nb * (nb + 1) / 2;
+  int ns = 32 / nbp;
+  const int cap = dcp / 64;
+  if (ns > cap) ns = cap;
+  return ns < 1 ? 1 : ns;
+}
+static size_t fused_smem(int m, int dcp, int cs) {
+  const int np = m * (m - 1) / 2, np4 = (np + 3) & ~3, mp4 = (m + 3) & ~3;
+  const int nb = mp4 / 4, nbp = nb * (nb + 1) / 2;
+  size_t fl = (size_t)2 * m * dcp + (size_t)cs * np4 + 2 * np4 + (size_t)m * mp4 + mp4 +
+              (size_t)fused_nsplit(m, dcp) * nbp * 16 + fused_cnt_words(np);
+  return ((size_t)cs + 1) * sizeof(double) + fl * sizeof(float) + 2 * (size_t)np4 + 32;
+}
+
+static int fused_cluster_size(int m, int d) {
+  static int forced = -1, max_cs = -1;
+  if (forced < 0) {
+    const char* e = getenv("SMI_STEIN_CLUSTER");  // 0 disables, 2 / 4 / 8 / 16 force a size
+    forced = e ? atoi(e) : 1;
+  }
+  if (forced == 0) return 0;
+  if (max_cs < 0) {  // 16 CTAs per cluster is a non-portable size: ask the device once
+    max_cs = 8;
+    if (cudaFuncSetAttribute(stein_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess &&
+        cudaFuncSetAttribute(stein_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) ==
+            cudaSuccess) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(16);
+      cfg.blockDim = dim3(kFusedThreads);
+      cfg.dynamicSmemBytes = 200 * 1024;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension;
+      at[0].val.clusterDim.x = 16;
+      at[0].val.clusterDim.y = at[0].val.clusterDim.z = 1;
+      cfg.attrs = at;
+      cfg.numAttrs = 1;
+      int nc = 0;
+      if (cudaOccupancyMaxActiveClusters(&nc, stein_cluster_kernel, &cfg) == cudaSuccess && nc >= 1) max_cs = 16;
+    }
+    (void)cudaGetLastError();
+  }
+  if (forced == 2 || forced == 4 || forced == 8 || forced == 16)
+    return forced <= max_cs && fused_smem(m, fused_dcp(d, forced), forced) <= 200 * 1024 ? forced : 0;
+  int cs = 1;  // at least 128 columns per CTA; more CTAs only when the set does not fit otherwise
+  while (cs < max_cs && d >= 2 * cs * 128) cs <<= 1;
+  for (; cs <= max_cs; cs <<= 1)
+    if (fused_smem(m, fused_dcp(d, cs), cs) <= 200 * 1024) return cs;
+  return 0;
+}
+
 int smi_stein_small_run(const float* X, const float* G, int m, int d, float c_att, float alpha,
                         int median_mode, float h_fixed, float* F, float* loss, float* h, float* d2_out,
                         bool dist_only, void* ws, size_t ws_bytes, cudaStream_t st) {
   if (m < 1 || m > 64 || d < 1) SMI_FAIL(SMI_ELIMIT, "small Stein path needs 1 <= m <= 64 (m=%d)", m);
   if (ws_bytes < smi_stein_small_workspace_bytes(m, d)) SMI_FAIL(SMI_ENOSPC, "stein workspace too small");
+  if (!dist_only && !d2_out) {
+    const int cs = fused_cluster_size(m, d);
+    if (cs) {
+      FusedArgs fa;
+      fa.X = X;
+      fa.G = G;
+      fa.m = m;
+      fa.d = d;
+      fa.dcp = fused_dcp(d, cs);
+      fa.nsplit = fused_nsplit(m, fa.dcp);
+      fa.c_att = c_att;
+      fa.alpha = alpha;
+      long long lo, hi;
+      smi_median_ranks((long long)m * m, median_mode, &lo, &hi);
+      fa.rank_lo = (int)lo;
+      fa.rank_hi = (int)hi;
+      fa.factor = m > 1 ? (float)(1.0 / log((double)m)) : 1.0f;
+      fa.h_fixed = h_fixed;
+      fa.F = F;
+      fa.loss = loss;
+      fa.h_out = h;
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(cs);
+      cfg.blockDim = dim3(kFusedThreads);
+      cfg.dynamicSmemBytes = fused_smem(m, fa.dcp, cs);
+      cfg.stream = st;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension;
+      at[0].val.clusterDim.x = cs;
+      at[0].val.clusterDim.y = at[0].val.clusterDim.z = 1;
+      cfg.attrs = at;
+      cfg.numAttrs = 1;
+      SMI_PROF_BEGIN(st);
+      SMI_CUDA_OK(cudaLaunchKernelEx(&cfg, stein_cluster_kernel, fa));
+      SMI_LAUNCH_OK_N("stein_cluster_kernel", st);
+      return SMI_OK;
+    }
+  }
   SmiArena ar(ws, ws_bytes);
   const int nchunk = small_nchunk(m, d), dc = small_dc(m), np = pairs_of(m);
   float* partial = ar.take<float>((size_t)nchunk * np * 2);
