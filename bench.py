@@ -356,8 +356,8 @@ def run_gpu(args):
             tf32_peak = 1100.0 * pk["bf16"] / 2250.0
             roof = dict(kernel=dom_name, bound="tensor", achieved=flop / dom_avg_ms / 1e9, peak=tf32_peak / 3.0,
                         unit="TFLOP/s", frac=(flop / dom_avg_ms / 1e9) / (tf32_peak / 3.0),
-                        traffic=27319040 if world == 1 else None,   # dram read + write bytes per launch, ncu capture
-                        traffic_source="profiles/r01f_ncu_bnn_reg_mma3_kernel_C2.txt",
+                        traffic=27392768 if world == 1 else None,   # dram read + write bytes per launch, ncu capture
+                        traffic_source="profiles/r01g_ncu_bnn_reg_mma3_ct_kernel_C2.txt",
                         algorithmic_flop=flop, peak_source=pk["src"],
                         note="warp-level mma.sync 3xTF32 kernel (one CTA per ELBO draw, per-draw weights) against the "
                              "tcgen05 3xTF32 roofline the north star names: peak = 1100 x measured bf16 / 2250 / 3")

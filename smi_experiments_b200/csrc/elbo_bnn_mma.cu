@@ -321,13 +321,20 @@ struct Mma3Plan {
   }
 };
 
-template <int ACT>
+// CB / CIR / CH > 0 fix the minibatch size, the padded input width up8(I + 1) and the hidden width at
+// compile time (the reference's UCI setting: 100 rows, 50 hidden units): every stride and trip count
+// of the five products then folds into the instruction stream.  0 = runtime value.
+template <int ACT, int CB, int CIR, int CH>
 __global__ void __launch_bounds__(kThreads3, 3)
 bnn_reg_mma3_kernel(const float* __restrict__ Z, const int32_t* __restrict__ idx, const float* __restrict__ x,
-                    const float* __restrict__ y, int L, int I, int H, int B, int noise, float sigma,
+                    const float* __restrict__ y, int L, int I, int H_, int B_, int noise, float sigma,
                     float lik_scale, MmaOffsets o, float* __restrict__ DZ, float* __restrict__ LOGP) {
   extern __shared__ __align__(16) float sm[];
-  const Mma3Plan pl(B, I, H);
+  const int B = CB > 0 ? CB : B_, H = CH > 0 ? CH : H_;
+  constexpr int KUI = CIR > 0 ? CIR / 8 : 2;
+  constexpr int KUH = CH > 0 ? ((CH + 7) / 8) : 2;
+  constexpr int KUB = CB > 0 ? ((CB + 7) / 8) : 2;
+  const Mma3Plan pl(B, CIR > 0 ? CIR - 1 : I, H);
   const int HP = pl.HP, IP = pl.IP, BR = pl.BR, HR = pl.HR, IR = pl.IR;
   float* xs = sm + pl.xs;
   float* hA = sm + pl.hA;
@@ -345,11 +352,19 @@ bnn_reg_mma3_kernel(const float* __restrict__ Z, const int32_t* __restrict__ idx
   const float* __restrict__ z = Z + (size_t)n * L;
   float* __restrict__ dz = DZ + (size_t)n * L;
   const bool gamma = noise == SMI_NOISE_GAMMA_PREC;
+#ifdef SMI_BNN_TRACE
+  __shared__ unsigned long long tr[16];
+#define BTR(i) do { if (threadIdx.x == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tr[i])); } while (0)
+#else
+#define BTR(i) do { } while (0)
+#endif
+  BTR(0);
 
   for (int t = threadIdx.x; t < pl.total / 4; t += blockDim.x)
     reinterpret_cast<float4*>(sm)[t] = make_float4(0.f, 0.f, 0.f, 0.f);
   __syncthreads();
 
+  BTR(1);
   // ---- stage the draw ----
   double lprior = 0.0;
   {
@@ -399,24 +414,35 @@ bnn_reg_mma3_kernel(const float* __restrict__ Z, const int32_t* __restrict__ idx
   const float prec = gamma ? expf(z[o.prec]) : 1.f / (sigma * sigma);
   __syncthreads();
 
+  BTR(2);
   // ---- forward 1: h1 = act(x W1 + b1) -> hA [b][j] (column H = 1);  A = x read as [m][r] ----
-  mma_gemm_bal<5, false, true>(B, H + 1, IR, xs, IP, W1p, HP, [&](int b, int j, float v0, float v1) {
-    if (b >= BR) return;
-    const bool live = b < B;
-    const float h0 = live ? (j < H ? act_f<ACT>(v0 + b1[j]) : (j == H ? 1.f : 0.f)) : 0.f;
-    const float h1v = live ? (j + 1 < H ? act_f<ACT>(v1 + b1[j + 1]) : (j + 1 == H ? 1.f : 0.f)) : 0.f;
-    *reinterpret_cast<float2*>(hA + b * HP + j) = make_float2(h0, h1v);
-  });
+  {
+    auto emit1 = [&](int b, int j, float v0, float v1) {
+      if (b >= BR) return;
+      const bool live = b < B;
+      const float h0 = live ? (j < H ? act_f<ACT>(v0 + b1[j]) : (j == H ? 1.f : 0.f)) : 0.f;
+      const float h1v = live ? (j + 1 < H ? act_f<ACT>(v1 + b1[j + 1]) : (j + 1 == H ? 1.f : 0.f)) : 0.f;
+      *reinterpret_cast<float2*>(hA + b * HP + j) = make_float2(h0, h1v);
+    };
+    if constexpr (CB > 0 && CH > 0) mma_gemm_bal_ct<5, false, true, KUI>(B, H + 1, IR, xs, IP, W1p, HP, emit1);
+    else mma_gemm_bal<5, false, true>(B, H + 1, IR, xs, IP, W1p, HP, emit1);
+  }
   __syncthreads();
+  BTR(3);
   // ---- forward 2: h2 = act(h1 W2 + b2) -> hB [b][j];  A = h1 read as [m][r] ----
-  mma_gemm_bal<5, false, true>(B, H, HR, hA, HP, W2p, HP, [&](int b, int j, float v0, float v1) {
-    if (b >= BR) return;
-    const bool live = b < B;
-    const float h0 = (live && j < H) ? act_f<ACT>(v0 + b2[j]) : 0.f;
-    const float h1v = (live && j + 1 < H) ? act_f<ACT>(v1 + b2[j + 1]) : 0.f;
-    *reinterpret_cast<float2*>(hB + b * HP + j) = make_float2(h0, h1v);
-  });
+  {
+    auto emit2 = [&](int b, int j, float v0, float v1) {
+      if (b >= BR) return;
+      const bool live = b < B;
+      const float h0 = (live && j < H) ? act_f<ACT>(v0 + b2[j]) : 0.f;
+      const float h1v = (live && j + 1 < H) ? act_f<ACT>(v1 + b2[j + 1]) : 0.f;
+      *reinterpret_cast<float2*>(hB + b * HP + j) = make_float2(h0, h1v);
+    };
+    if constexpr (CB > 0 && CH > 0) mma_gemm_bal_ct<5, false, true, KUH>(B, H, HR, hA, HP, W2p, HP, emit2);
+    else mma_gemm_bal<5, false, true>(B, H, HR, hA, HP, W2p, HP, emit2);
+  }
   __syncthreads();
+  BTR(4);
   // ---- output layer: four lanes per row, residuals ----
   double ll = 0.0;
   {
@@ -449,6 +475,7 @@ bnn_reg_mma3_kernel(const float* __restrict__ Z, const int32_t* __restrict__ idx
   double lp_const = 0.0;
   if (threadIdx.x == 0) lp_const = (double)B * (0.5 * (double)logf(prec) - 0.5 * (double)kLog2Pi);
   __syncthreads();
+  BTR(5);
   // ---- backward: output layer ----
   for (int j = threadIdx.x; j < H; j += blockDim.x) {
     float g = 0.f;
@@ -466,6 +493,7 @@ bnn_reg_mma3_kernel(const float* __restrict__ Z, const int32_t* __restrict__ idx
     }
   }
   __syncthreads();
+  BTR(6);
   // dh2 = dout w3 act'(h2), in place (hB); lanes along j
   for (int t = threadIdx.x; t < BR * (HP >> 2); t += blockDim.x) {
     const int b = t / (HP >> 2), j0 = (t - b * (HP >> 2)) << 2;
@@ -479,29 +507,40 @@ bnn_reg_mma3_kernel(const float* __restrict__ Z, const int32_t* __restrict__ idx
     *reinterpret_cast<float4*>(hB + b * HP + j0) = make_float4(v[0], v[1], v[2], v[3]);
   }
   __syncthreads();
+  BTR(7);
   // ---- layer 2: [dW2; db2] = [h1, 1]^T dh2 ----
-  mma_gemm_bal<4>(H + 1, H, BR, hA, HP, hB, HP, [&](int k, int j, float v0, float v1) {
-    if (k > H) return;
-    if (j < H) {
-      if (k < H) dz[o.w2 + k * H + j] = v0 - W2p[k * HP + j];
-      else dz[o.b2 + j] = v0 - b2[j];
-    }
-    if (j + 1 < H) {
-      if (k < H) dz[o.w2 + k * H + j + 1] = v1 - W2p[k * HP + j + 1];
-      else dz[o.b2 + j + 1] = v1 - b2[j + 1];
-    }
-  });
+  {
+    auto emit3 = [&](int k, int j, float v0, float v1) {
+      if (k > H) return;
+      if (j < H) {
+        if (k < H) dz[o.w2 + k * H + j] = v0 - W2p[k * HP + j];
+        else dz[o.b2 + j] = v0 - b2[j];
+      }
+      if (j + 1 < H) {
+        if (k < H) dz[o.w2 + k * H + j + 1] = v1 - W2p[k * HP + j + 1];
+        else dz[o.b2 + j + 1] = v1 - b2[j + 1];
+      }
+    };
+    if constexpr (CB > 0 && CH > 0) mma_gemm_bal_ct<4, false, false, KUB>(H + 1, H, BR, hA, HP, hB, HP, emit3);
+    else mma_gemm_bal<4, false, false>(H + 1, H, BR, hA, HP, hB, HP, emit3);
+  }
   __syncthreads();
+  BTR(8);
   // ---- dh1 = (dh2 W2^T) act'(h1), over h1;  A = dh2 read as [m][r], B = W2 read as [n][r] ----
-  mma_gemm_bal<5, true, true>(B, H, HR, hB, HP, W2p, HP, [&](int b, int k, float v0, float v1) {
-    if (b >= BR) return;
-    const float2 h = *reinterpret_cast<const float2*>(hA + b * HP + k);
-    const bool live = b < B;
-    const float d0 = (live && k < H) ? v0 * dact_from_out<ACT>(h.x) : 0.f;
-    const float d1 = (live && k + 1 < H) ? v1 * dact_from_out<ACT>(h.y) : 0.f;
-    *reinterpret_cast<float2*>(hA + b * HP + k) = make_float2(d0, d1);
-  });
+  {
+    auto emit4 = [&](int b, int k, float v0, float v1) {
+      if (b >= BR) return;
+      const float2 h = *reinterpret_cast<const float2*>(hA + b * HP + k);
+      const bool live = b < B;
+      const float d0 = (live && k < H) ? v0 * dact_from_out<ACT>(h.x) : 0.f;
+      const float d1 = (live && k + 1 < H) ? v1 * dact_from_out<ACT>(h.y) : 0.f;
+      *reinterpret_cast<float2*>(hA + b * HP + k) = make_float2(d0, d1);
+    };
+    if constexpr (CB > 0 && CH > 0) mma_gemm_bal_ct<5, true, true, KUH>(B, H, HR, hB, HP, W2p, HP, emit4);
+    else mma_gemm_bal<5, true, true>(B, H, HR, hB, HP, W2p, HP, emit4);
+  }
   __syncthreads();
+  BTR(9);
   // ---- layer 1: [dW1; db1] = [x, 1]^T dh1 ----
   mma_gemm<1>(I + 1, H, BR, xs, IP, hA, HP, [&](int i, int j, float v0, float v1) {
     if (i > I) return;
@@ -514,6 +553,15 @@ bnn_reg_mma3_kernel(const float* __restrict__ Z, const int32_t* __restrict__ idx
       else dz[o.b1 + j + 1] = v1 - b1[j + 1];
     }
   });
+  BTR(10);
+#ifdef SMI_BNN_TRACE
+  if (threadIdx.x == 0 && (n == 0 || n == 700 || n == 1500)) {
+    printf("bnn n=%d: zero %d stage %d fwd1 %d fwd2 %d out %d bwdout %d dh2 %d dW2 %d dh1 %d dW1 %d total %d ns\n", n,
+           (int)(tr[1] - tr[0]), (int)(tr[2] - tr[1]), (int)(tr[3] - tr[2]), (int)(tr[4] - tr[3]), (int)(tr[5] - tr[4]),
+           (int)(tr[6] - tr[5]), (int)(tr[7] - tr[6]), (int)(tr[8] - tr[7]), (int)(tr[9] - tr[8]), (int)(tr[10] - tr[9]),
+           (int)(tr[10] - tr[0]));
+  }
+#endif
   // ---- priors, precision site, log p ----
   lprior = block_sum(lprior, red);
   if (threadIdx.x == 0) {
@@ -541,7 +589,16 @@ int smi_bnn_reg_mma_launch(const SmiModelDesc& md, const float* Z, const int32_t
     if (!two && smem3 <= 75 * 1024) {
       MmaOffsets o3;
       o3.prec = off7[0], o3.w1 = off7[1], o3.b1 = off7[2], o3.w2 = off7[3], o3.b2 = off7[4], o3.w3 = off7[5], o3.b3 = off7[6];
-      auto k3 = md.act == SMI_ACT_RELU ? bnn_reg_mma3_kernel<SMI_ACT_RELU> : bnn_reg_mma3_kernel<SMI_ACT_TANH>;
+      using K3 = void (*)(const float*, const int32_t*, const float*, const float*, int, int, int, int, int, float,
+                          float, MmaOffsets, float*, float*);
+      const bool relu = md.act == SMI_ACT_RELU;
+      K3 k3 = relu ? bnn_reg_mma3_kernel<SMI_ACT_RELU, 0, 0, 0> : bnn_reg_mma3_kernel<SMI_ACT_TANH, 0, 0, 0>;
+      static const bool generic = getenv("SMI_BNN_GENERIC") != nullptr;   // comparison runs
+      if (!generic && B == 100 && H == 50) {   // the UCI setting (experiments/uci_benchmark.py: 50 hidden units, subsample 100)
+        const int ir = up8(I + 1);
+        if (ir == 8) k3 = relu ? bnn_reg_mma3_kernel<SMI_ACT_RELU, 100, 8, 50> : bnn_reg_mma3_kernel<SMI_ACT_TANH, 100, 8, 50>;
+        else if (ir == 16) k3 = relu ? bnn_reg_mma3_kernel<SMI_ACT_RELU, 100, 16, 50> : bnn_reg_mma3_kernel<SMI_ACT_TANH, 100, 16, 50>;
+      }
       SMI_CUDA_OK(cudaFuncSetAttribute(k3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
       SMI_PROF_BEGIN(st);
       k3<<<ndraws, kThreads3, smem3, st>>>(Z, idx, x, y, L, I, H, B, md.noise, md.sigma, lik_scale, o3, DZ, LOGP);

@@ -190,4 +190,79 @@ __device__ __forceinline__ void mma_gemm_bal(int M, int N, int R8, const float* 
   }
 }
 
+// Compile-time tile count and K unrolling: the runtime `u < nv` tests of mma_unit_rt cost a
+// compare + branch + reconvergence per tile and K step (ncu: 14 issued instructions per HMMA in
+// the regression kernel); here the run length is dispatched once per run and, with constant
+// strides / R8 at the call site, every fragment address folds into an immediate offset.
+template <int NT, bool BMR, bool AMR, int KU>
+__device__ __forceinline__ void mma_unit_ct(float (&acc)[NT][4], int R8, const float* __restrict__ PT, int ps, int m0,
+                                            const float* __restrict__ Q, int qs, int n0) {
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const float* pa = AMR ? PT + (m0 + g) * ps + t : PT + t * ps + m0 + g;
+  const int a8 = AMR ? 8 * ps : 8, a4 = AMR ? 4 : 4 * ps, astep = AMR ? 8 : 8 * ps;
+  const float* pb = BMR ? Q + (n0 + g) * qs + t : Q + t * qs + n0 + g;
+  const int qs4 = BMR ? 4 : 4 * qs;
+  const int nstep = BMR ? 8 * qs : 8;
+  const int kstep = BMR ? 8 : 8 * qs;
+#pragma unroll KU
+  for (int k0 = 0; k0 < R8; k0 += 8) {
+    uint32_t ah[4], al[4];
+    split_tf32(pa[0], ah[0], al[0]);
+    split_tf32(pa[a8], ah[1], al[1]);
+    split_tf32(pa[a4], ah[2], al[2]);
+    split_tf32(pa[a4 + a8], ah[3], al[3]);
+#pragma unroll
+    for (int u = 0; u < NT; ++u) {
+      uint32_t bh[2], bl[2];
+      split_tf32(pb[u * nstep], bh[0], bl[0]);
+      split_tf32(pb[qs4 + u * nstep], bh[1], bl[1]);
+      mma_tf32(acc[u], al, bh);
+      mma_tf32(acc[u], ah, bl);
+      mma_tf32(acc[u], ah, bh);
+    }
+    pa += astep;
+    pb += kstep;
+  }
+}
+
+template <int NT, bool BMR, bool AMR, int KU, typename Emit>
+__device__ __forceinline__ void mma_run_ct(int R8, const float* __restrict__ PT, int ps, int m0,
+                                           const float* __restrict__ Q, int qs, int n0, Emit& emit) {
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  float acc[NT][4];
+#pragma unroll
+  for (int a = 0; a < NT; ++a) acc[a][0] = acc[a][1] = acc[a][2] = acc[a][3] = 0.f;
+  mma_unit_ct<NT, BMR, AMR, KU>(acc, R8, PT, ps, m0, Q, qs, n0);
+#pragma unroll
+  for (int a = 0; a < NT; ++a) {
+    emit(m0 + g, n0 + a * 8 + 2 * t, acc[a][0], acc[a][1]);
+    emit(m0 + g + 8, n0 + a * 8 + 2 * t, acc[a][2], acc[a][3]);
+  }
+}
+
+// mma_gemm_bal with the run length dispatched to compile-time tile counts (NTMAX <= 5).
+template <int NTMAX, bool BMR, bool AMR, int KU, typename Emit>
+__device__ __forceinline__ void mma_gemm_bal_ct(int M, int N, int R8, const float* __restrict__ PT, int ps,
+                                                const float* __restrict__ Q, int qs, Emit emit) {
+  static_assert(NTMAX >= 1 && NTMAX <= 5, "run lengths 1..5");
+  const int ntm = (M + 15) >> 4, ntn = (N + 7) >> 3, P = ntm * ntn;
+  const int warp = threadIdx.x >> 5;
+  const int nwarps = blockDim.x >> 5;
+  int p0 = warp * P / nwarps;
+  const int p1 = (warp + 1) * P / nwarps;
+  while (p0 < p1) {
+    const int mt = p0 / ntn, nb = p0 - mt * ntn;
+    const int nv = min(min(NTMAX, ntn - nb), p1 - p0);
+    const int m0 = mt << 4, n0 = nb << 3;
+    switch (nv) {
+      case 1: mma_run_ct<1, BMR, AMR, KU>(R8, PT, ps, m0, Q, qs, n0, emit); break;
+      case 2: if constexpr (NTMAX >= 2) mma_run_ct<2, BMR, AMR, KU>(R8, PT, ps, m0, Q, qs, n0, emit); break;
+      case 3: if constexpr (NTMAX >= 3) mma_run_ct<3, BMR, AMR, KU>(R8, PT, ps, m0, Q, qs, n0, emit); break;
+      case 4: if constexpr (NTMAX >= 4) mma_run_ct<4, BMR, AMR, KU>(R8, PT, ps, m0, Q, qs, n0, emit); break;
+      default: if constexpr (NTMAX >= 5) mma_run_ct<5, BMR, AMR, KU>(R8, PT, ps, m0, Q, qs, n0, emit); break;
+    }
+    p0 += nv;
+  }
+}
+
 }  // namespace mma3
