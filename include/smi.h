@@ -108,6 +108,20 @@ long long smi_launch_count(int reset);
 int smi_profile(int on);
 int smi_profile_report(char* buf, size_t cap);
 
+/* ---- Host-buffer staging: the reference hands engine.update host (NumPy) arrays every step
+ *      (src/engine_run.py:52, experiments/uci_benchmark.py:228); jax.device_put stages them.
+ *   smi_stage_create : two pinned host buffers of `nbytes` used alternately, each guarded by the
+ *                      CUDA event of its last copy (the host may run ahead of the stream).
+ *   smi_stage_h2d    : memcpy src -> pinned, cudaMemcpyAsync pinned -> dst on `stream`; returns
+ *                      without waiting for the copy.  nbytes <= the handle's capacity.
+ *   Not for use during CUDA-graph capture.                                                    */
+int smi_stage_create(size_t nbytes, void** handle);
+int smi_stage_h2d(void* handle, const void* src, size_t nbytes, void* dst, void* stream);
+/* `count` host arrays in ONE copy: array i goes to dst + off_i, off_0 = 0 and
+ * off_{i+1} = off_i + nbytes[i] rounded up to 256 (sum <= the handle's capacity).             */
+int smi_stage_h2dv(void* handle, const void* const* srcs, const size_t* nbytes, int count, void* dst, void* stream);
+int smi_stage_destroy(void* handle);
+
 /* ---- Stein force: replaces RBFKernel.compute + _apply_kernel + _kernel_grad + force sum
  *      + ||F|| (NumPyro steinvi.py::_svgd_loss_and_grads).
  *   X, G : (m, d) particles and per-particle ELBO gradients.

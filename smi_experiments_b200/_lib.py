@@ -58,6 +58,10 @@ PROTOTYPES = {
     "smi_launch_count": (C.c_longlong, [_I]),
     "smi_profile": (_I, [_I]),
     "smi_profile_report": (_I, [C.c_char_p, _Z]),
+    "smi_stage_create": (_I, [_Z, C.POINTER(C.c_void_p)]),
+    "smi_stage_h2d": (_I, [_P, _P, _Z, _P, _P]),
+    "smi_stage_h2dv": (_I, [_P, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), _I, _P, _P]),
+    "smi_stage_destroy": (_I, [_P]),
     "smi_stein_force_workspace_bytes": (_Z, [_I, _I, _I]),
     "smi_stein_force_f32": (_I, [_P, _P, _I, _I, _F, _F, _I, _F, _I, _P, _P, _P, _P, _Z, _P]),
     "smi_sqdist_workspace_bytes": (_Z, [_I, _I, _I]),

@@ -119,3 +119,84 @@ SMI_API int smi_profile_report(char* buf, size_t cap) {
   }
   return SMI_OK;
 }
+
+// ---- host-buffer staging ------------------------------------------------------------------
+namespace {
+struct SmiStage {
+  void* pin[2];
+  cudaEvent_t ev[2];
+  bool used[2];
+  size_t cap;
+  int turn;
+};
+}  // namespace
+
+SMI_API int smi_stage_create(size_t nbytes, void** handle) {
+  if (!handle || nbytes == 0) SMI_FAIL(SMI_EINVAL, "smi_stage_create: bad argument");
+  SmiStage* s = new SmiStage();
+  s->pin[0] = s->pin[1] = nullptr;
+  s->used[0] = s->used[1] = false;
+  s->cap = nbytes;
+  s->turn = 0;
+  for (int i = 0; i < 2; ++i) {
+    if (cudaMallocHost(&s->pin[i], nbytes) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s->ev[i], cudaEventDisableTiming) != cudaSuccess) {
+      const cudaError_t e = cudaGetLastError();
+      for (int j = 0; j <= i; ++j)
+        if (s->pin[j]) cudaFreeHost(s->pin[j]);
+      delete s;
+      SMI_FAIL(SMI_ECUDA, "smi_stage_create: %s", cudaGetErrorString(e));
+    }
+  }
+  *handle = s;
+  return SMI_OK;
+}
+
+SMI_API int smi_stage_h2d(void* handle, const void* src, size_t nbytes, void* dst, void* stream) {
+  SmiStage* s = (SmiStage*)handle;
+  if (!s || !src || !dst) SMI_FAIL(SMI_EINVAL, "smi_stage_h2d: null pointer");
+  if (nbytes > s->cap) SMI_FAIL(SMI_ENOSPC, "smi_stage_h2d: %zu bytes into a stage of %zu", nbytes, s->cap);
+  const int t = s->turn;
+  if (s->used[t]) SMI_CUDA_OK(cudaEventSynchronize(s->ev[t]));   // its previous copy must have executed
+  memcpy(s->pin[t], src, nbytes);
+  SMI_CUDA_OK(cudaMemcpyAsync(dst, s->pin[t], nbytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  SMI_CUDA_OK(cudaEventRecord(s->ev[t], (cudaStream_t)stream));
+  s->used[t] = true;
+  s->turn = t ^ 1;
+  return SMI_OK;
+}
+
+SMI_API int smi_stage_h2dv(void* handle, const void* const* srcs, const size_t* nbytes, int count, void* dst,
+                           void* stream) {
+  SmiStage* s = (SmiStage*)handle;
+  if (!s || !srcs || !nbytes || !dst || count < 1) SMI_FAIL(SMI_EINVAL, "smi_stage_h2dv: bad argument");
+  size_t total = 0;
+  for (int i = 0; i < count; ++i) total = smi_align_up(total, 256) + nbytes[i];
+  if (total > s->cap) SMI_FAIL(SMI_ENOSPC, "smi_stage_h2dv: %zu bytes into a stage of %zu", total, s->cap);
+  const int t = s->turn;
+  if (s->used[t]) SMI_CUDA_OK(cudaEventSynchronize(s->ev[t]));
+  size_t off = 0;
+  for (int i = 0; i < count; ++i) {
+    off = smi_align_up(off, 256);
+    if (!srcs[i] && nbytes[i]) SMI_FAIL(SMI_EINVAL, "smi_stage_h2dv: null source %d", i);
+    memcpy((char*)s->pin[t] + off, srcs[i], nbytes[i]);
+    off += nbytes[i];
+  }
+  SMI_CUDA_OK(cudaMemcpyAsync(dst, s->pin[t], total, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  SMI_CUDA_OK(cudaEventRecord(s->ev[t], (cudaStream_t)stream));
+  s->used[t] = true;
+  s->turn = t ^ 1;
+  return SMI_OK;
+}
+
+SMI_API int smi_stage_destroy(void* handle) {
+  SmiStage* s = (SmiStage*)handle;
+  if (!s) return SMI_OK;
+  for (int i = 0; i < 2; ++i) {
+    if (s->used[i]) cudaEventSynchronize(s->ev[i]);
+    cudaEventDestroy(s->ev[i]);
+    cudaFreeHost(s->pin[i]);
+  }
+  delete s;
+  return SMI_OK;
+}

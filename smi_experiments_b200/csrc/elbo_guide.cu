@@ -71,7 +71,7 @@ guide_prep_kernel(const SmiModelDesc md, const float* __restrict__ psi, int m, i
 // KSUB > 1 (fewer, fatter partials for guide_weights) is used only when one pass covers all draws
 // and components (S <= 128, m <= 32).
 // smem: zt[64][128], mt[64][32], it[64][32], columns XOR-swizzled by ((k & 7) << 2).
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
 guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU, const float* __restrict__ SIG,
                     const float* __restrict__ ISIG, int m, int S, int L, int row0, float* __restrict__ Z,
                     float* __restrict__ QP, int nkq, int ksub) {
@@ -111,16 +111,19 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
           const int kk = (threadIdx.x % kHalf) * 2, sl0 = threadIdx.x / kHalf, dsl = blockDim.x / kHalf;
           const float2 sg2 = *reinterpret_cast<const float2*>(SIG + (size_t)i * L + k0 + kk);
           const float2 mu2 = *reinterpret_cast<const float2*>(MU + (size_t)i * L + k0 + kk);
-          for (int sl = sl0; sl < Sc; sl += 4 * dsl) {
-            float2 ev[4];
+          // all loads of a pass in flight before the first is consumed (the CTA has nothing else to
+          // overlap them with): two rounds for S = 100
+          constexpr int kLB = 8;
+          for (int sl = sl0; sl < Sc; sl += kLB * dsl) {
+            float2 ev[kLB];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < kLB; ++u) {
               const int s2 = sl + u * dsl;
               ev[u] = s2 < Sc ? __ldcs(reinterpret_cast<const float2*>(eps + ((size_t)r * S + sb + s2) * L + k0 + kk))
                               : make_float2(0.f, 0.f);
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < kLB; ++u) {
               const int s2 = sl + u * dsl;
               if (s2 >= Sc) continue;
               const float2 z2 = make_float2(fmaf(sg2.x, ev[u].x, mu2.x), fmaf(sg2.y, ev[u].y, mu2.y));
@@ -177,27 +180,42 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
       }
       // ---- sum the latent slices in a fixed order, write the partial ----
       __syncthreads();
-      float* red = zt;   // [KS][nsj][16]
+      float* red = zt;   // [16][KS][nsj]: consecutive threads -> consecutive words
+      const int tlin = ts * njg + tj;
       if (lane_on) {
 #pragma unroll
         for (int a = 0; a < 4; ++a)
 #pragma unroll
-          for (int b = 0; b < 4; ++b) red[((ks * nsj) + ts * njg + tj) * 16 + a * 4 + b] = acc[a][b];
+          for (int b = 0; b < 4; ++b) red[((a * 4 + b) * KS + ks) * nsj + tlin] = acc[a][b];
       }
       __syncthreads();
+      // the slice sums go to shared memory as the [Sc][mc] block they form in QP, then out as whole
+      // rows (the per-thread 4 x 4 patches written directly cost 32 sectors per store instruction)
+      const int mc = min(JCH, m - jb);
+      float* outb = red + 16 * KS * nsj;   // [Sc][mc], behind the slice partials
       if (ks == 0) {
 #pragma unroll
         for (int a = 0; a < 4; ++a) {
-          const int s = sb + ts * 4 + a;
-          if (s >= S) continue;
+          const int sl = ts * 4 + a;
+          if (sl >= Sc) continue;
 #pragma unroll
           for (int b = 0; b < 4; ++b) {
-            const int j = jb + tj * 4 + b;
-            if (j >= m || tj * 4 + b >= JCH) continue;
+            const int jl = tj * 4 + b;
+            if (jl >= mc) continue;
             float v = 0.f;
-            for (int q = 0; q < KS; ++q) v += red[((q * nsj) + ts * njg + tj) * 16 + a * 4 + b];
-            QP[(((size_t)r * nkq + kq) * S + s) * m + j] = v;
+            for (int q = 0; q < KS; ++q) v += red[((a * 4 + b) * KS + q) * nsj + tlin];
+            outb[sl * mc + jl] = v;
           }
+        }
+      }
+      __syncthreads();
+      float* qdst = QP + (((size_t)r * nkq + kq) * S + sb) * m + jb;
+      if (mc == m) {   // contiguous block
+        for (int t = threadIdx.x; t < Sc * m; t += blockDim.x) qdst[t] = outb[t];
+      } else {
+        for (int t = threadIdx.x; t < Sc * mc; t += blockDim.x) {
+          const int sl = t / mc, jl = t - sl * mc;
+          qdst[(size_t)sl * m + jl] = outb[t];
         }
       }
     }

@@ -18,6 +18,7 @@ equivalent of jit with donated arguments); `update` returns a SteinVIState that 
 engine's buffers.
 """
 
+import ctypes as C
 import math
 from collections import namedtuple
 from functools import partial
@@ -62,6 +63,48 @@ def _radius(fn):
     raise NotImplementedError("only init_to_uniform(radius) initialisation is on the reference's path")
 
 
+def _host_array(arr):
+    if isinstance(arr, torch.Tensor):
+        arr = arr.detach().numpy()
+    return arr if (type(arr) is np.ndarray and arr.flags.c_contiguous) else np.ascontiguousarray(arr)
+
+
+class _Stage:
+    """Pinned staging pair (libsmi) + the device tensors a group of host arguments lands in: the
+    arrays are packed back to back (256-byte aligned) so one H2D copy moves the whole group."""
+
+    def __init__(self, arrays, dtypes, device):
+        self.sig = tuple((a.shape, a.dtype) for a in arrays)
+        n = len(arrays)
+        offs, total = [], 0
+        for a in arrays:
+            total = (total + 255) // 256 * 256
+            offs.append(total)
+            total += int(a.nbytes)
+        self.total = max(total, 1)
+        self.nbytes = sum(int(a.nbytes) for a in arrays)
+        h = C.c_void_p()
+        _lib.call("smi_stage_create", self.total, C.byref(h))
+        self.handle = h
+        self.buf = torch.empty(self.total, dtype=torch.uint8, device=device)
+        self.buf_ptr = self.buf.data_ptr()
+        self.srcs = (C.c_void_p * n)()
+        self.sizes = (C.c_size_t * n)(*[int(a.nbytes) for a in arrays])
+        self.n = n
+        self.raw, self.dev = [], []
+        for a, off, dt in zip(arrays, offs, dtypes):
+            src_dtype = torch.from_numpy(np.empty(0, dtype=a.dtype)).dtype
+            raw = self.buf[off:off + a.nbytes].view(src_dtype).reshape(a.shape)
+            self.raw.append(raw)
+            self.dev.append(raw if src_dtype == dt else torch.empty(a.shape, dtype=dt, device=device))
+
+    def __del__(self):
+        try:
+            _lib.load().smi_stage_destroy(self.handle)
+        except Exception:
+            pass
+
+
 class SteinVI:
     """numpyro.contrib.einstein.SteinVI for the reference's models (see models.py)."""
 
@@ -94,37 +137,42 @@ class SteinVI:
         self.launches_per_update = 0
 
     # ---- data binding: the reference's call-site kwargs -> device tensors -------------------
-    def _to_dev(self, name, arr, dtype):
-        """Host arrays are staged through pinned memory and copied H2D on the current stream
-        every call; CUDA tensors are used in place."""
-        if isinstance(arr, torch.Tensor) and arr.is_cuda:
-            t = arr if arr.dtype == dtype else arr.to(dtype)
-            return t.contiguous()
-        src = arr if isinstance(arr, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(arr))
-        slot = self._stage.get(name)
-        if slot is None or slot[0][0].shape != src.shape or slot[0][0].dtype != src.dtype:
-            # two pinned buffers used alternately, each guarded by the event of its last H2D copy:
-            # without a per-step host sync the host runs ahead of the stream and must not overwrite
-            # a staging buffer whose copy has not executed yet
-            pins = [torch.empty(src.shape, dtype=src.dtype, pin_memory=True) for _ in range(2)]
-            evs = [torch.cuda.Event(), torch.cuda.Event()]
-            dev = torch.empty(src.shape, dtype=dtype, device=self.device)
-            raw = dev if src.dtype == dtype else torch.empty(src.shape, dtype=src.dtype, device=self.device)
-            slot = [pins, raw, dev, evs, 0, [False, False]]
-            self._stage[name] = slot
-        pins, raw, dev, evs, turn, used = slot
-        pin = pins[turn]
-        if used[turn]:
-            evs[turn].synchronize()
-        pin.copy_(src)
-        raw.copy_(pin, non_blocking=True)
-        evs[turn].record()
-        used[turn] = True
-        slot[4] = turn ^ 1
-        if raw is not dev:
-            dev.copy_(raw)  # dtype conversion (e.g. uint8 pixels -> fp32), on the device
-        self.h2d_bytes += src.numel() * src.element_size()
-        return dev
+    def _to_dev(self, names, arrs, dtypes):
+        """Host arrays are staged through pinned memory and copied H2D on the current stream every
+        call, the whole group in one copy (smi_stage_h2dv: two pinned buffers used alternately, each
+        guarded by the event of its last copy, so a host that runs ahead of the stream cannot
+        overwrite a buffer whose copy has not executed); CUDA tensors are used in place."""
+        out = [None] * len(arrs)
+        host = []
+        for i, (arr, dt) in enumerate(zip(arrs, dtypes)):
+            if isinstance(arr, torch.Tensor) and arr.is_cuda:
+                out[i] = (arr if arr.dtype == dt else arr.to(dt)).contiguous()
+            else:
+                host.append(i)
+        if host:
+            hs = [_host_array(arrs[i]) for i in host]
+            key = tuple(names[i] for i in host)
+            slot = self._stage.get(key)
+            if slot is None or slot.sig != tuple((a.shape, a.dtype) for a in hs):
+                slot = _Stage(hs, [dtypes[i] for i in host], self.device)
+                self._stage[key] = slot
+            for j, a in enumerate(hs):
+                slot.srcs[j] = a.ctypes.data
+            _lib.call("smi_stage_h2dv", slot.handle, slot.srcs, slot.sizes, slot.n, slot.buf_ptr, ops._stream())
+            for j, i in enumerate(host):
+                if slot.raw[j] is not slot.dev[j]:
+                    slot.dev[j].copy_(slot.raw[j])  # dtype conversion (e.g. uint8 pixels -> fp32), on the device
+                out[i] = slot.dev[j]
+            self.h2d_bytes += slot.nbytes
+        return out
+
+    def _view(self, name, t, fn):
+        """fn(t), cached while the same device tensor keeps coming back (the staged one does)."""
+        c = self._views.get(name)
+        if c is None or c[0] is not t:
+            c = (t, fn(t))
+            self._views[name] = c
+        return c[1]
 
     def _bind(self, args, kwargs):
         kw = dict(self.static_kwargs)
@@ -132,25 +180,24 @@ class SteinVI:
         m = self.model
         self.h2d_bytes = 0
         if not hasattr(self, "_stage"):
-            self._stage = {}
+            self._stage, self._views = {}, {}
         if isinstance(m, models.GaussianTarget):
             return dict(x=None, y=None, n_total=0, B=0, lik_scale=1.0, idx=False)
         x = args[0] if len(args) > 0 else kw["x"]
         y = args[1] if len(args) > 1 else kw["y"]
         if isinstance(m, models.BNNRegression):
-            xd = self._to_dev("x", x, torch.float32)
-            if xd.dim() == 1:
-                xd = xd[:, None]
-            yd = self._to_dev("y", y, torch.float32).reshape(-1)
+            xd, yd = self._to_dev(("x", "y"), (x, y), (torch.float32, torch.float32))
+            xd = self._view("x", xd, lambda t: t[:, None] if t.dim() == 1 else t)
+            yd = self._view("y", yd, lambda t: t.reshape(-1))
             n = xd.shape[0]
             sub = kw.get("subsample", None)
             if sub is None or sub >= n:
                 return dict(x=xd, y=yd, n_total=0, B=n, lik_scale=1.0, idx=False)
             return dict(x=xd, y=yd, n_total=n, B=int(sub), lik_scale=float(n) / float(sub), idx=True)
         if isinstance(m, models.BNNClassifier):
-            xd = self._to_dev("x", x, torch.float32)
-            xd = xd.reshape(xd.shape[0], -1)
-            yd = self._to_dev("y", y, torch.int32).reshape(-1)
+            xd, yd = self._to_dev(("x", "y"), (x, y), (torch.float32, torch.int32))
+            xd = self._view("x", xd, lambda t: t.reshape(t.shape[0], -1))
+            yd = self._view("y", yd, lambda t: t.reshape(-1))
             b = xd.shape[0]
             n = kw.get("n", b)
             bs = kw.get("batch_size", None)
