@@ -273,7 +273,7 @@ guide_weights_kernel(const SmiModelDesc md, const float* __restrict__ QP, const 
 // at C2: 66 vs 53 us).  MP = padded component count.
 constexpr int kGradKT = 64, kGradSG = 4;
 template <int MP>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, MP <= 20 ? 3 : 2)
 guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, const float* __restrict__ MU,
                   const float* __restrict__ SIG, const float* __restrict__ ISIG, const float* __restrict__ W,
                   const float* __restrict__ DZ, const float* __restrict__ LOGP, const float* __restrict__ LOGQ,
