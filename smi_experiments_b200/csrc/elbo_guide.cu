@@ -70,7 +70,7 @@ guide_prep_kernel(const SmiModelDesc md, const float* __restrict__ psi, int m, i
 // are split over KS slices so the CTA stays busy; the slices are summed in a fixed order at the end.
 // KSUB > 1 (fewer, fatter partials for guide_weights) is used only when one pass covers all draws
 // and components (S <= 128, m <= 32).
-// smem: zt[64][128], mt[64][32], it[64][32], columns XOR-swizzled by ((k & 7) << 2).
+// smem: zt[64][128], mt[64][32], it[64][32], columns XOR-swizzled by ((k & 7) << 2); out[128][32].
 __global__ void __launch_bounds__(256, 3)
 guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU, const float* __restrict__ SIG,
                     const float* __restrict__ ISIG, int m, int S, int L, int row0, float* __restrict__ Z,
@@ -103,8 +103,10 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
         const int k0 = (kq * ksub + sub) * kGuideKT;
         if (k0 >= L) break;
         __syncthreads();
-        // stage the z tile (and write Z on the first component chunk)
-        if ((L & 1) == 0 && k0 + kGuideKT <= L) {
+        // stage the z tile (and write Z on the first component chunk); with one tile per CTA
+        // (ksub == 1) it stays in shared memory for the later component chunks
+        if (ksub == 1 && jb > 0) {
+        } else if ((L & 1) == 0 && k0 + kGuideKT <= L) {
           // even L (every AutoNormal layout of the reference's models) keeps (row, k0) 8-byte aligned:
           // the tile moves as float2 with four independent loads in flight per thread
           constexpr int kHalf = kGuideKT / 2;
@@ -180,7 +182,7 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
       }
       // ---- sum the latent slices in a fixed order, write the partial ----
       __syncthreads();
-      float* red = zt;   // [16][KS][nsj]: consecutive threads -> consecutive words
+      float* red = mt;   // [16][KS][nsj] over mt + it (4096 words): consecutive threads -> consecutive words
       const int tlin = ts * njg + tj;
       if (lane_on) {
 #pragma unroll
@@ -192,7 +194,7 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
       // the slice sums go to shared memory as the [Sc][mc] block they form in QP, then out as whole
       // rows (the per-thread 4 x 4 patches written directly cost 32 sectors per store instruction)
       const int mc = min(JCH, m - jb);
-      float* outb = red + 16 * KS * nsj;   // [Sc][mc], behind the slice partials
+      float* outb = it + kGuideKT * 32;    // [Sc][mc], its own 4096 words (zt must survive the chunk loop)
       if (ks == 0) {
 #pragma unroll
         for (int a = 0; a < 4; ++a) {
@@ -359,11 +361,13 @@ guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, 
   }
 }
 
-// Same as guide_grad_kernel for m > 64 (weak-scaling runs: 20 particles per GPU x N GPUs).  The
-// component tables no longer fit in registers, so the roles are swapped: each thread keeps its
-// draws (z_s and the running T_s, 16 of each per pass) in registers and streams the components
-// through in chunks of 16.
-constexpr int kBigNS = 16, kBigJC = 16;
+// Same as guide_grad_kernel for m > 32 (weak-scaling runs: 20 particles per GPU x N GPUs).  The
+// component tables no longer fit in registers, so the roles are swapped: each thread keeps ALL its
+// draws of a pass (eps_s and the running T_s, NS of each) in registers and streams the components
+// through in chunks of 8: one batch of 16 table loads per chunk, applied to all NS draws (with the
+// tables re-read per 16-draw pass the kernel ran 6x off its issue bound at m = 40).
+constexpr int kBigJC = 8;
+template <int NS>
 __global__ void __launch_bounds__(256, 2)
 guide_grad_big_kernel(const float* __restrict__ psi, const float* __restrict__ eps, const float* __restrict__ MU,
                       const float* __restrict__ SIG, const float* __restrict__ ISIG, const float* __restrict__ W,
@@ -373,60 +377,84 @@ guide_grad_big_kernel(const float* __restrict__ psi, const float* __restrict__ e
                       float* __restrict__ G, float* __restrict__ elbo) {
   const float tau = tau_dev ? *tau_dev : tau_host;
   extern __shared__ float sm[];
-  float* wt = sm;                                   // [S][m] (+ kBigJC floats of slack)
-  float* part = wt + (size_t)S * m + kBigJC;        // [4][64][2]
+  const int mw = (m + 3) & ~3;                      // row pitch of the weights: float4 reads
+  float* wt = sm;                                   // [S][mw] + one zero row of mw + kBigJC floats
+  float* part = wt + (size_t)(S + 1) * mw + kBigJC; // [4][64][2]
   const int kt = blockIdx.x, r = blockIdx.y, i = row0 + r;
   const int kk = threadIdx.x & 63, sg = threadIdx.x >> 6;
   const int k = kt * kGuideKT + kk;
-  for (int t = threadIdx.x; t < S * m; t += blockDim.x) wt[t] = W[(size_t)r * S * m + t];
-  for (int t = threadIdx.x; t < kBigJC; t += blockDim.x) wt[(size_t)S * m + t] = 0.f;
+  for (int t = threadIdx.x; t < S * mw; t += blockDim.x) {
+    const int s = t / mw, j = t - s * mw;
+    wt[t] = j < m ? W[((size_t)r * S + s) * m + j] : 0.f;
+  }
+  for (int t = threadIdx.x; t < mw + kBigJC; t += blockDim.x) wt[(size_t)S * mw + t] = 0.f;
   __syncthreads();
   float gl = 0.f, gs = 0.f;
   if (k < L) {
     const float mu_i = MU[(size_t)i * L + k], sg_i = SIG[(size_t)i * L + k], is_i = ISIG[(size_t)i * L + k];
     const float jac = tr_of[k] == SMI_T_EXP ? 1.f : 0.f;
-    for (int sb = 0; sb < S; sb += 4 * kBigNS) {
-      float zz[kBigNS], T[kBigNS];
+    const float* mucol = MU + k;
+    const float* iscol = ISIG + k;
+    auto load_tab = [&](int jb, float (&mu)[kBigJC], float (&q)[kBigJC]) {
 #pragma unroll
-      for (int t = 0; t < kBigNS; ++t) {
+      for (int j = 0; j < kBigJC; ++j) {
+        const int jj = min(jb + j, m - 1);
+        mu[j] = __ldg(mucol + (size_t)jj * L);
+        const float is = jb + j < m ? __ldg(iscol + (size_t)jj * L) : 0.f;   // q = 0 masks components past m
+        q[j] = is * is;
+      }
+    };
+    for (int sb = 0; sb < S; sb += 4 * NS) {
+      float ep[NS], T[NS];
+#pragma unroll
+      for (int t = 0; t < NS; ++t) {
         const int s = sb + sg + 4 * t;
-        const float ep = s < S ? __ldg(eps + ((size_t)r * S + s) * L + k) : 0.f;
-        zz[t] = fmaf(sg_i, ep, mu_i);
+        ep[t] = s < S ? __ldcs(eps + ((size_t)r * S + s) * L + k) : 0.f;
         T[t] = 0.f;
       }
+      auto apply = [&](int jb, const float (&mu)[kBigJC], const float (&qq)[kBigJC]) {
+#pragma unroll
+        for (int t = 0; t < NS; ++t) {
+          const int s = sb + sg + 4 * t;
+          const float* row = wt + (size_t)min(s, S) * mw + jb;   // row S is zeros; warp-uniform: broadcast reads
+          const float z = fmaf(sg_i, ep[t], mu_i);
+          float acc = T[t];
+#pragma unroll
+          for (int j4 = 0; j4 < kBigJC; j4 += 4) {
+            const float4 w4 = *reinterpret_cast<const float4*>(row + j4);
+            acc = fmaf(w4.x * (z - mu[j4]), qq[j4], acc);
+            acc = fmaf(w4.y * (z - mu[j4 + 1]), qq[j4 + 1], acc);
+            acc = fmaf(w4.z * (z - mu[j4 + 2]), qq[j4 + 2], acc);
+            acc = fmaf(w4.w * (z - mu[j4 + 3]), qq[j4 + 3], acc);
+          }
+          T[t] = acc;
+        }
+      };
       for (int jb = 0; jb < m; jb += kBigJC) {
         float mu[kBigJC], q[kBigJC];
-#pragma unroll
-        for (int j = 0; j < kBigJC; ++j) {
-          mu[j] = 0.f, q[j] = 0.f;
-          if (jb + j < m) {
-            mu[j] = __ldg(MU + (size_t)(jb + j) * L + k);
-            const float is = __ldg(ISIG + (size_t)(jb + j) * L + k);
-            q[j] = is * is;
-          }
-        }
-#pragma unroll
-        for (int t = 0; t < kBigNS; ++t) {
-          const int s = sb + sg + 4 * t;
-          if (s < S) {
-            const float* row = wt + (size_t)s * m + jb;   // warp-uniform: broadcast reads
-            float acc = T[t];
-#pragma unroll
-            for (int j = 0; j < kBigJC; ++j) acc = fmaf(row[j] * (zz[t] - mu[j]), q[j], acc);
-            T[t] = acc;
-          }
-        }
+        load_tab(jb, mu, q);
+        apply(jb, mu, q);
       }
+      // tail: DZ in batches of 8 loads
 #pragma unroll
-      for (int t = 0; t < kBigNS; ++t) {
-        const int s = sb + sg + 4 * t;
-        if (s < S) {
-          const size_t e = ((size_t)r * S + s) * L + k;
-          const float ep = __ldg(eps + e);
-          const float du = fmaf(tau, __ldg(DZ + e), T[t]) + jac;
-          const float wi = wt[(size_t)s * m + i];
-          gl += du - wi * ep * is_i;
-          gs += du * ep - wi * (ep * ep - 1.f) * is_i;
+      for (int t0 = 0; t0 < NS; t0 += 8) {
+        float dzv[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int s = sb + sg + 4 * (t0 + u);
+          dzv[u] = (t0 + u < NS && s < S) ? __ldcs(DZ + ((size_t)r * S + s) * L + k) : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          if (t0 + u >= NS) continue;
+          const int s = sb + sg + 4 * (t0 + u);
+          if (s < S) {
+            const float e1 = ep[t0 + u];
+            const float du = fmaf(tau, dzv[u], T[t0 + u]) + jac;
+            const float wi = wt[(size_t)s * mw + i];
+            gl += du - wi * e1 * is_i;
+            gs += du * e1 - wi * (e1 * e1 - 1.f) * is_i;
+          }
         }
       }
     }
@@ -540,7 +568,7 @@ int smi_guide_prep(const SmiModelDesc& md, const float* psi, int m, ElboWs& w, c
 
 int smi_guide_sample(const SmiModelDesc& md, const float* eps, int m, int S, int row0, int nrows, ElboWs& w,
                      cudaStream_t st) {
-  const size_t smem = (size_t)kGuideKT * (128 + 64) * sizeof(float);
+  const size_t smem = ((size_t)kGuideKT * (128 + 64) + 128 * 32) * sizeof(float);
   static bool set = false;
   if (!set) {
     SMI_CUDA_OK(cudaFuncSetAttribute(guide_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -588,14 +616,15 @@ int smi_guide_grad(const SmiModelDesc& md, const float* psi, const float* eps, i
   if (m <= 20) return launch_grad<20>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
   if (m <= 24) return launch_grad<24>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
   if (m <= 32) return launch_grad<32>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
-  const size_t smem = ((size_t)S * m + kBigJC + 4 * 64 * 2) * sizeof(float);
+  const int mw = (m + 3) & ~3;
+  const size_t smem = ((size_t)(S + 1) * mw + kBigJC + 4 * 64 * 2) * sizeof(float);
   if (smem > 220 * 1024) SMI_FAIL(SMI_ELIMIT, "guide_grad: S * m = %d x %d too large for shared memory", S, m);
-  SMI_CUDA_OK(cudaFuncSetAttribute(guide_grad_big_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  auto kern = S <= 64 ? guide_grad_big_kernel<16> : (S <= 100 ? guide_grad_big_kernel<25> : guide_grad_big_kernel<32>);
+  SMI_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid(w.nkt, nrows);
   SMI_PROF_BEGIN(st);
-  guide_grad_big_kernel<<<grid, 256, smem, st>>>(psi, eps, w.MU, w.SIG, w.ISIG, w.W, w.DZ, w.LOGP, w.LOGQ, w.loc_of,
-                                                 w.rho_of, w.tr_of, m, S, md.latent_dim, md.particle_dim, tau, tau_dev, row0,
-                                                 G, elbo);
+  kern<<<grid, 256, smem, st>>>(psi, eps, w.MU, w.SIG, w.ISIG, w.W, w.DZ, w.LOGP, w.LOGQ, w.loc_of, w.rho_of, w.tr_of, m, S,
+                                md.latent_dim, md.particle_dim, tau, tau_dev, row0, G, elbo);
   SMI_LAUNCH_OK_N("guide_grad_big_kernel", st);
   return SMI_OK;
 }

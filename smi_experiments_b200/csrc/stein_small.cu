@@ -281,6 +281,7 @@ struct FusedArgs {
 };
 
 constexpr int kFusedThreads = 1024;
+constexpr int kFusedSmemMax = 226 * 1024;   // 227 KB per CTA less the static part
 // words of the count / sort scratch for np pair values
 __host__ __device__ inline int fused_cnt_words(int np) {
   const int np4 = (np + 3) & ~3;
@@ -669,12 +670,12 @@ static int fused_cluster_size(int m, int d) {
   if (max_cs < 0) {  // 16 CTAs per cluster is a non-portable size: ask the device once
     max_cs = 8;
     if (cudaFuncSetAttribute(stein_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess &&
-        cudaFuncSetAttribute(stein_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) ==
+        cudaFuncSetAttribute(stein_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemMax) ==
             cudaSuccess) {
       cudaLaunchConfig_t cfg = {};
       cfg.gridDim = dim3(16);
       cfg.blockDim = dim3(kFusedThreads);
-      cfg.dynamicSmemBytes = 200 * 1024;
+      cfg.dynamicSmemBytes = kFusedSmemMax;
       cudaLaunchAttribute at[1];
       at[0].id = cudaLaunchAttributeClusterDimension;
       at[0].val.clusterDim.x = 16;
@@ -687,11 +688,11 @@ static int fused_cluster_size(int m, int d) {
     (void)cudaGetLastError();
   }
   if (forced == 2 || forced == 4 || forced == 8 || forced == 16)
-    return forced <= max_cs && fused_smem(m, fused_dcp(d, forced), forced) <= 200 * 1024 ? forced : 0;
+    return forced <= max_cs && fused_smem(m, fused_dcp(d, forced), forced) <= kFusedSmemMax ? forced : 0;
   int cs = 1;  // at least 128 columns per CTA; more CTAs only when the set does not fit otherwise
   while (cs < max_cs && d >= 2 * cs * 128) cs <<= 1;
   for (; cs <= max_cs; cs <<= 1)
-    if (fused_smem(m, fused_dcp(d, cs), cs) <= 200 * 1024) return cs;
+    if (fused_smem(m, fused_dcp(d, cs), cs) <= kFusedSmemMax) return cs;
   return 0;
 }
 

@@ -40,7 +40,7 @@ def _run(cuda, md, psi, eps, idx, x, y, S, B, lik_scale, tau, row0=0, nrows=None
     return G.cpu().numpy(), E.cpu().numpy()
 
 
-@pytest.mark.parametrize("m,S,N,B,I", [(3, 4, 30, 7, 13), (5, 100, 455, 100, 13), (20, 8, 64, 64, 5)])
+@pytest.mark.parametrize("m,S,N,B,I", [(3, 4, 30, 7, 13), (5, 100, 455, 100, 13), (20, 8, 64, 64, 5), (36, 6, 64, 64, 5)])
 def test_uci_bnn_smi(cuda, m, S, N, B, I):
     from smi_experiments_b200 import models
     pm, om = models.uci_bnn(I), omodels.uci_bnn(I)
@@ -69,7 +69,9 @@ def test_reg_1d_bnn_smi(cuda, h):
 
 
 @pytest.mark.parametrize("guide,m,S,dim", [("normal", 1, 100, 10), ("normal", 20, 100, 100), ("delta", 20, 1, 1000),
-                                           ("delta", 10, 1, 30)])
+                                           ("delta", 10, 1, 30),
+                                           # m > 32: component-streaming gradient kernel, 16 / 25 / 32 draws per thread
+                                           ("normal", 40, 100, 100), ("normal", 70, 33, 50), ("normal", 35, 130, 70)])
 def test_gaussian_target(cuda, guide, m, S, dim):
     from smi_experiments_b200 import models
     pm, om = models.GaussianTarget(dim), omodels.gaussian(dim)
