@@ -70,7 +70,7 @@ guide_prep_kernel(const SmiModelDesc md, const float* __restrict__ psi, int m, i
 // are split over KS slices so the CTA stays busy; the slices are summed in a fixed order at the end.
 // KSUB > 1 (fewer, fatter partials for guide_weights) is used only when one pass covers all draws
 // and components (S <= 128, m <= 32).
-// smem: zt[64][128], mt[64][32], it[64][32], columns XOR-swizzled by ((k & 7) << 2); out[128][32].
+// smem: zt[64][128] (eps), mt[64][32] (A), it[64][32] (B), columns XOR-swizzled by ((k & 7) << 2); out[128][32].
 __global__ void __launch_bounds__(256, 3)
 guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU, const float* __restrict__ SIG,
                     const float* __restrict__ ISIG, int m, int S, int L, int row0, float* __restrict__ Z,
@@ -130,34 +130,38 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
               if (s2 >= Sc) continue;
               const float2 z2 = make_float2(fmaf(sg2.x, ev[u].x, mu2.x), fmaf(sg2.y, ev[u].y, mu2.y));
               if (jb == 0) *reinterpret_cast<float2*>(Z + ((size_t)r * S + sb + s2) * L + k0 + kk) = z2;
-              zt[kk * 128 + (s2 ^ ((kk & 7) << 2))] = z2.x;
-              zt[(kk + 1) * 128 + (s2 ^ (((kk + 1) & 7) << 2))] = z2.y;
+              zt[kk * 128 + (s2 ^ ((kk & 7) << 2))] = ev[u].x;
+              zt[(kk + 1) * 128 + (s2 ^ (((kk + 1) & 7) << 2))] = ev[u].y;
             }
           }
         } else {
           for (int t = threadIdx.x; t < Sc * kGuideKT; t += blockDim.x) {
             const int sl = t / kGuideKT, kk = t - sl * kGuideKT;
             const int s = sb + sl, k = k0 + kk;
-            float z = 0.f;
+            float ep = 0.f;
             if (k < L) {
               const size_t e = ((size_t)r * S + s) * L + k;
-              z = fmaf(SIG[(size_t)i * L + k], eps[e], MU[(size_t)i * L + k]);
-              if (jb == 0) Z[e] = z;
+              ep = eps[e];
+              if (jb == 0) Z[e] = fmaf(SIG[(size_t)i * L + k], ep, MU[(size_t)i * L + k]);
             }
-            zt[kk * 128 + (sl ^ ((kk & 7) << 2))] = z;
+            zt[kk * 128 + (sl ^ ((kk & 7) << 2))] = ep;
           }
         }
         for (int t = threadIdx.x; t < JCH * kGuideKT; t += blockDim.x) {
           const int jl = t / kGuideKT, kk = t - jl * kGuideKT;
           const int j = jb + jl, k = k0 + kk;
-          float mu = 0.f, is = 0.f;  // is = 0 masks padded latents and components
+          // (z - mu_j) / sigma_j with z = mu_i + sigma_i eps, as A + B eps: A = (mu_i - mu_j) / sigma_j,
+          // B = sigma_i / sigma_j (one FMA per pair in the inner loop, and no cancellation against z);
+          // A = B = 0 masks padded latents and components
+          float av = 0.f, bv = 0.f;
           if (j < m && k < L) {
-            mu = MU[(size_t)j * L + k];
-            is = ISIG[(size_t)j * L + k];
+            const float is = ISIG[(size_t)j * L + k];
+            av = (MU[(size_t)i * L + k] - MU[(size_t)j * L + k]) * is;
+            bv = SIG[(size_t)i * L + k] * is;
           }
           const int c = jl ^ ((kk & 7) << 2);
-          mt[kk * 32 + c] = mu;
-          it[kk * 32 + c] = is;
+          mt[kk * 32 + c] = av;
+          it[kk * 32 + c] = bv;
         }
         __syncthreads();
         if (lane_on) {
@@ -174,7 +178,7 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
             for (int a = 0; a < 4; ++a)
 #pragma unroll
               for (int b = 0; b < 4; ++b) {
-                const float df = (zz[a] - mm[b]) * ii[b];
+                const float df = fmaf(ii[b], zz[a], mm[b]);
                 acc[a][b] = fmaf(df, df, acc[a][b]);
               }
           }
@@ -296,18 +300,20 @@ guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, 
   __syncthreads();
   float gl = 0.f, gs = 0.f;
   if (k < L) {
-    float mu[MP], q[MP];
+    // T = sum_j w_j (z - mu_j) q_j with z = mu_i + u, u = sigma_i eps:  T = u sum_j w_j q_j + sum_j w_j c_j,
+    // c_j = (mu_i - mu_j) q_j: two FMAs per (draw, component) and no subtraction against z
+    const float mu_i = MU[(size_t)i * L + k], sg_i = SIG[(size_t)i * L + k], is_i = ISIG[(size_t)i * L + k];
+    float cq[MP], q[MP];
 #pragma unroll
     for (int j = 0; j < MP; ++j) {
-      mu[j] = 0.f;
+      cq[j] = 0.f;
       q[j] = 0.f;
       if (j < m) {
-        mu[j] = MU[(size_t)j * L + k];
         const float is = ISIG[(size_t)j * L + k];
         q[j] = is * is;
+        cq[j] = (mu_i - MU[(size_t)j * L + k]) * q[j];
       }
     }
-    const float mu_i = MU[(size_t)i * L + k], sg_i = SIG[(size_t)i * L + k], is_i = ISIG[(size_t)i * L + k];
     const float jac = tr_of[k] == SMI_T_EXP ? 1.f : 0.f;
     // batches of 8 draws: the 16 global loads are issued before any of them is consumed (the kernel
     // is HBM-latency bound: ncu long-scoreboard stall 7 per issue with the loads left to the compiler)
@@ -326,10 +332,14 @@ guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, 
         const int s = s0 + u * kGradSG;
         if (s < S) {
           const float ep = epv[u];
-          const float z = fmaf(sg_i, ep, mu_i);
-          float T = 0.f;
+          float T1 = 0.f, T2 = 0.f;
 #pragma unroll
-          for (int j = 0; j < MP; ++j) T = fmaf(wt[s * MP + j] * (z - mu[j]), q[j], T);
+          for (int j = 0; j < MP; ++j) {
+            const float wj = wt[s * MP + j];
+            T1 = fmaf(wj, q[j], T1);
+            T2 = fmaf(wj, cq[j], T2);
+          }
+          const float T = fmaf(sg_i * ep, T1, T2);
           const float du = fmaf(tau, dzv[u], T) + jac;
           const float wi = wt[s * MP + i];
           gl += du - wi * ep * is_i;
@@ -366,7 +376,7 @@ guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, 
 // draws of a pass (eps_s and the running T_s, NS of each) in registers and streams the components
 // through in chunks of 8: one batch of 16 table loads per chunk, applied to all NS draws (with the
 // tables re-read per 16-draw pass the kernel ran 6x off its issue bound at m = 40).
-constexpr int kBigJC = 8;
+constexpr int kBigJC = 8, kBigKT = 64, kBigSG = 4;   // CTA = 64 latents x 4 draw groups (32 x 8 measured slower)
 template <int NS>
 __global__ void __launch_bounds__(256, 2)
 guide_grad_big_kernel(const float* __restrict__ psi, const float* __restrict__ eps, const float* __restrict__ MU,
@@ -379,10 +389,10 @@ guide_grad_big_kernel(const float* __restrict__ psi, const float* __restrict__ e
   extern __shared__ float sm[];
   const int mw = (m + 3) & ~3;                      // row pitch of the weights: float4 reads
   float* wt = sm;                                   // [S][mw] + one zero row of mw + kBigJC floats
-  float* part = wt + (size_t)(S + 1) * mw + kBigJC; // [4][64][2]
+  float* part = wt + (size_t)(S + 1) * mw + kBigJC; // [kBigSG][kBigKT][2]
   const int kt = blockIdx.x, r = blockIdx.y, i = row0 + r;
-  const int kk = threadIdx.x & 63, sg = threadIdx.x >> 6;
-  const int k = kt * kGuideKT + kk;
+  const int kk = threadIdx.x & (kBigKT - 1), sg = threadIdx.x / kBigKT;
+  const int k = kt * kBigKT + kk;
   for (int t = threadIdx.x; t < S * mw; t += blockDim.x) {
     const int s = t / mw, j = t - s * mw;
     wt[t] = j < m ? W[((size_t)r * S + s) * m + j] : 0.f;
@@ -399,35 +409,40 @@ guide_grad_big_kernel(const float* __restrict__ psi, const float* __restrict__ e
 #pragma unroll
       for (int j = 0; j < kBigJC; ++j) {
         const int jj = min(jb + j, m - 1);
-        mu[j] = __ldg(mucol + (size_t)jj * L);
         const float is = jb + j < m ? __ldg(iscol + (size_t)jj * L) : 0.f;   // q = 0 masks components past m
         q[j] = is * is;
+        mu[j] = (mu_i - __ldg(mucol + (size_t)jj * L)) * q[j];               // c_j = (mu_i - mu_j) q_j
       }
     };
-    for (int sb = 0; sb < S; sb += 4 * NS) {
-      float ep[NS], T[NS];
+    for (int sb = 0; sb < S; sb += kBigSG * NS) {
+      // T_s = u_s sum_j w_sj q_j + sum_j w_sj c_j (see guide_grad_kernel): two running sums per draw
+      float ep[NS], T1[NS], T2[NS];
 #pragma unroll
       for (int t = 0; t < NS; ++t) {
-        const int s = sb + sg + 4 * t;
+        const int s = sb + sg + kBigSG * t;
         ep[t] = s < S ? __ldcs(eps + ((size_t)r * S + s) * L + k) : 0.f;
-        T[t] = 0.f;
+        T1[t] = T2[t] = 0.f;
       }
-      auto apply = [&](int jb, const float (&mu)[kBigJC], const float (&qq)[kBigJC]) {
+      auto apply = [&](int jb, const float (&cq)[kBigJC], const float (&qq)[kBigJC]) {
 #pragma unroll
         for (int t = 0; t < NS; ++t) {
-          const int s = sb + sg + 4 * t;
+          const int s = sb + sg + kBigSG * t;
           const float* row = wt + (size_t)min(s, S) * mw + jb;   // row S is zeros; warp-uniform: broadcast reads
-          const float z = fmaf(sg_i, ep[t], mu_i);
-          float acc = T[t];
+          float a1 = T1[t], a2 = T2[t];
 #pragma unroll
           for (int j4 = 0; j4 < kBigJC; j4 += 4) {
             const float4 w4 = *reinterpret_cast<const float4*>(row + j4);
-            acc = fmaf(w4.x * (z - mu[j4]), qq[j4], acc);
-            acc = fmaf(w4.y * (z - mu[j4 + 1]), qq[j4 + 1], acc);
-            acc = fmaf(w4.z * (z - mu[j4 + 2]), qq[j4 + 2], acc);
-            acc = fmaf(w4.w * (z - mu[j4 + 3]), qq[j4 + 3], acc);
+            a1 = fmaf(w4.x, qq[j4], a1);
+            a2 = fmaf(w4.x, cq[j4], a2);
+            a1 = fmaf(w4.y, qq[j4 + 1], a1);
+            a2 = fmaf(w4.y, cq[j4 + 1], a2);
+            a1 = fmaf(w4.z, qq[j4 + 2], a1);
+            a2 = fmaf(w4.z, cq[j4 + 2], a2);
+            a1 = fmaf(w4.w, qq[j4 + 3], a1);
+            a2 = fmaf(w4.w, cq[j4 + 3], a2);
           }
-          T[t] = acc;
+          T1[t] = a1;
+          T2[t] = a2;
         }
       };
       for (int jb = 0; jb < m; jb += kBigJC) {
@@ -441,16 +456,16 @@ guide_grad_big_kernel(const float* __restrict__ psi, const float* __restrict__ e
         float dzv[8];
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
-          const int s = sb + sg + 4 * (t0 + u);
+          const int s = sb + sg + kBigSG * (t0 + u);
           dzv[u] = (t0 + u < NS && s < S) ? __ldcs(DZ + ((size_t)r * S + s) * L + k) : 0.f;
         }
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
           if (t0 + u >= NS) continue;
-          const int s = sb + sg + 4 * (t0 + u);
+          const int s = sb + sg + kBigSG * (t0 + u);
           if (s < S) {
             const float e1 = ep[t0 + u];
-            const float du = fmaf(tau, dzv[u], T[t0 + u]) + jac;
+            const float du = fmaf(tau, dzv[u], fmaf(sg_i * e1, T1[t0 + u], T2[t0 + u])) + jac;
             const float wi = wt[(size_t)s * mw + i];
             gl += du - wi * e1 * is_i;
             gs += du * e1 - wi * (e1 * e1 - 1.f) * is_i;
@@ -459,15 +474,15 @@ guide_grad_big_kernel(const float* __restrict__ psi, const float* __restrict__ e
       }
     }
   }
-  part[(sg * 64 + kk) * 2] = gl;
-  part[(sg * 64 + kk) * 2 + 1] = gs;
+  part[(sg * kBigKT + kk) * 2] = gl;
+  part[(sg * kBigKT + kk) * 2 + 1] = gs;
   __syncthreads();
   if (sg == 0 && k < L) {
     float a = 0.f, b = 0.f;
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {
-      a += part[(g * 64 + kk) * 2];
-      b += part[(g * 64 + kk) * 2 + 1];
+    for (int g = 0; g < kBigSG; ++g) {
+      a += part[(g * kBigKT + kk) * 2];
+      b += part[(g * kBigKT + kk) * 2 + 1];
     }
     const float inv = 1.f / (float)S;
     G[(size_t)r * d + loc_of[k]] = a * inv;
@@ -616,12 +631,14 @@ int smi_guide_grad(const SmiModelDesc& md, const float* psi, const float* eps, i
   if (m <= 20) return launch_grad<20>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
   if (m <= 24) return launch_grad<24>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
   if (m <= 32) return launch_grad<32>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+  if (m <= 40) return launch_grad<40>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+  if (m <= 48) return launch_grad<48>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
   const int mw = (m + 3) & ~3;
-  const size_t smem = ((size_t)(S + 1) * mw + kBigJC + 4 * 64 * 2) * sizeof(float);
+  const size_t smem = ((size_t)(S + 1) * mw + kBigJC + kBigSG * kBigKT * 2) * sizeof(float);
   if (smem > 220 * 1024) SMI_FAIL(SMI_ELIMIT, "guide_grad: S * m = %d x %d too large for shared memory", S, m);
   auto kern = S <= 64 ? guide_grad_big_kernel<16> : (S <= 100 ? guide_grad_big_kernel<25> : guide_grad_big_kernel<32>);
   SMI_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dim3 grid(w.nkt, nrows);
+  dim3 grid((md.latent_dim + kBigKT - 1) / kBigKT, nrows);
   SMI_PROF_BEGIN(st);
   kern<<<grid, 256, smem, st>>>(psi, eps, w.MU, w.SIG, w.ISIG, w.W, w.DZ, w.LOGP, w.LOGQ, w.loc_of, w.rho_of, w.tr_of, m, S,
                                 md.latent_dim, md.particle_dim, tau, tau_dev, row0, G, elbo);
