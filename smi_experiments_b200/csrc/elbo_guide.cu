@@ -10,6 +10,7 @@
 //   drho_ik  = mean_s ( dU_k eps_k - w_i (eps_k^2 - 1) / sigma_ik ) * sigmoid(rho_ik)
 // Everything is summed in a fixed order (no floating-point atomics).
 #include <math.h>
+#include <stdlib.h>
 
 #include "elbo.cuh"
 
@@ -531,12 +532,20 @@ static int nlb_of(int L) { return (L + 255) / 256; }
 size_t smi_elbo_carve(SmiArena& ar, ElboWs& w, const SmiModelDesc& md, int m, int S, int nrows, int B) {
   const int L = md.latent_dim;
   w.nkt = (L + kGuideKT - 1) / kGuideKT;
-  // fatter QP partials when one pass covers all draws and components: aim at ~16 CTAs per SM
+  // KSUB tiles per CTA (fatter QP partials) when one pass covers all draws and components.  The CTAs
+  // of guide_sample run in near lock-step rounds of 3 per SM, each CTA = KSUB tile passes + one
+  // reduction (~0.4 of a pass): pick the KSUB with the fewest round-passes (C2: 52 x 20 tiles -> KSUB 3
+  // = one round of 360 CTAs instead of three rounds of 1040; measured 52 -> 43 us).
   w.ksub = 1;
   if (S <= 128 && m <= 32) {
-    const long long ctas = (long long)w.nkt * nrows;
-    w.ksub = (int)(ctas / 2400);
-    w.ksub = w.ksub < 1 ? 1 : (w.ksub > 8 ? 8 : w.ksub);
+    const long long slots = 3LL * smi_num_sms();
+    double best = 1e30;
+    for (int ks = 1; ks <= 8; ++ks) {
+      const long long ctas = (long long)((w.nkt + ks - 1) / ks) * nrows;
+      const double cost = (double)((ctas + slots - 1) / slots) * ((double)ks + 0.4);
+      if (cost < best - 1e-9) best = cost, w.ksub = ks;
+    }
+    if (getenv("SMI_KSUB")) w.ksub = atoi(getenv("SMI_KSUB"));
   }
   w.nkq = (w.nkt + w.ksub - 1) / w.ksub;
   w.loc_of = ar.take<int>(L);
