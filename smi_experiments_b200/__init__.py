@@ -17,3 +17,4 @@ from .early_stop import OnlineEarlyStop  # noqa: F401
 from .steinvi import ASVGD, SVGD, PRNGKey, SteinVI, SteinVIRunResult, SteinVIState  # noqa: F401
 
 __version__ = "0.1.0"
+from .logger import ClassExpLogger, ExpLogger  # noqa: F401
