@@ -230,7 +230,14 @@ int smi_prng_step_f32(const SmiModelDesc* md, const uint32_t* key_in, uint32_t* 
                       int S, int n_total, int B, int row0, int nrows, float* eps, int32_t* idx,
                       void* stream);
 
-/* jax.random primitives on the device (partitionable threefry layout), used by engine.init
+/* Threefry stream layout of every PRNG entry below and of the predictive draws: JAX flipped the default of
+ * jax_threefry_partitionable in 0.5.0 and the reference leaves JAX unpinned (requirements.txt), so both exist.
+ * Process-wide; returns the previous layout; any other argument only queries.  Default: partitionable.  */
+#define SMI_PRNG_PARTITIONABLE 1
+#define SMI_PRNG_LEGACY 0
+int smi_prng_layout(int layout);
+
+/* jax.random primitives on the device (layout per smi_prng_layout), used by engine.init
  * (numpyro init_to_uniform / guide initialisation) and exposed for known-answer tests.
  *   smi_prng_split      : keys_out (num, 2) = jax.random.split(key, num)
  *   smi_prng_uniform_f32: out (n) = jax.random.uniform(key, (n,), minval=lo, maxval=hi)

@@ -23,30 +23,31 @@ def softplus(x):
     return np.maximum(x, 0) + np.log1p(np.exp(-np.abs(x)))
 
 
-def predictive_reg(spec, psi, key, num_samples, x, y=None, guide="normal", dtype=np.float64):
+def predictive_reg(spec, psi, key, num_samples, x, y=None, guide="normal", dtype=np.float64,
+                   layout_mode=prng.LAYOUT_PARTITIONABLE):
     """dict(assign (S,), latents (S, L), y_loc (S, n), y (S, n), loglik (S, n) | None)."""
     rows, L, d = models.layout(spec, guide)
     psi = np.asarray(psi, dtype)
     m, S, n = psi.shape[0], int(num_samples), x.shape[0]
-    ka, kg, km = prng.split(np.asarray(key, np.uint32), 3)
+    ka, kg, km = prng.split(np.asarray(key, np.uint32), 3, layout_mode)
     if guide == "normal":
-        assign = prng.randint_bits_to_index(prng.random_bits(ka, S), m)
+        assign = prng.randint_bits_to_index(prng.random_bits(ka, S, layout_mode), m)
     else:
         assign = (np.arange(S) % m).astype(np.int32)
-    dkeys, nkeys = prng.split(kg, S), prng.split(km, S)
+    dkeys, nkeys = prng.split(kg, S, layout_mode), prng.split(km, S, layout_mode)
     lat = np.zeros((S, L), dtype)
     noise = np.zeros((S, n), dtype)
     for s in range(S):
         kk = dkeys[s]
         p = psi[assign[s]]
         for r in rows:
-            kk, sub = prng.split(kk, 2)
+            kk, sub = prng.split(kk, 2, layout_mode)
             u = p[r["loc"]:r["loc"] + r["size"]]
             if guide == "normal":
-                eps = prng.normal(sub, r["size"]).astype(dtype)
+                eps = prng.normal(sub, r["size"], layout_mode).astype(dtype)
                 u = u + softplus(p[r["rho"]:r["rho"] + r["size"]]) * eps
             lat[s, r["lat"]:r["lat"] + r["size"]] = np.exp(u) if r["transform"] == models.T_EXP else u
-        noise[s] = prng.normal(nkeys[s], n).astype(dtype)
+        noise[s] = prng.normal(nkeys[s], n, layout_mode).astype(dtype)
     tdt = torch.float64 if dtype == np.float64 else torch.float32
     theta = torch.from_numpy(lat).to(tdt)
     xb = torch.from_numpy(np.asarray(x, dtype)).to(tdt).reshape(n, -1)[None].expand(S, n, -1)
@@ -130,7 +131,8 @@ def classification_metrics(logits, y, ypred=None, bins=100):
     return out
 
 
-def predictive_cls(spec, psi, key, num_samples, x, guide="normal", dtype=np.float64):
+def predictive_cls(spec, psi, key, num_samples, x, guide="normal", dtype=np.float64,
+                   layout_mode=prng.LAYOUT_PARTITIONABLE):
     """Classifier counterpart of predictive_reg (reference src/models/mlp.py:14-65 under
     MixtureGuidePredictive): dict(assign, latents (S, L), logits (S, n, O), y (S, n)).
     y = argmax(logits + Gumbel), Gumbel = -log(-log(uniform(key_s, (n, O), minval=tiny)))
@@ -138,19 +140,19 @@ def predictive_cls(spec, psi, key, num_samples, x, guide="normal", dtype=np.floa
     rows, L, d = models.layout(spec, guide)
     psi = np.asarray(psi, dtype)
     m, S, n = psi.shape[0], int(num_samples), x.shape[0]
-    ka, kg, km = prng.split(np.asarray(key, np.uint32), 3)
-    assign = (prng.randint_bits_to_index(prng.random_bits(ka, S), m) if guide == "normal"
+    ka, kg, km = prng.split(np.asarray(key, np.uint32), 3, layout_mode)
+    assign = (prng.randint_bits_to_index(prng.random_bits(ka, S, layout_mode), m) if guide == "normal"
               else (np.arange(S) % m).astype(np.int32))
-    dkeys, nkeys = prng.split(kg, S), prng.split(km, S)
+    dkeys, nkeys = prng.split(kg, S, layout_mode), prng.split(km, S, layout_mode)
     lat = np.zeros((S, L), dtype)
     for s in range(S):
         kk = dkeys[s]
         p = psi[assign[s]]
         for r in rows:
-            kk, sub = prng.split(kk, 2)
+            kk, sub = prng.split(kk, 2, layout_mode)
             u = p[r["loc"]:r["loc"] + r["size"]]
             if guide == "normal":
-                u = u + softplus(p[r["rho"]:r["rho"] + r["size"]]) * prng.normal(sub, r["size"]).astype(dtype)
+                u = u + softplus(p[r["rho"]:r["rho"] + r["size"]]) * prng.normal(sub, r["size"], layout_mode).astype(dtype)
             lat[s, r["lat"]:r["lat"] + r["size"]] = u
     tdt = torch.float64 if dtype == np.float64 else torch.float32
     xb = torch.from_numpy(np.asarray(x, dtype).reshape(n, -1)).to(tdt)[None].expand(S, n, -1)
@@ -159,7 +161,7 @@ def predictive_cls(spec, psi, key, num_samples, x, guide="normal", dtype=np.floa
     tiny = np.float32(1.17549435e-38)
     y = np.zeros((S, n), np.int32)
     for s in range(S):
-        f = prng.bits_to_unit_float(prng.random_bits(nkeys[s], n * O)).astype(np.float32)
+        f = prng.bits_to_unit_float(prng.random_bits(nkeys[s], n * O, layout_mode)).astype(np.float32)
         u = np.maximum(tiny, f + tiny).astype(np.float64)
         g = -np.log(-np.log(u)).reshape(n, O)
         y[s] = np.argmax(logits[s] + g, axis=-1)

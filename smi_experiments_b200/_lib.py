@@ -82,6 +82,7 @@ PROTOTYPES = {
     "smi_elbo_grad_tau_f32": (_I, [_MD, _P, _P, _P, _P, _P, _I, _I, _I, _F, _P, _I, _I, _P, _P, _P, _Z, _P]),
     "smi_asvgd_tau_f32": (_I, [_P, _I, _I, _I, _I, _I, _P, _P]),
     "smi_prng_step_f32": (_I, [_MD, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
+    "smi_prng_layout": (_I, [_I]),
     "smi_prng_split": (_I, [_P, _I, _P, _P]),
     "smi_prng_uniform_f32": (_I, [_P, _Z, _F, _F, _P, _P]),
     "smi_prng_normal_f32": (_I, [_P, _Z, _P, _P]),

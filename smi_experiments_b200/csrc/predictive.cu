@@ -44,7 +44,7 @@ struct PredOffsets {
 template <int ACT>
 __global__ void __launch_bounds__(kThreads)
 predictive_reg_kernel(const SmiModelDesc md, PredOffsets o, const float* __restrict__ psi, int m,
-                      const uint32_t* __restrict__ key, int S, const float* __restrict__ x, int n,
+                      const uint32_t* __restrict__ key, int legacy, int S, const float* __restrict__ x, int n,
                       const float* __restrict__ y, int32_t* __restrict__ assign, float* __restrict__ latents,
                       float* __restrict__ y_loc, float* __restrict__ y_draw, float* __restrict__ loglik) {
   extern __shared__ float sm[];
@@ -58,15 +58,15 @@ predictive_reg_kernel(const SmiModelDesc md, PredOffsets o, const float* __restr
   const bool delta = md.guide == SMI_GUIDE_DELTA;
   if (threadIdx.x == 0) {
     const Key k0 = {key[0], key[1]};
-    const Key ka = split_at(k0, 0), kg = split_at(k0, 1), km = split_at(k0, 2);
+    const Key ka = split_at(k0, 0, 3, legacy), kg = split_at(k0, 1, 3, legacy), km = split_at(k0, 2, 3, legacy);
     // AutoDelta (Predictive with batch_ndims = 1): draw s IS particle s
-    s_a = delta ? s % m : (int)(((unsigned long long)bits_at(ka, (uint32_t)s) * (unsigned long long)m) >> 32);
-    Key kk = split_at(kg, (uint32_t)s);
+    s_a = delta ? s % m : (int)(((unsigned long long)bits_at(ka, (uint32_t)s, (uint32_t)S, legacy) * (unsigned long long)m) >> 32);
+    Key kk = split_at(kg, (uint32_t)s, (uint32_t)S, legacy);
     for (int t = 0; t < md.n_sites; ++t) {
-      site_key[t] = split_at(kk, 1);
-      kk = split_at(kk, 0);
+      site_key[t] = split_at(kk, 1, 2, legacy);
+      kk = split_at(kk, 0, 2, legacy);
     }
-    noise_key = split_at(km, (uint32_t)s);
+    noise_key = split_at(km, (uint32_t)s, (uint32_t)S, legacy);
     if (assign) assign[s] = s_a;
   }
   __syncthreads();
@@ -76,7 +76,7 @@ predictive_reg_kernel(const SmiModelDesc md, PredOffsets o, const float* __restr
     const Key k = site_key[t];
     for (int q = threadIdx.x; q < st.size; q += blockDim.x) {
       float u = p[st.loc + q];
-      if (!delta) u = fmaf(softplus_f(p[st.rho + q]), normal_from_bits(bits_at(k, (uint32_t)q)), u);
+      if (!delta) u = fmaf(softplus_f(p[st.rho + q]), normal_from_bits(bits_at(k, (uint32_t)q, (uint32_t)st.size, legacy)), u);
       const float v = st.transform == SMI_T_EXP ? expf(u) : u;
       th[st.lat + q] = v;
       if (latents) latents[(size_t)s * L + st.lat + q] = v;
@@ -112,7 +112,7 @@ predictive_reg_kernel(const SmiModelDesc md, PredOffsets o, const float* __restr
     if (lane == 0) {
       const size_t e = (size_t)s * n + r;
       y_loc[e] = out;
-      if (y_draw) y_draw[e] = fmaf(sigma, normal_from_bits(bits_at(noise_key, (uint32_t)r)), out);
+      if (y_draw) y_draw[e] = fmaf(sigma, normal_from_bits(bits_at(noise_key, (uint32_t)r, (uint32_t)n, legacy)), out);
       if (loglik) {
         const float z = (y[r] - out) / sigma;
         loglik[e] = -0.5f * z * z + lognorm;
@@ -215,7 +215,8 @@ SMI_API int smi_predictive_reg_f32(const SmiModelDesc* md, const float* psi, int
   auto kern = md->act == SMI_ACT_RELU ? predictive_reg_kernel<SMI_ACT_RELU> : predictive_reg_kernel<SMI_ACT_TANH>;
   if (smem > 48 * 1024) SMI_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   SMI_PROF_BEGIN(st);
-  kern<<<num_samples, kThreads, smem, st>>>(*md, o, psi, m, key, num_samples, x, n, y, assign, latents, y_loc, y_draw,
+  kern<<<num_samples, kThreads, smem, st>>>(*md, o, psi, m, key, g_smi_prng_legacy, num_samples, x, n, y, assign, latents, y_loc,
+                                            y_draw,
                                             loglik);
   SMI_LAUNCH_OK_N("predictive_reg_kernel", st);
   return SMI_OK;
@@ -379,19 +380,19 @@ SMI_API int smi_metric_classification_f32(const float* logits, const int32_t* y,
 // predictive_reg_kernel; every CTA of a draw walks the (short) chain itself.
 __global__ void __launch_bounds__(kThreads)
 predictive_latents_kernel(const SmiModelDesc md, const float* __restrict__ psi, int m, const uint32_t* __restrict__ key,
-                          int S, int32_t* __restrict__ assign, float* __restrict__ latents) {
+                          int legacy, int S, int32_t* __restrict__ assign, float* __restrict__ latents) {
   __shared__ Key site_key[SMI_MAX_SITES];
   __shared__ int s_a;
   const int s = blockIdx.y, L = md.latent_dim, d = md.particle_dim;
   const bool delta = md.guide == SMI_GUIDE_DELTA;
   if (threadIdx.x == 0) {
     const Key k0 = {key[0], key[1]};
-    const Key ka = split_at(k0, 0), kg = split_at(k0, 1);
-    s_a = delta ? s % m : (int)(((unsigned long long)bits_at(ka, (uint32_t)s) * (unsigned long long)m) >> 32);
-    Key kk = split_at(kg, (uint32_t)s);
+    const Key ka = split_at(k0, 0, 3, legacy), kg = split_at(k0, 1, 3, legacy);
+    s_a = delta ? s % m : (int)(((unsigned long long)bits_at(ka, (uint32_t)s, (uint32_t)S, legacy) * (unsigned long long)m) >> 32);
+    Key kk = split_at(kg, (uint32_t)s, (uint32_t)S, legacy);
     for (int t = 0; t < md.n_sites; ++t) {
-      site_key[t] = split_at(kk, 1);
-      kk = split_at(kk, 0);
+      site_key[t] = split_at(kk, 1, 2, legacy);
+      kk = split_at(kk, 0, 2, legacy);
     }
     if (assign && blockIdx.x == 0) assign[s] = s_a;
   }
@@ -404,7 +405,7 @@ predictive_latents_kernel(const SmiModelDesc md, const float* __restrict__ psi, 
     const SmiSite st = md.sites[t];
     const int q = k - st.lat;
     float u = p[st.loc + q];
-    if (!delta) u = fmaf(softplus_f(p[st.rho + q]), normal_from_bits(bits_at(site_key[t], (uint32_t)q)), u);
+    if (!delta) u = fmaf(softplus_f(p[st.rho + q]), normal_from_bits(bits_at(site_key[t], (uint32_t)q, (uint32_t)st.size, legacy)), u);
     latents[(size_t)s * L + k] = st.transform == SMI_T_EXP ? expf(u) : u;
   }
 }
@@ -415,7 +416,8 @@ SMI_API int smi_predictive_latents_f32(const SmiModelDesc* md, const float* psi,
   if (m < 1 || num_samples < 1) SMI_FAIL(SMI_EINVAL, "smi_predictive_latents_f32: m=%d S=%d", m, num_samples);
   dim3 grid((md->latent_dim + 2047) / 2048, num_samples);
   SMI_PROF_BEGIN((cudaStream_t)stream);
-  predictive_latents_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(*md, psi, m, key, num_samples, assign, latents);
+  predictive_latents_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(*md, psi, m, key, g_smi_prng_legacy, num_samples, assign,
+                                                                         latents);
   SMI_LAUNCH_OK_N("predictive_latents_kernel", (cudaStream_t)stream);
   return SMI_OK;
 }
@@ -427,7 +429,7 @@ SMI_API int smi_predictive_latents_f32(const SmiModelDesc* md, const float* psi,
 template <int ACT>
 __global__ void __launch_bounds__(kThreads)
 cls_head_kernel(const float* __restrict__ Zl, long long L, int off_b2, int off_w2, int off_b3, int off_w3,
-                const float* __restrict__ H1, int n, int H, int O, const uint32_t* __restrict__ key, int S,
+                const float* __restrict__ H1, int n, int H, int O, const uint32_t* __restrict__ key, int legacy, int S,
                 float* __restrict__ logits, int32_t* __restrict__ ydraw, int rows_per_block) {
   extern __shared__ float sm[];
   float* W2 = sm;                 // [H][H]
@@ -444,7 +446,7 @@ cls_head_kernel(const float* __restrict__ Zl, long long L, int off_b2, int off_w
   for (int t = threadIdx.x; t < O; t += blockDim.x) b3[t] = z[off_b3 + t];
   if (threadIdx.x == 0) {
     const Key k0 = {key[0], key[1]};
-    noise_key = split_at(split_at(k0, 2), (uint32_t)s);
+    noise_key = split_at(split_at(k0, 2, 3, legacy), (uint32_t)s, (uint32_t)S, legacy);
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
@@ -468,7 +470,7 @@ cls_head_kernel(const float* __restrict__ Zl, long long L, int off_b2, int off_w
       for (int j = 0; j < H; ++j) a = fmaf(h2[j], W3[j * O + lane], a);
       logits[((size_t)s * n + r) * O + lane] = a;
       if (ydraw) {
-        const uint32_t bits = bits_at(noise_key, (uint32_t)(r * O + lane));
+        const uint32_t bits = bits_at(noise_key, (uint32_t)(r * O + lane), (uint32_t)(n * O), legacy);
         const float f = __uint_as_float((bits >> 9) | 0x3F800000u) - 1.0f;
         const float u = fmaxf(1.17549435e-38f, f + 1.17549435e-38f);
         best = a - logf(-logf(u));
@@ -503,7 +505,8 @@ SMI_API int smi_predictive_cls_head_f32(const SmiModelDesc* md, const float* lat
   cudaStream_t st = (cudaStream_t)stream;
   SMI_PROF_BEGIN(st);
   kern<<<grid, kThreads, smem, st>>>(latents, (long long)md->latent_dim, md->sites[2].lat, md->sites[3].lat,
-                                     md->sites[4].lat, md->sites[5].lat, h1, n, H, O, key, num_samples, logits, y_draw,
+                                     md->sites[4].lat, md->sites[5].lat, h1, n, H, O, key, g_smi_prng_legacy, num_samples,
+                                     logits, y_draw,
                                      rows_per_block);
   SMI_LAUNCH_OK_N("cls_head_kernel", st);
   return SMI_OK;

@@ -19,7 +19,8 @@ using namespace smi_prng;
 
 __global__ void __launch_bounds__(256)
 prng_step_kernel(const SmiModelDesc md, const uint32_t* __restrict__ key_in, uint32_t* __restrict__ key_out,
-                 int m, int S, int n_total, int B, int row0, float* __restrict__ eps, int32_t* __restrict__ idx) {
+                 int m, int S, int n_total, int B, int row0, int legacy, float* __restrict__ eps,
+                 int32_t* __restrict__ idx) {
   extern __shared__ int perm[];  // [n_total] + [B] when idx is produced
   __shared__ Key site_key[SMI_MAX_SITES];
   __shared__ Key plate_key;
@@ -28,22 +29,22 @@ prng_step_kernel(const SmiModelDesc md, const uint32_t* __restrict__ key_in, uin
   if (threadIdx.x == 0) {
     const Key state = {key_in[0], key_in[1]};
     if (blockIdx.x == 0 && key_out) {
-      const Key nk = split_at(state, 0);
+      const Key nk = split_at(state, 0, 3, legacy);
       key_out[0] = nk.a;
       key_out[1] = nk.b;
     }
-    const Key step = split_at(state, 2);
-    const Key attractive = split_at(step, 0);
-    const Key pk = split_at(attractive, (uint32_t)(row0 + r));
-    const Key dk = split_at(pk, (uint32_t)s);
-    Key key = split_at(dk, 0);  // guide key
+    const Key step = split_at(state, 2, 3, legacy);
+    const Key attractive = split_at(step, 0, 2, legacy);
+    const Key pk = split_at(attractive, (uint32_t)(row0 + r), (uint32_t)m, legacy);
+    const Key dk = split_at(pk, (uint32_t)s, (uint32_t)S, legacy);
+    Key key = split_at(dk, 0, 2, legacy);  // guide key
     if (n_total > 0) {          // the data plate consumes the first subkey
-      plate_key = split_at(key, 1);
-      key = split_at(key, 0);
+      plate_key = split_at(key, 1, 2, legacy);
+      key = split_at(key, 0, 2, legacy);
     }
     for (int t = 0; t < md.n_sites; ++t) {
-      site_key[t] = split_at(key, 1);
-      key = split_at(key, 0);
+      site_key[t] = split_at(key, 1, 2, legacy);
+      key = split_at(key, 0, 2, legacy);
     }
   }
   __syncthreads();
@@ -52,15 +53,15 @@ prng_step_kernel(const SmiModelDesc md, const uint32_t* __restrict__ key_in, uin
     for (int t = 0; t < md.n_sites; ++t) {
       const Key k = site_key[t];
       const int n = md.sites[t].size, off = md.sites[t].lat;
-      for (int q = threadIdx.x; q < n; q += blockDim.x) out[off + q] = normal_from_bits(bits_at(k, (uint32_t)q));
+      for (int q = threadIdx.x; q < n; q += blockDim.x) out[off + q] = normal_from_bits(bits_at(k, (uint32_t)q, (uint32_t)n, legacy));
     }
   }
   if (idx) {
     int* jt = perm + n_total;
     for (int t = threadIdx.x; t < n_total; t += blockDim.x) perm[t] = t;
     for (int t = threadIdx.x; t < B; t += blockDim.x) {
-      const Key kt = split_at(plate_key, (uint32_t)t);
-      const uint32_t bits = bits_at(kt, 0u);
+      const Key kt = split_at(plate_key, (uint32_t)t, (uint32_t)B, legacy);
+      const uint32_t bits = bits_at(kt, 0u, 1u, legacy);
       jt[t] = (int)(((unsigned long long)bits * (unsigned long long)(n_total - t)) >> 32);
     }
     __syncthreads();
@@ -78,11 +79,11 @@ prng_step_kernel(const SmiModelDesc md, const uint32_t* __restrict__ key_in, uin
   }
 }
 
-__global__ void prng_split_kernel(const uint32_t* __restrict__ key, int num, uint32_t* __restrict__ out) {
+__global__ void prng_split_kernel(const uint32_t* __restrict__ key, int num, int legacy, uint32_t* __restrict__ out) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= num) return;
   const Key k = {key[0], key[1]};
-  const Key r = split_at(k, (uint32_t)j);
+  const Key r = split_at(k, (uint32_t)j, (uint32_t)num, legacy);
   out[2 * j] = r.a;
   out[2 * j + 1] = r.b;
 }
@@ -90,13 +91,18 @@ __global__ void prng_split_kernel(const uint32_t* __restrict__ key, int num, uin
 // MODE 0: raw bits, 1: uniform [lo, hi), 2: normal
 template <int MODE>
 __global__ void __launch_bounds__(256)
-prng_fill_kernel(const uint32_t* __restrict__ key, size_t n, float lo, float hi, void* __restrict__ out) {
+prng_fill_kernel(const uint32_t* __restrict__ key, size_t n, float lo, float hi, int legacy, void* __restrict__ out) {
   const Key k = {key[0], key[1]};
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    uint32_t o0, o1;
-    threefry2x32(k.a, k.b, (uint32_t)(i >> 32), (uint32_t)i, o0, o1);
-    const uint32_t bits = o0 ^ o1;
+    uint32_t bits;
+    if (legacy) {   // flat shapes below 2^32 words (checked by the callers)
+      bits = bits_at(k, (uint32_t)i, (uint32_t)n, 1);
+    } else {
+      uint32_t o0, o1;
+      threefry2x32(k.a, k.b, (uint32_t)(i >> 32), (uint32_t)i, o0, o1);
+      bits = o0 ^ o1;
+    }
     if (MODE == 0) {
       ((uint32_t*)out)[i] = bits;
     } else if (MODE == 1) {
@@ -119,7 +125,7 @@ int fill_grid(size_t n) {
 SMI_API int smi_prng_split(const uint32_t* key, int num, uint32_t* keys_out, void* stream) {
   if (!key || !keys_out || num < 1) SMI_FAIL(SMI_EINVAL, "smi_prng_split: bad argument");
   SMI_PROF_BEGIN((cudaStream_t)stream);
-  prng_split_kernel<<<(num + 127) / 128, 128, 0, (cudaStream_t)stream>>>(key, num, keys_out);
+  prng_split_kernel<<<(num + 127) / 128, 128, 0, (cudaStream_t)stream>>>(key, num, g_smi_prng_legacy, keys_out);
   SMI_LAUNCH_OK_N("prng_split_kernel", (cudaStream_t)stream);
   return SMI_OK;
 }
@@ -127,8 +133,9 @@ SMI_API int smi_prng_split(const uint32_t* key, int num, uint32_t* keys_out, voi
 SMI_API int smi_prng_uniform_f32(const uint32_t* key, size_t n, float lo, float hi, float* out, void* stream) {
   if (!key || !out) SMI_FAIL(SMI_EINVAL, "smi_prng_uniform_f32: null pointer");
   if (n == 0) return SMI_OK;
+  if (g_smi_prng_legacy && n >= (1ull << 32)) SMI_FAIL(SMI_ELIMIT, "legacy PRNG layout: at most 2^32 - 1 words per call");
   SMI_PROF_BEGIN((cudaStream_t)stream);
-  prng_fill_kernel<1><<<fill_grid(n), 256, 0, (cudaStream_t)stream>>>(key, n, lo, hi, out);
+  prng_fill_kernel<1><<<fill_grid(n), 256, 0, (cudaStream_t)stream>>>(key, n, lo, hi, g_smi_prng_legacy, out);
   SMI_LAUNCH_OK_N("prng_fill_kernel", (cudaStream_t)stream);
   return SMI_OK;
 }
@@ -136,8 +143,9 @@ SMI_API int smi_prng_uniform_f32(const uint32_t* key, size_t n, float lo, float 
 SMI_API int smi_prng_normal_f32(const uint32_t* key, size_t n, float* out, void* stream) {
   if (!key || !out) SMI_FAIL(SMI_EINVAL, "smi_prng_normal_f32: null pointer");
   if (n == 0) return SMI_OK;
+  if (g_smi_prng_legacy && n >= (1ull << 32)) SMI_FAIL(SMI_ELIMIT, "legacy PRNG layout: at most 2^32 - 1 words per call");
   SMI_PROF_BEGIN((cudaStream_t)stream);
-  prng_fill_kernel<2><<<fill_grid(n), 256, 0, (cudaStream_t)stream>>>(key, n, 0.f, 1.f, out);
+  prng_fill_kernel<2><<<fill_grid(n), 256, 0, (cudaStream_t)stream>>>(key, n, 0.f, 1.f, g_smi_prng_legacy, out);
   SMI_LAUNCH_OK_N("prng_fill_kernel", (cudaStream_t)stream);
   return SMI_OK;
 }
@@ -145,8 +153,9 @@ SMI_API int smi_prng_normal_f32(const uint32_t* key, size_t n, float* out, void*
 SMI_API int smi_prng_bits_u32(const uint32_t* key, size_t n, uint32_t* out, void* stream) {
   if (!key || !out) SMI_FAIL(SMI_EINVAL, "smi_prng_bits_u32: null pointer");
   if (n == 0) return SMI_OK;
+  if (g_smi_prng_legacy && n >= (1ull << 32)) SMI_FAIL(SMI_ELIMIT, "legacy PRNG layout: at most 2^32 - 1 words per call");
   SMI_PROF_BEGIN((cudaStream_t)stream);
-  prng_fill_kernel<0><<<fill_grid(n), 256, 0, (cudaStream_t)stream>>>(key, n, 0.f, 1.f, out);
+  prng_fill_kernel<0><<<fill_grid(n), 256, 0, (cudaStream_t)stream>>>(key, n, 0.f, 1.f, g_smi_prng_legacy, out);
   SMI_LAUNCH_OK_N("prng_fill_kernel", (cudaStream_t)stream);
   return SMI_OK;
 }
@@ -166,8 +175,14 @@ SMI_API int smi_prng_step_f32(const SmiModelDesc* md, const uint32_t* key_in, ui
       SMI_CUDA_OK(cudaFuncSetAttribute(prng_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   }
   SMI_PROF_BEGIN((cudaStream_t)stream);
-  prng_step_kernel<<<nrows * S, 256, smem, (cudaStream_t)stream>>>(*md, key_in, key_out, m, S, n_total, B, row0, eps,
-                                                                   idx);
+  prng_step_kernel<<<nrows * S, 256, smem, (cudaStream_t)stream>>>(*md, key_in, key_out, m, S, n_total, B, row0,
+                                                                   g_smi_prng_legacy, eps, idx);
   SMI_LAUNCH_OK_N("prng_step_kernel", (cudaStream_t)stream);
   return SMI_OK;
+}
+
+SMI_API int smi_prng_layout(int layout) {
+  const int prev = g_smi_prng_legacy ? SMI_PRNG_LEGACY : SMI_PRNG_PARTITIONABLE;
+  if (layout == SMI_PRNG_LEGACY || layout == SMI_PRNG_PARTITIONABLE) g_smi_prng_legacy = layout == SMI_PRNG_LEGACY;
+  return prev;
 }

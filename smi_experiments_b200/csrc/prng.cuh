@@ -42,17 +42,36 @@ struct Key {
   uint32_t a, b;
 };
 
-// jax.random.split(key, n)[j], partitionable layout: threefry(key, (0, j)).
-__device__ __forceinline__ Key split_at(Key k, uint32_t j) {
-  Key r;
-  threefry2x32(k.a, k.b, 0u, j, r.a, r.b);
-  return r;
-}
-// random_bits(key, 32, shape)[j] for a flat shape with fewer than 2^32 elements.
-__device__ __forceinline__ uint32_t bits_at(Key k, uint32_t j) {
+// Two stream layouts (jax_threefry_partitionable flipped its default in JAX 0.5.0 and the reference leaves
+// JAX unpinned):
+//   partitionable: word j of any flat shape = out0 ^ out1 of threefry(key, (0, j)); split(key, n)[j] = threefry(key, (0, j))
+//   legacy       : counters iota(n) (zero-padded to even) cut in two halves (x0, x1); the outputs are
+//                  concat(out0, out1)[:n]; split(key, n) = the 2n words reshaped (n, 2)
+// `legacy` is warp-uniform everywhere it is used.
+__device__ __forceinline__ uint32_t bits_at(Key k, uint32_t j, uint32_t n, int legacy) {
   uint32_t o0, o1;
-  threefry2x32(k.a, k.b, 0u, j, o0, o1);
-  return o0 ^ o1;
+  if (!legacy) {
+    threefry2x32(k.a, k.b, 0u, j, o0, o1);
+    return o0 ^ o1;
+  }
+  const uint32_t half = (n + 1u) >> 1;
+  if (j < half) {
+    threefry2x32(k.a, k.b, j, j + half < n ? j + half : 0u, o0, o1);
+    return o0;
+  }
+  threefry2x32(k.a, k.b, j - half, j, o0, o1);
+  return o1;
+}
+// jax.random.split(key, num)[j]
+__device__ __forceinline__ Key split_at(Key k, uint32_t j, uint32_t num, int legacy) {
+  Key r;
+  if (!legacy) {
+    threefry2x32(k.a, k.b, 0u, j, r.a, r.b);
+  } else {
+    r.a = bits_at(k, 2u * j, 2u * num, 1);
+    r.b = bits_at(k, 2u * j + 1u, 2u * num, 1);
+  }
+  return r;
 }
 
 // Giles' single-precision erfinv (the polynomial XLA lowers erf_inv(f32) to).

@@ -158,6 +158,16 @@ def asvgd_tau(step, step0, num_steps, num_cycles, trans_speed, m, out):
          _ptr(out), _stream())
 
 
+PRNG_LAYOUTS = {"partitionable": 1, "legacy": 0}   # SMI_PRNG_PARTITIONABLE / SMI_PRNG_LEGACY
+
+
+def set_prng_layout(layout):
+    """Threefry stream layout of every PRNG launch (jax_threefry_partitionable on / off; JAX >= 0.5 / older).
+    Process-wide.  Returns the previous layout's name; ``None`` only queries."""
+    code = load().smi_prng_layout(-1 if layout is None else PRNG_LAYOUTS[layout])
+    return "partitionable" if code == 1 else "legacy"
+
+
 def prng_step(md, key_in, key_out, m, S, n_total=0, B=0, row0=0, nrows=None, eps=None, idx=None):
     """threefry key chain of one update: fills eps (nrows, S, L) / idx (nrows, S, B), next key.  row a9."""
     _need_cuda(key_in, key_out, eps, idx)

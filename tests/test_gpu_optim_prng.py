@@ -58,28 +58,40 @@ def _key(dev, k):
     return torch.from_numpy(np.asarray(k, np.uint32).view(np.int32).copy()).to(dev)
 
 
-def test_prng_primitives_bit_exact(cuda, lib):
+@pytest.fixture(params=["partitionable", "legacy"])
+def layout(request):
+    """Both jax_threefry_partitionable stream layouts (row n2); restores the default afterwards."""
+    from smi_experiments_b200 import ops
+    prev = ops.set_prng_layout(request.param)
+    yield oprng.LAYOUT_PARTITIONABLE if request.param == "partitionable" else oprng.LAYOUT_LEGACY
+    ops.set_prng_layout(prev)
+
+
+def test_prng_primitives_bit_exact(cuda, lib, layout):
     from smi_experiments_b200 import ops
     key = np.array([0x13198a2e, 0x03707344], np.uint32)
     kt = _key(cuda, key)
     out = torch.empty(7, 2, dtype=torch.int32, device=cuda)
     ops.call("smi_prng_split", ops._ptr(kt), 7, ops._ptr(out), ops._stream())
-    assert (out.cpu().numpy().view(np.uint32) == oprng.split(key, 7)).all()
+    assert (out.cpu().numpy().view(np.uint32) == oprng.split(key, 7, layout)).all()
     n = 100_003
     bits = torch.empty(n, dtype=torch.int32, device=cuda)
     ops.call("smi_prng_bits_u32", ops._ptr(kt), n, ops._ptr(bits), ops._stream())
-    assert (bits.cpu().numpy().view(np.uint32) == oprng.random_bits(key, n)).all()
+    assert (bits.cpu().numpy().view(np.uint32) == oprng.random_bits(key, n, layout)).all()
     u = torch.empty(n, dtype=torch.float32, device=cuda)
     ops.call("smi_prng_uniform_f32", ops._ptr(kt), n, -0.1, 0.1, ops._ptr(u), ops._stream())
-    assert (u.cpu().numpy() == oprng.uniform(key, n, -0.1, 0.1)).all()
+    assert (u.cpu().numpy() == oprng.uniform(key, n, -0.1, 0.1, layout)).all()
     z = torch.empty(n, dtype=torch.float32, device=cuda)
     ops.call("smi_prng_normal_f32", ops._ptr(kt), n, ops._ptr(z), ops._stream())
     # erfinv polynomial: device uses fused multiply-adds, numpy does not -> a few ulp
-    np.testing.assert_allclose(z.cpu().numpy(), oprng.normal(key, n), rtol=2e-6, atol=2e-7)
+    np.testing.assert_allclose(z.cpu().numpy(), oprng.normal(key, n, layout), rtol=2e-6, atol=2e-7)
+    # an even word count takes the other branch of the legacy halves
+    ops.call("smi_prng_bits_u32", ops._ptr(kt), 1000, ops._ptr(bits), ops._stream())
+    assert (bits[:1000].cpu().numpy().view(np.uint32) == oprng.random_bits(key, 1000, layout)).all()
 
 
 @pytest.mark.parametrize("case", ["uci", "gauss_delta", "cls"])
-def test_prng_step_chain(cuda, case):
+def test_prng_step_chain(cuda, case, layout):
     """Key chain of one update: indices bit-exact, normals to a few ulp, next key bit-exact."""
     from smi_experiments_b200 import models, ops, _lib
     if case == "uci":
@@ -93,7 +105,7 @@ def test_prng_step_chain(cuda, case):
         m, S, N, B = 4, 1, 0, None
     md, lay = models.make_desc(pm, gk)
     key = np.array([7, 42], np.uint32)
-    next_key, attractive = ostep.draw_keys(key)
+    next_key, attractive = ostep.draw_keys(key, layout)
     kin, kout = _key(cuda, key), torch.zeros(2, dtype=torch.int32, device=cuda)
     eps = torch.empty(m, S, lay.latent_dim, dtype=torch.float32, device=cuda) if guide == "normal" else None
     idx = torch.empty(m, S, B, dtype=torch.int32, device=cuda) if B else None
@@ -101,9 +113,9 @@ def test_prng_step_chain(cuda, case):
     assert (kout.cpu().numpy().view(np.uint32) == next_key).all()
     if case == "cls":
         # the plate consumes a subkey although no indices are produced: emulate with b = 1
-        e_ref, _ = ostep.draw_noise(attractive, m, S, om, guide, N, 1)
+        e_ref, _ = ostep.draw_noise(attractive, m, S, om, guide, N, 1, layout)
     else:
-        e_ref, i_ref = ostep.draw_noise(attractive, m, S, om, guide, N if B else None, B)
+        e_ref, i_ref = ostep.draw_noise(attractive, m, S, om, guide, N if B else None, B, layout)
     if idx is not None:
         assert (idx.cpu().numpy() == i_ref).all()
         assert all(len(set(r)) == B for r in idx.cpu().numpy().reshape(-1, B))

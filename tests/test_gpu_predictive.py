@@ -26,9 +26,21 @@ def _particles(smi, model, guide, m, seed):
     return psi
 
 
-@pytest.mark.parametrize("which,S,n", [("uci", 64, 23), ("uci", 7, 1), ("sine", 40, 40)])
-def test_mixture_predictive_matches_oracle(cuda, which, S, n):
+@pytest.mark.parametrize("which,S,n,layout", [("uci", 64, 23, "partitionable"), ("uci", 7, 1, "partitionable"),
+                                              ("sine", 40, 40, "partitionable"), ("uci", 64, 23, "legacy"),
+                                              ("sine", 7, 40, "legacy")])
+def test_mixture_predictive_matches_oracle(cuda, which, S, n, layout):
     import smi_experiments_b200 as smi
+    from oracle import prng as oprng
+    prev = smi.set_prng_layout(layout)
+    try:
+        _mixture_predictive_case(cuda, smi, which, S, n,
+                                 oprng.LAYOUT_LEGACY if layout == "legacy" else oprng.LAYOUT_PARTITIONABLE)
+    finally:
+        smi.set_prng_layout(prev)
+
+
+def _mixture_predictive_case(cuda, smi, which, S, n, layout_mode):
     if which == "uci":
         model, spec, I = smi.uci_bnn(6), om.uci_bnn(6), 6
     else:
@@ -46,7 +58,7 @@ def test_mixture_predictive_matches_oracle(cuda, which, S, n):
     pred = smi.MixtureGuidePredictive(model, guide, St, num_samples=S)
     out = pred(smi.PRNGKey(11), x, y)
     ref = op.predictive_reg(spec, psi.numpy().astype(np.float64), [0, 11], S, x.astype(np.float64),
-                            y.astype(np.float64))
+                            y.astype(np.float64), layout_mode=layout_mode)
     assert np.array_equal(out["_assign"].cpu().numpy(), ref["assign"])                    # bit-exact
     lat = torch.cat([out[s.name].reshape(S, -1) for s in model.sites()], 1).cpu().numpy()
     assert rel(lat, ref["latents"]) <= TOL
