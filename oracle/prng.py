@@ -119,6 +119,20 @@ def normal(key, n, layout=LAYOUT_PARTITIONABLE):
     return normal_from_bits(random_bits(key, n, layout))
 
 
+def randint_jax(key, span, layout=LAYOUT_PARTITIONABLE):
+    """jax.random.randint(key, (), 0, span) for int32 (jax/_src/random.py::_randint): two words from
+    split(key); ((hi % span) * (2^32 % span) + lo % span) % span in wrapping uint32 arithmetic."""
+    k = split(key, 2, layout)
+    hi = np.uint32(random_bits(k[0], 1, layout)[0])
+    lo = np.uint32(random_bits(k[1], 1, layout)[0])
+    sp = np.uint32(span)
+    with np.errstate(over="ignore"):
+        mult = np.uint32(65536) % sp
+        mult = np.uint32(mult * mult) % sp
+        off = np.uint32(np.uint32(np.uint32(hi % sp) * mult) + np.uint32(lo % sp)) % sp
+    return int(off)
+
+
 def randint_bits_to_index(bits, span):
     """Uniform integer in [0, span) from one 32-bit word by multiply-shift (device rule)."""
     return ((bits.astype(np.uint64) * np.uint64(span)) >> np.uint64(32)).astype(np.int32)

@@ -25,7 +25,7 @@ def draw_keys(state_key, layout_mode=prng.LAYOUT_PARTITIONABLE):
     return next_key, attractive_key
 
 
-def subsample_indices(key, n_total, b, layout_mode=prng.LAYOUT_PARTITIONABLE):
+def subsample_indices(key, n_total, b, layout_mode=prng.LAYOUT_PARTITIONABLE, randint="mulshift"):
     """Partial Fisher-Yates over arange(n_total): slot t swaps positions (n-1-t, j_t),
     j_t uniform in [0, n-t); returns the last b entries.  j_t is drawn from ONE 32-bit word of
     split(key, b)[t] by multiply-shift (device rule) -- jax.random.randint's two-word
@@ -34,15 +34,18 @@ def subsample_indices(key, n_total, b, layout_mode=prng.LAYOUT_PARTITIONABLE):
     val = np.arange(n_total, dtype=np.int32)
     for t in range(b):
         span = n_total - t
-        bits = prng.random_bits(keys[t], 1, layout_mode)
-        j = int(prng.randint_bits_to_index(bits, span)[0])
+        if randint == "jax":   # the switch for jax.random.randint's own construction
+            j = prng.randint_jax(keys[t], span, layout_mode)
+        else:
+            bits = prng.random_bits(keys[t], 1, layout_mode)
+            j = int(prng.randint_bits_to_index(bits, span)[0])
         i = span - 1
         val[i], val[j] = val[j], val[i]
     return val[n_total - b:].copy()
 
 
 def draw_noise(attractive_key, m, S, spec, guide="normal", n_total=None, b=None,
-               layout_mode=prng.LAYOUT_PARTITIONABLE):
+               layout_mode=prng.LAYOUT_PARTITIONABLE, randint="mulshift"):
     """eps (m, S, L) float32 and idx (m, S, b) int32 for one step.
     Chain: split(attractive, m)[i] -> split(., S)[s] -> split(., 2)[0] = guide key; the seed
     handler then peels one subkey per RNG-consuming statement: the data plate (if subsampled)
@@ -58,7 +61,7 @@ def draw_noise(attractive_key, m, S, spec, guide="normal", n_total=None, b=None,
             if b is not None:
                 pair = prng.split(key, 2, layout_mode)
                 key, sub = pair[0], pair[1]
-                idx[i, s] = subsample_indices(sub, n_total, b, layout_mode)
+                idx[i, s] = subsample_indices(sub, n_total, b, layout_mode, randint)
             if guide == "normal":
                 for r in rows:
                     pair = prng.split(key, 2, layout_mode)

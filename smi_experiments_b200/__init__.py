@@ -18,4 +18,4 @@ from .steinvi import ASVGD, SVGD, PRNGKey, SteinVI, SteinVIRunResult, SteinVISta
 
 __version__ = "0.1.0"
 from .logger import ClassExpLogger, ExpLogger  # noqa: F401
-from .ops import set_prng_layout  # noqa: F401
+from .ops import set_prng_layout, set_randint_rule  # noqa: F401

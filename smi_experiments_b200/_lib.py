@@ -83,6 +83,7 @@ PROTOTYPES = {
     "smi_asvgd_tau_f32": (_I, [_P, _I, _I, _I, _I, _I, _P, _P]),
     "smi_prng_step_f32": (_I, [_MD, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
     "smi_prng_layout": (_I, [_I]),
+    "smi_prng_randint": (_I, [_I]),
     "smi_prng_split": (_I, [_P, _I, _P, _P]),
     "smi_prng_uniform_f32": (_I, [_P, _Z, _F, _F, _P, _P]),
     "smi_prng_normal_f32": (_I, [_P, _Z, _P, _P]),

@@ -15,6 +15,7 @@ void smi_set_error(const char* fmt, ...) {
 
 thread_local long long g_smi_launches = 0;
 int g_smi_prng_legacy = 0;
+int g_smi_randint_jax = 0;
 
 SMI_API long long smi_launch_count(int reset) {
   const long long v = g_smi_launches;

@@ -25,6 +25,7 @@ void smi_set_error(const char* fmt, ...);
   } while (0)
 
 extern thread_local long long g_smi_launches;
+extern int g_smi_randint_jax;    // subsample index rule (smi_prng_randint)
 extern int g_smi_prng_legacy;   // threefry stream layout of every PRNG launch (smi_prng_layout)
 #define SMI_LAUNCH_OK()                 \
   do {                                  \

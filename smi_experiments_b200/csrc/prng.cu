@@ -19,7 +19,7 @@ using namespace smi_prng;
 
 __global__ void __launch_bounds__(256)
 prng_step_kernel(const SmiModelDesc md, const uint32_t* __restrict__ key_in, uint32_t* __restrict__ key_out,
-                 int m, int S, int n_total, int B, int row0, int legacy, float* __restrict__ eps,
+                 int m, int S, int n_total, int B, int row0, int legacy, int randint_jax, float* __restrict__ eps,
                  int32_t* __restrict__ idx) {
   extern __shared__ int perm[];  // [n_total] + [B] when idx is produced
   __shared__ Key site_key[SMI_MAX_SITES];
@@ -61,8 +61,19 @@ prng_step_kernel(const SmiModelDesc md, const uint32_t* __restrict__ key_in, uin
     for (int t = threadIdx.x; t < n_total; t += blockDim.x) perm[t] = t;
     for (int t = threadIdx.x; t < B; t += blockDim.x) {
       const Key kt = split_at(plate_key, (uint32_t)t, (uint32_t)B, legacy);
-      const uint32_t bits = bits_at(kt, 0u, 1u, legacy);
-      jt[t] = (int)(((unsigned long long)bits * (unsigned long long)(n_total - t)) >> 32);
+      const uint32_t span = (uint32_t)(n_total - t);
+      if (!randint_jax) {   // one word, multiply-shift
+        const uint32_t bits = bits_at(kt, 0u, 1u, legacy);
+        jt[t] = (int)(((unsigned long long)bits * (unsigned long long)span) >> 32);
+      } else {
+        // jax.random.randint(key, (), 0, span): two words from split(key), (hi % span) * (2^32 % span) + lo % span
+        // in wrapping uint32 arithmetic, % span
+        const uint32_t hi = bits_at(split_at(kt, 0, 2, legacy), 0u, 1u, legacy);
+        const uint32_t lo = bits_at(split_at(kt, 1, 2, legacy), 0u, 1u, legacy);
+        uint32_t mult = 65536u % span;
+        mult = (mult * mult) % span;
+        jt[t] = (int)(((hi % span) * mult + lo % span) % span);
+      }
     }
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -176,7 +187,7 @@ SMI_API int smi_prng_step_f32(const SmiModelDesc* md, const uint32_t* key_in, ui
   }
   SMI_PROF_BEGIN((cudaStream_t)stream);
   prng_step_kernel<<<nrows * S, 256, smem, (cudaStream_t)stream>>>(*md, key_in, key_out, m, S, n_total, B, row0,
-                                                                   g_smi_prng_legacy, eps, idx);
+                                                                   g_smi_prng_legacy, g_smi_randint_jax, eps, idx);
   SMI_LAUNCH_OK_N("prng_step_kernel", (cudaStream_t)stream);
   return SMI_OK;
 }
@@ -184,5 +195,11 @@ SMI_API int smi_prng_step_f32(const SmiModelDesc* md, const uint32_t* key_in, ui
 SMI_API int smi_prng_layout(int layout) {
   const int prev = g_smi_prng_legacy ? SMI_PRNG_LEGACY : SMI_PRNG_PARTITIONABLE;
   if (layout == SMI_PRNG_LEGACY || layout == SMI_PRNG_PARTITIONABLE) g_smi_prng_legacy = layout == SMI_PRNG_LEGACY;
+  return prev;
+}
+
+SMI_API int smi_prng_randint(int mode) {
+  const int prev = g_smi_randint_jax ? SMI_RANDINT_JAX : SMI_RANDINT_MULSHIFT;
+  if (mode == SMI_RANDINT_JAX || mode == SMI_RANDINT_MULSHIFT) g_smi_randint_jax = mode == SMI_RANDINT_JAX;
   return prev;
 }

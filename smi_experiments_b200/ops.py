@@ -168,6 +168,13 @@ def set_prng_layout(layout):
     return "partitionable" if code == 1 else "legacy"
 
 
+def set_randint_rule(rule):
+    """Index rule of the data-plate subsample: "mulshift" (one word, default) or "jax" (jax.random.randint's
+    two-word construction).  Process-wide.  Returns the previous rule's name; ``None`` only queries."""
+    code = load().smi_prng_randint(-1 if rule is None else {"mulshift": 0, "jax": 1}[rule])
+    return "jax" if code == 1 else "mulshift"
+
+
 def prng_step(md, key_in, key_out, m, S, n_total=0, B=0, row0=0, nrows=None, eps=None, idx=None):
     """threefry key chain of one update: fills eps (nrows, S, L) / idx (nrows, S, B), next key.  row a9."""
     _need_cuda(key_in, key_out, eps, idx)

@@ -136,3 +136,29 @@ def test_prng_step_row_sharding(cuda):
     i2 = torch.empty(2, S, B, dtype=torch.int32, device=cuda)
     ops.prng_step(md, kin, kout, m, S, N, B, 2, 2, e2, i2)
     assert torch.equal(e2, eps[2:4]) and torch.equal(i2, idx[2:4])
+
+
+@pytest.mark.parametrize("layout_name", ["partitionable", "legacy"])
+def test_subsample_jax_randint_rule(cuda, layout_name):
+    """Switch: j_t drawn as jax.random.randint does (two words, modular) instead of one-word multiply-shift."""
+    from smi_experiments_b200 import models, ops, _lib
+    pm, om_ = models.uci_bnn(3), omodels.uci_bnn(3)
+    md, lay = models.make_desc(pm, _lib.GUIDE_NORMAL)
+    m, S, N, B = 2, 3, 91, 17
+    key = np.array([5, 77], np.uint32)
+    lm = oprng.LAYOUT_PARTITIONABLE if layout_name == "partitionable" else oprng.LAYOUT_LEGACY
+    prev_l, prev_r = ops.set_prng_layout(layout_name), ops.set_randint_rule("jax")
+    try:
+        kin, kout = _key(cuda, key), torch.zeros(2, dtype=torch.int32, device=cuda)
+        idx = torch.empty(m, S, B, dtype=torch.int32, device=cuda)
+        ops.prng_step(md, kin, kout, m, S, N, B, 0, m, None, idx)
+        _, attractive = ostep.draw_keys(key, lm)
+        _, i_ref = ostep.draw_noise(attractive, m, S, om_, "normal", N, B, lm, randint="jax")
+        got = idx.cpu().numpy()
+        assert (got == i_ref).all()
+        assert all(len(set(r)) == B and 0 <= min(r) and max(r) < N for r in got.reshape(-1, B))
+        _, i_ms = ostep.draw_noise(attractive, m, S, om_, "normal", N, B, lm)
+        assert (got != i_ms).any()
+    finally:
+        ops.set_prng_layout(prev_l)
+        ops.set_randint_rule(prev_r)
