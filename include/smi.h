@@ -236,12 +236,17 @@ int smi_prng_step_f32(const SmiModelDesc* md, const uint32_t* key_in, uint32_t* 
 #define SMI_PRNG_PARTITIONABLE 1
 #define SMI_PRNG_LEGACY 0
 int smi_prng_layout(int layout);
-/* Index rule of the data-plate subsample (numpyro/primitives.py::_subsample_fn, CPU branch: j_t =
- * random.randint(split(key, B)[t], (), 0, n - t)).  MULSHIFT (default): one 32-bit word, (bits * span) >> 32.
- * JAX: jax.random.randint's construction -- two words from split(key), ((hi % span) * (2^32 % span) + lo % span)
- * % span in wrapping uint32 arithmetic.  Process-wide; returns the previous rule; any other argument queries. */
+/* Rule of the data-plate subsample (numpyro/primitives.py::_subsample_fn).
+ *   CPU backend of the reference: partial Fisher-Yates, j_t = random.randint(split(key, B)[t], (), 0, n - t):
+ *     MULSHIFT (default): one 32-bit word, (bits * span) >> 32.
+ *     JAX: jax.random.randint's construction -- two words from split(key), ((hi % span) * (2^32 % span) +
+ *          lo % span) % span in wrapping uint32 arithmetic.
+ *   Any other backend of the reference: CHOICE = jax.random.choice(key, n, (B,), replace=False) =
+ *     permutation(key, n)[:B], rounds of a stable sort by fresh 32-bit words (n <= 16384 here).
+ * Process-wide; returns the previous rule; any other argument queries.                                       */
 #define SMI_RANDINT_MULSHIFT 0
 #define SMI_RANDINT_JAX 1
+#define SMI_RANDINT_CHOICE 2
 int smi_prng_randint(int mode);
 
 /* jax.random primitives on the device (layout per smi_prng_layout), used by engine.init

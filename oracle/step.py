@@ -30,6 +30,16 @@ def subsample_indices(key, n_total, b, layout_mode=prng.LAYOUT_PARTITIONABLE, ra
     j_t uniform in [0, n-t); returns the last b entries.  j_t is drawn from ONE 32-bit word of
     split(key, b)[t] by multiply-shift (device rule) -- jax.random.randint's two-word
     modular construction is NOT reproduced [NP?]."""
+    if randint == "choice":
+        # the branch _subsample_fn takes off the CPU backend: random.choice(key, n, (b,), replace=False)
+        # = permutation(key, n)[:b]; jax/_src/random.py::_shuffle: rounds of a stable sort by fresh words
+        rounds = int(np.ceil(3 * np.log(max(1, n_total)) / np.log(np.iinfo(np.uint32).max)))
+        x = np.arange(n_total, dtype=np.int32)
+        for _ in range(rounds):
+            pair = prng.split(key, 2, layout_mode)
+            key, sub = pair[0], pair[1]
+            x = x[np.argsort(prng.random_bits(sub, n_total, layout_mode), kind="stable")]
+        return x[:b].copy()
     keys = prng.split(key, b, layout_mode)
     val = np.arange(n_total, dtype=np.int32)
     for t in range(b):

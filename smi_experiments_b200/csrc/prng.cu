@@ -21,7 +21,7 @@ __global__ void __launch_bounds__(256)
 prng_step_kernel(const SmiModelDesc md, const uint32_t* __restrict__ key_in, uint32_t* __restrict__ key_out,
                  int m, int S, int n_total, int B, int row0, int legacy, int randint_jax, float* __restrict__ eps,
                  int32_t* __restrict__ idx) {
-  extern __shared__ int perm[];  // [n_total] + [B] when idx is produced
+  extern __shared__ __align__(8) int perm[];  // [n_total] + [B] when idx is produced (sort buffers for the choice rule)
   __shared__ Key site_key[SMI_MAX_SITES];
   __shared__ Key plate_key;
   const int r = blockIdx.x / S, s = blockIdx.x - r * S;
@@ -56,13 +56,55 @@ prng_step_kernel(const SmiModelDesc md, const uint32_t* __restrict__ key_in, uin
       for (int q = threadIdx.x; q < n; q += blockDim.x) out[off + q] = normal_from_bits(bits_at(k, (uint32_t)q, (uint32_t)n, legacy));
     }
   }
-  if (idx) {
+  if (idx && randint_jax == SMI_RANDINT_CHOICE) {
+    // _subsample_fn off the CPU backend: jax.random.choice(key, n, (B,), replace=False) = permutation(key, n)[:B];
+    // permutation = ceil(3 ln n / ln(2^32 - 1)) rounds of a STABLE sort of the current order by fresh 32-bit
+    // words (jax/_src/random.py::_shuffle).  Sorted here as 64-bit (word << 32 | position): unique keys make
+    // the bitonic network stable.
+    int P = 1;
+    while (P < n_total) P <<= 1;
+    unsigned long long* sk = reinterpret_cast<unsigned long long*>(perm);   // [P]
+    int* cur = reinterpret_cast<int*>(sk + P);                               // [n_total] current order
+    int* nxt = cur + n_total;                                                // [n_total]
+    const int rounds = (int)ceil(3.0 * log((double)max(1, n_total)) / log(4294967295.0));
+    for (int t = threadIdx.x; t < n_total; t += blockDim.x) cur[t] = t;
+    Key k = plate_key;
+    for (int rd = 0; rd < rounds; ++rd) {
+      const Key sub = split_at(k, 1, 2, legacy);
+      k = split_at(k, 0, 2, legacy);
+      for (int t = threadIdx.x; t < P; t += blockDim.x)
+        sk[t] = t < n_total ? ((unsigned long long)bits_at(sub, (uint32_t)t, (uint32_t)n_total, legacy) << 32) | (unsigned)t
+                            : ~0ull;
+      __syncthreads();
+      for (int kk = 2; kk <= P; kk <<= 1)
+        for (int j = kk >> 1; j > 0; j >>= 1) {
+          for (int t = threadIdx.x; t < P; t += blockDim.x) {
+            const int u = t ^ j;
+            if (u > t) {
+              const unsigned long long a = sk[t], b = sk[u];
+              if ((a > b) == ((t & kk) == 0)) {
+                sk[t] = b;
+                sk[u] = a;
+              }
+            }
+          }
+          __syncthreads();
+        }
+      for (int t = threadIdx.x; t < n_total; t += blockDim.x) nxt[t] = cur[(int)(sk[t] & 0xffffffffull)];
+      __syncthreads();
+      int* tmp = cur;
+      cur = nxt;
+      nxt = tmp;
+    }
+    int32_t* out = idx + ((size_t)r * S + s) * B;
+    for (int b = threadIdx.x; b < B; b += blockDim.x) out[b] = cur[b];
+  } else if (idx) {
     int* jt = perm + n_total;
     for (int t = threadIdx.x; t < n_total; t += blockDim.x) perm[t] = t;
     for (int t = threadIdx.x; t < B; t += blockDim.x) {
       const Key kt = split_at(plate_key, (uint32_t)t, (uint32_t)B, legacy);
       const uint32_t span = (uint32_t)(n_total - t);
-      if (!randint_jax) {   // one word, multiply-shift
+      if (randint_jax != SMI_RANDINT_JAX) {   // one word, multiply-shift
         const uint32_t bits = bits_at(kt, 0u, 1u, legacy);
         jt[t] = (int)(((unsigned long long)bits * (unsigned long long)span) >> 32);
       } else {
@@ -181,6 +223,11 @@ SMI_API int smi_prng_step_f32(const SmiModelDesc* md, const uint32_t* key_in, ui
   if (idx) {
     if (n_total < 1 || B < 1 || B > n_total) SMI_FAIL(SMI_EINVAL, "smi_prng_step_f32: subsample %d of %d", B, n_total);
     smem = ((size_t)n_total + B) * sizeof(int);
+    if (g_smi_randint_jax == SMI_RANDINT_CHOICE) {
+      size_t P = 1;
+      while (P < (size_t)n_total) P <<= 1;
+      smem = P * sizeof(unsigned long long) + 2 * (size_t)n_total * sizeof(int);
+    }
     if (smem > 200 * 1024) SMI_FAIL(SMI_ELIMIT, "smi_prng_step_f32: plate of %d rows exceeds shared memory", n_total);
     if (smem > 48 * 1024)
       SMI_CUDA_OK(cudaFuncSetAttribute(prng_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -199,7 +246,7 @@ SMI_API int smi_prng_layout(int layout) {
 }
 
 SMI_API int smi_prng_randint(int mode) {
-  const int prev = g_smi_randint_jax ? SMI_RANDINT_JAX : SMI_RANDINT_MULSHIFT;
-  if (mode == SMI_RANDINT_JAX || mode == SMI_RANDINT_MULSHIFT) g_smi_randint_jax = mode == SMI_RANDINT_JAX;
+  const int prev = g_smi_randint_jax;
+  if (mode == SMI_RANDINT_JAX || mode == SMI_RANDINT_MULSHIFT || mode == SMI_RANDINT_CHOICE) g_smi_randint_jax = mode;
   return prev;
 }

@@ -168,11 +168,16 @@ def set_prng_layout(layout):
     return "partitionable" if code == 1 else "legacy"
 
 
+SUBSAMPLE_RULES = {"mulshift": 0, "jax": 1, "choice": 2}
+
+
 def set_randint_rule(rule):
-    """Index rule of the data-plate subsample: "mulshift" (one word, default) or "jax" (jax.random.randint's
-    two-word construction).  Process-wide.  Returns the previous rule's name; ``None`` only queries."""
-    code = load().smi_prng_randint(-1 if rule is None else {"mulshift": 0, "jax": 1}[rule])
-    return "jax" if code == 1 else "mulshift"
+    """Rule of the data-plate subsample: partial Fisher-Yates with "mulshift" (one word, default) or "jax"
+    (jax.random.randint's two-word construction) indices -- the reference's CPU-backend branch -- or "choice"
+    (jax.random.choice without replacement = sort-based permutation, its branch on any other backend).
+    Process-wide.  Returns the previous rule's name; ``None`` only queries."""
+    code = load().smi_prng_randint(-1 if rule is None else SUBSAMPLE_RULES[rule])
+    return {v: k for k, v in SUBSAMPLE_RULES.items()}[code]
 
 
 def prng_step(md, key_in, key_out, m, S, n_total=0, B=0, row0=0, nrows=None, eps=None, idx=None):

@@ -138,22 +138,24 @@ def test_prng_step_row_sharding(cuda):
     assert torch.equal(e2, eps[2:4]) and torch.equal(i2, idx[2:4])
 
 
+@pytest.mark.parametrize("rule,N,B", [("jax", 91, 17), ("choice", 91, 17), ("choice", 3000, 64)])
 @pytest.mark.parametrize("layout_name", ["partitionable", "legacy"])
-def test_subsample_jax_randint_rule(cuda, layout_name):
-    """Switch: j_t drawn as jax.random.randint does (two words, modular) instead of one-word multiply-shift."""
+def test_subsample_rules(cuda, layout_name, rule, N, B):
+    """Switches: j_t drawn as jax.random.randint does (two words, modular) instead of one-word multiply-shift;
+    sort-based permutation (random.choice without replacement; 3000 rows need two sort rounds)."""
     from smi_experiments_b200 import models, ops, _lib
     pm, om_ = models.uci_bnn(3), omodels.uci_bnn(3)
     md, lay = models.make_desc(pm, _lib.GUIDE_NORMAL)
-    m, S, N, B = 2, 3, 91, 17
+    m, S = 2, 3
     key = np.array([5, 77], np.uint32)
     lm = oprng.LAYOUT_PARTITIONABLE if layout_name == "partitionable" else oprng.LAYOUT_LEGACY
-    prev_l, prev_r = ops.set_prng_layout(layout_name), ops.set_randint_rule("jax")
+    prev_l, prev_r = ops.set_prng_layout(layout_name), ops.set_randint_rule(rule)
     try:
         kin, kout = _key(cuda, key), torch.zeros(2, dtype=torch.int32, device=cuda)
         idx = torch.empty(m, S, B, dtype=torch.int32, device=cuda)
         ops.prng_step(md, kin, kout, m, S, N, B, 0, m, None, idx)
         _, attractive = ostep.draw_keys(key, lm)
-        _, i_ref = ostep.draw_noise(attractive, m, S, om_, "normal", N, B, lm, randint="jax")
+        _, i_ref = ostep.draw_noise(attractive, m, S, om_, "normal", N, B, lm, randint=rule)
         got = idx.cpu().numpy()
         assert (got == i_ref).all()
         assert all(len(set(r)) == B and 0 <= min(r) and max(r) < N for r in got.reshape(-1, B))
