@@ -372,6 +372,135 @@ guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, 
   }
 }
 
+// 48 < m <= 192: the components are split over four thread groups (thread = latent column x component
+// group), each with its MPC-component tables in registers.  Per batch of 8 draws every thread writes its
+// partial (sum_j w q_j, sum_j w c_j) for the 8 draws to shared memory; after one barrier each thread
+// finishes two of the draws (sums the four partials, applies eps / d log p).  Double-buffered partials:
+// one barrier per batch.  Against the component-streaming kernel below (tables re-read from L2 per chunk,
+// all draws of a thread in registers) this keeps the register-table inner loop of guide_grad_kernel.
+constexpr int kSplitCG = 4, kSplitNB = 8;
+template <int MPC>
+__global__ void __launch_bounds__(256, 2)
+guide_grad_split_kernel(const float* __restrict__ psi, const float* __restrict__ eps, const float* __restrict__ MU,
+                        const float* __restrict__ SIG, const float* __restrict__ ISIG, const float* __restrict__ W,
+                        const float* __restrict__ DZ, const float* __restrict__ LOGP, const float* __restrict__ LOGQ,
+                        const int* __restrict__ loc_of, const int* __restrict__ rho_of, const int* __restrict__ tr_of,
+                        int m, int S, int L, int d, float tau_host, const float* __restrict__ tau_dev, int row0,
+                        float* __restrict__ G, float* __restrict__ elbo) {
+  constexpr int MW = kSplitCG * MPC, KT = kGradKT, NB = kSplitNB;
+  const float tau = tau_dev ? *tau_dev : tau_host;
+  extern __shared__ __align__(16) float sm[];
+  float* wt = sm;                                                     // [S + NB][MW], rows >= S and columns >= m zero
+  float2* part = reinterpret_cast<float2*>(wt + (size_t)(S + NB) * MW);   // [2][NB][CG][KT]
+  float2* red = part + 2 * NB * kSplitCG * KT;                        // [CG][KT]
+  const int kt = blockIdx.x, r = blockIdx.y, i = row0 + r;
+  const int kk = threadIdx.x & (KT - 1), cg = threadIdx.x / KT;
+  const int k = kt * KT + kk;
+  const bool live = k < L;
+  for (int t = threadIdx.x; t < (S + NB) * MW; t += blockDim.x) {
+    const int s = t / MW, j = t - s * MW;
+    wt[t] = (s < S && j < m) ? W[((size_t)r * S + s) * m + j] : 0.f;
+  }
+  float cq[MPC], q[MPC];
+  float mu_i = 0.f, sg_i = 0.f, is_i = 0.f, jac = 0.f;
+  if (live) {
+    mu_i = MU[(size_t)i * L + k], sg_i = SIG[(size_t)i * L + k], is_i = ISIG[(size_t)i * L + k];
+    jac = tr_of[k] == SMI_T_EXP ? 1.f : 0.f;
+  }
+#pragma unroll
+  for (int jj = 0; jj < MPC; ++jj) {
+    const int j = cg * MPC + jj;
+    cq[jj] = 0.f;
+    q[jj] = 0.f;
+    if (live && j < m) {
+      const float is = ISIG[(size_t)j * L + k];
+      q[jj] = is * is;
+      cq[jj] = (mu_i - MU[(size_t)j * L + k]) * q[jj];
+    }
+  }
+  // this thread finishes draws 2 cg, 2 cg + 1 of every batch: their eps / d log p are fetched a batch ahead
+  const float* ebase = eps + (size_t)r * S * L + k;
+  const float* dbase = DZ + (size_t)r * S * L + k;
+  float epn[2], dzn[2];
+#pragma unroll
+  for (int f = 0; f < 2; ++f) {
+    const int s = 2 * cg + f;
+    epn[f] = (live && s < S) ? __ldcs(ebase + (size_t)s * L) : 0.f;
+    dzn[f] = (live && s < S) ? __ldcs(dbase + (size_t)s * L) : 0.f;
+  }
+  __syncthreads();
+  float gl = 0.f, gs = 0.f;
+  const int nbatch = (S + NB - 1) / NB;
+  for (int b = 0; b < nbatch; ++b) {
+    const int s0 = b * NB;
+    float2* pb = part + (size_t)(b & 1) * NB * kSplitCG * KT;
+#pragma unroll
+    for (int u = 0; u < NB; ++u) {
+      const float* row = wt + (size_t)(s0 + u) * MW + cg * MPC;   // warp-uniform: broadcast reads
+      float a1 = 0.f, a2 = 0.f;
+#pragma unroll
+      for (int j4 = 0; j4 < MPC; j4 += 4) {
+        const float4 w4 = *reinterpret_cast<const float4*>(row + j4);
+        a1 = fmaf(w4.x, q[j4], a1);
+        a2 = fmaf(w4.x, cq[j4], a2);
+        a1 = fmaf(w4.y, q[j4 + 1], a1);
+        a2 = fmaf(w4.y, cq[j4 + 1], a2);
+        a1 = fmaf(w4.z, q[j4 + 2], a1);
+        a2 = fmaf(w4.z, cq[j4 + 2], a2);
+        a1 = fmaf(w4.w, q[j4 + 3], a1);
+        a2 = fmaf(w4.w, cq[j4 + 3], a2);
+      }
+      pb[(u * kSplitCG + cg) * KT + kk] = make_float2(a1, a2);
+    }
+    const float epc[2] = {epn[0], epn[1]}, dzc[2] = {dzn[0], dzn[1]};
+#pragma unroll
+    for (int f = 0; f < 2; ++f) {   // next batch's finishing inputs
+      const int s = s0 + NB + 2 * cg + f;
+      epn[f] = (live && s < S) ? __ldcs(ebase + (size_t)s * L) : 0.f;
+      dzn[f] = (live && s < S) ? __ldcs(dbase + (size_t)s * L) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int f = 0; f < 2; ++f) {
+      const int u = 2 * cg + f, s = s0 + u;
+      if (live && s < S) {
+        float t1 = 0.f, t2 = 0.f;
+#pragma unroll
+        for (int g = 0; g < kSplitCG; ++g) {   // fixed order
+          const float2 p = pb[(u * kSplitCG + g) * KT + kk];
+          t1 += p.x;
+          t2 += p.y;
+        }
+        const float ep = epc[f];
+        const float du = fmaf(tau, dzc[f], fmaf(sg_i * ep, t1, t2)) + jac;
+        const float wi = wt[(size_t)s * MW + i];
+        gl += du - wi * ep * is_i;
+        gs += du * ep - wi * (ep * ep - 1.f) * is_i;
+      }
+    }
+  }
+  red[cg * KT + kk] = make_float2(gl, gs);
+  __syncthreads();
+  if (cg == 0 && live) {
+    float a = 0.f, b2 = 0.f;
+#pragma unroll
+    for (int g = 0; g < kSplitCG; ++g) {
+      a += red[g * KT + kk].x;
+      b2 += red[g * KT + kk].y;
+    }
+    const float inv = 1.f / (float)S;
+    G[(size_t)r * d + loc_of[k]] = a * inv;
+    G[(size_t)r * d + rho_of[k]] = b2 * inv * sigmoid_f(psi[(size_t)i * d + rho_of[k]]);
+  }
+  if (kt == 0 && elbo && threadIdx.x < 32) {
+    double v = 0.0;
+    for (int s = threadIdx.x; s < S; s += 32)
+      v += (double)tau * (double)LOGP[(size_t)r * S + s] - (double)LOGQ[(size_t)r * S + s];
+    v = warp_sum(v);
+    if (threadIdx.x == 0) elbo[r] = (float)(v / (double)S);
+  }
+}
+
 // Same as guide_grad_kernel for m > 32 (weak-scaling runs: 20 particles per GPU x N GPUs).  The
 // component tables no longer fit in registers, so the roles are swapped: each thread keeps ALL its
 // draws of a pass (eps_s and the running T_s, NS of each) in registers and streams the components
@@ -631,6 +760,23 @@ static int launch_grad(const SmiModelDesc& md, const float* psi, const float* ep
   return SMI_OK;
 }
 
+template <int MPC>
+static int launch_grad_split(const SmiModelDesc& md, const float* psi, const float* eps, int m, int S, float tau,
+                             const float* tau_dev, int row0, int nrows, ElboWs& w, float* G, float* elbo,
+                             cudaStream_t st) {
+  const size_t smem = ((size_t)(S + kSplitNB) * kSplitCG * MPC) * sizeof(float) +
+                      ((size_t)2 * kSplitNB * kSplitCG * kGradKT + kSplitCG * kGradKT) * sizeof(float2);
+  if (smem > 220 * 1024) return SMI_ELIMIT;   // caller falls back to the streaming kernel
+  SMI_CUDA_OK(cudaFuncSetAttribute(guide_grad_split_kernel<MPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid((md.latent_dim + kGradKT - 1) / kGradKT, nrows);
+  SMI_PROF_BEGIN(st);
+  guide_grad_split_kernel<MPC><<<grid, 256, smem, st>>>(psi, eps, w.MU, w.SIG, w.ISIG, w.W, w.DZ, w.LOGP, w.LOGQ,
+                                                        w.loc_of, w.rho_of, w.tr_of, m, S, md.latent_dim,
+                                                        md.particle_dim, tau, tau_dev, row0, G, elbo);
+  SMI_LAUNCH_OK_N("guide_grad_split_kernel", st);
+  return SMI_OK;
+}
+
 int smi_guide_grad(const SmiModelDesc& md, const float* psi, const float* eps, int m, int S, float tau,
                    const float* tau_dev, int row0, int nrows, ElboWs& w, float* G, float* elbo, cudaStream_t st) {
   if (m <= 4) return launch_grad<4>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
@@ -642,6 +788,16 @@ int smi_guide_grad(const SmiModelDesc& md, const float* psi, const float* eps, i
   if (m <= 32) return launch_grad<32>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
   if (m <= 40) return launch_grad<40>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
   if (m <= 48) return launch_grad<48>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+  if (m <= 4 * 48 && !getenv("SMI_GRAD_STREAM")) {
+    const int mpc = (m + 3) / 4;
+    int rc;
+    if (mpc <= 16) rc = launch_grad_split<16>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+    else if (mpc <= 24) rc = launch_grad_split<24>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+    else if (mpc <= 32) rc = launch_grad_split<32>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+    else if (mpc <= 40) rc = launch_grad_split<40>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+    else rc = launch_grad_split<48>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+    if (rc != SMI_ELIMIT) return rc;
+  }
   const int mw = (m + 3) & ~3;
   const size_t smem = ((size_t)(S + 1) * mw + kBigJC + kBigSG * kBigKT * 2) * sizeof(float);
   if (smem > 220 * 1024) SMI_FAIL(SMI_ELIMIT, "guide_grad: S * m = %d x %d too large for shared memory", S, m);

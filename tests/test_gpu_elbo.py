@@ -71,8 +71,23 @@ def test_reg_1d_bnn_smi(cuda, h):
 @pytest.mark.parametrize("guide,m,S,dim", [("normal", 1, 100, 10), ("normal", 20, 100, 100), ("delta", 20, 1, 1000),
                                            ("delta", 10, 1, 30),
                                            # m > 32: component-streaming gradient kernel, 16 / 25 / 32 draws per thread
-                                           ("normal", 40, 100, 100), ("normal", 70, 33, 50), ("normal", 35, 130, 70)])
+                                           ("normal", 40, 100, 100), ("normal", 70, 33, 50), ("normal", 35, 130, 70),
+                                           # 48 < m <= 192: component-split gradient kernel (m = 160 is 8 GPUs x 20)
+                                           ("normal", 160, 100, 40), ("normal", 100, 13, 30), ("normal", 192, 9, 20),
+                                           # m > 192: component-streaming kernel
+                                           ("normal", 200, 20, 24)])
 def test_gaussian_target(cuda, guide, m, S, dim):
+    _gaussian_target_case(cuda, guide, m, S, dim)
+
+
+def test_gaussian_target_streaming_gradient_kernel(cuda, monkeypatch):
+    """The component-streaming kernel (m > 192 by default) on a size the split kernel would take."""
+    monkeypatch.setenv("SMI_GRAD_STREAM", "1")
+    _gaussian_target_case(cuda, "normal", 70, 33, 50)
+    _gaussian_target_case(cuda, "normal", 60, 100, 30)
+
+
+def _gaussian_target_case(cuda, guide, m, S, dim):
     from smi_experiments_b200 import models
     pm, om = models.GaussianTarget(dim), omodels.gaussian(dim)
     md, psi, eps, rng, L, d = _setup(pm, om, guide, m, S, seed=dim + m, radius=2.0)
