@@ -15,7 +15,7 @@ PKG = os.path.dirname(HERE)
 OUT = os.path.join(PKG, "libsmi.so")
 OBJ = os.path.join(HERE, "build")
 
-SOURCES = ["common.cu", "stein_small.cu", "select.cu", "stein_tc.cu", "stein_api.cu", "optim.cu",
+SOURCES = ["common.cu", "stein_small.cu", "stein_mid.cu", "select.cu", "stein_tc.cu", "stein_api.cu", "optim.cu",
            "elbo_guide.cu", "elbo_mlp.cu", "elbo_bnn_mma.cu", "elbo_mlp_cls.cu", "elbo_cls_tc.cu", "elbo_api.cu", "prng.cu", "predictive.cu"]
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")

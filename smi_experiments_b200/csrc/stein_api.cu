@@ -4,15 +4,18 @@
 #include "stein_small.cuh"
 #include "stein_tc.cuh"
 
+// SMI_PATH_SMALL = the CUDA-core difference-form kernels: stein_small.cu up to m = 64, stein_mid.cu up to 256
+constexpr int kSmallMax = 64, kMidMax = 256;
 static int resolve_path(int m, int path) {
-  if (path == SMI_PATH_AUTO) return m <= 64 ? SMI_PATH_SMALL : SMI_PATH_TC;
+  if (path == SMI_PATH_AUTO) return m <= kMidMax ? SMI_PATH_SMALL : SMI_PATH_TC;
   return path;
 }
 
 SMI_API size_t smi_stein_force_workspace_bytes(int m, int d, int path) {
   if (m < 1 || d < 1) return 0;
   path = resolve_path(m, path);
-  if (path == SMI_PATH_SMALL) return m <= 64 ? smi_stein_small_workspace_bytes(m, d) : 0;
+  if (path == SMI_PATH_SMALL)
+    return m <= kSmallMax ? smi_stein_small_workspace_bytes(m, d) : (m <= kMidMax ? smi_stein_mid_workspace_bytes(m, d) : 0);
   return smi_stein_tc_workspace_bytes(m, m, d);
 }
 
@@ -25,6 +28,8 @@ SMI_API int smi_stein_force_f32(const float* X, const float* G, int m, int d, fl
     SMI_FAIL(SMI_EINVAL, "smi_stein_force_f32: median_mode=%d", median_mode);
   path = resolve_path(m, path);
   cudaStream_t st = (cudaStream_t)stream;
+  if (path == SMI_PATH_SMALL && m > kSmallMax)
+    return smi_stein_mid_run(X, G, m, d, c_att, alpha, median_mode, h_fixed, F, loss, h, ws, ws_bytes, st);
   if (path == SMI_PATH_SMALL)
     return smi_stein_small_run(X, G, m, d, c_att, alpha, median_mode, h_fixed, F, loss, h, nullptr, false,
                                ws, ws_bytes, st);
@@ -35,12 +40,14 @@ SMI_API int smi_stein_force_f32(const float* X, const float* G, int m, int d, fl
 }
 
 SMI_API size_t smi_sqdist_workspace_bytes(int m, int d, int path) {
+  if (path == SMI_PATH_AUTO && m > kSmallMax) path = SMI_PATH_TC;   // the mid path has no distance-only mode
   return smi_stein_force_workspace_bytes(m, d, path);
 }
 
 SMI_API int smi_sqdist_f32(const float* X, int m, int d, int path, float* D2, void* ws, size_t ws_bytes,
                            void* stream) {
   if (!X || !D2 || !ws) SMI_FAIL(SMI_EINVAL, "smi_sqdist_f32: null pointer");
+  if (path == SMI_PATH_AUTO && m > kSmallMax) path = SMI_PATH_TC;
   path = resolve_path(m, path);
   cudaStream_t st = (cudaStream_t)stream;
   if (path == SMI_PATH_SMALL)

@@ -167,8 +167,9 @@ class ShardedSteinVI(SteinVI):
         G_rows = b["G_all"][r0:r0 + n]
         ops.elbo_grad(self.md, X, b["eps"], b["idx"], data["x"], data["y"], S, max(data["B"], 1), data["lik_scale"],
                       self._tau(), r0, n, G_rows, b["elbo"], self._ws_elbo)
-        if m <= 64:
-            # small m: every rank evaluates the (tiny) full force after gathering the scores
+        if m <= 256:
+            # small m: every rank evaluates the (tiny) full force after gathering the scores (one cluster
+            # launch up to m = 64 when the set fits, the three mid-path launches up to 256)
             dist.all_gather_into_tensor(b["G_all"], G_rows, group=self.group)
             nbytes = _lib.load().smi_stein_force_workspace_bytes(m, d, _lib.PATH_SMALL)
             w = self._ws_stein.get(nbytes, self.device)

@@ -41,6 +41,37 @@ def test_small_path_matches_oracle(cuda, m, d, alpha):
     assert abs(float(loss.item()) - float(loss64)) <= RTOL * float(loss64)
 
 
+@pytest.mark.parametrize("m,d", [(65, 300), (80, 6604), (160, 6604), (97, 1), (250, 130), (256, 1027)])
+@pytest.mark.parametrize("alpha,mode", [(1.0, 1), (10.0, 0)])
+def test_mid_path_matches_oracle(cuda, m, d, alpha, mode):
+    """64 < m <= 256 (weak-scaling particle counts): CUDA-core difference-form path, exact radix-select median."""
+    from smi_experiments_b200 import ops
+    x, g = _mk(m, d, seed=m * 1000 + d)
+    F, loss, h = ops.stein_force(torch.from_numpy(x).to(cuda), torch.from_numpy(g).to(cuda), alpha=alpha,
+                                 median_mode=mode, path=ops.PATH_SMALL)
+    F64, loss64, h64, _ = ostein.stein_force(x, g, alpha, 1.0, mode, np.float64)
+    assert abs(float(h.item()) - float(h64)) <= RTOL * float(h64)
+    assert _rel(F.cpu().numpy(), F64) <= RTOL
+    assert abs(float(loss.item()) - float(loss64)) <= RTOL * float(loss64)
+    # AUTO takes the same path for these sizes, bit for bit
+    F2, loss2, h2 = ops.stein_force(torch.from_numpy(x).to(cuda), torch.from_numpy(g).to(cuda), alpha=alpha,
+                                    median_mode=mode)
+    assert torch.equal(F, F2) and float(h2.item()) == float(h.item()) and float(loss2.item()) == float(loss.item())
+
+
+def test_mid_path_collapsed_and_fixed_bandwidth(cuda):
+    from smi_experiments_b200 import ops
+    x, g = _mk(120, 700, seed=11, collapse=True)
+    F, loss, h = ops.stein_force(torch.from_numpy(x).to(cuda), torch.from_numpy(g).to(cuda))
+    hv = float(h.item())
+    F64, loss64, _, _ = ostein.stein_force(x, g, 1.0, 1.0, dtype=np.float64, h=hv)
+    assert _rel(F.cpu().numpy(), F64) <= RTOL
+    F, loss, h = ops.stein_force(torch.from_numpy(x).to(cuda), torch.from_numpy(g).to(cuda), h_fixed=0.25)
+    assert float(h.item()) == 0.25
+    F64, loss64, _, _ = ostein.stein_force(x, g, dtype=np.float64, h=0.25)
+    assert _rel(F.cpu().numpy(), F64) <= RTOL and abs(float(loss.item()) - float(loss64)) <= RTOL * float(loss64)
+
+
 def test_small_path_collapsed_particles(cuda):
     from smi_experiments_b200 import ops
     x, g = _mk(20, 2000, seed=7, collapse=True)
