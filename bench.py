@@ -387,6 +387,17 @@ def run_gpu(args):
         else:
             from smi_experiments_b200.dist import bench_sharded_force
             sw = bench_sharded_force(args.sweep_m, 10000, args.sweep_reps, flush, pk)
+        # the rest of configs[4]'s sweep (m = 1k .. 16k at d = 1e4), same timing, compact entries
+        if args.sweep_m == 16384 and not args.no_sweep_points:
+            pts = []
+            for mm in (1024, 2048, 4096, 8192):
+                if world == 1:
+                    p = bench_stein_sweep(torch, smi, dev, mm, 10000, args.sweep_reps, flush, pk)
+                else:
+                    p = bench_sharded_force(mm, 10000, args.sweep_reps, flush, pk)
+                pts.append(dict(m=mm, ms=p["ms"], tflops=p["roofline"]["achieved"], frac=p["roofline"]["frac"]))
+            pts.append(dict(m=sw["m"], ms=sw["ms"], tflops=sw["roofline"]["achieved"], frac=sw["roofline"]["frac"]))
+            sw["sweep"] = pts
         if rank == 0:
             line["stein_force"] = sw
     if rank == 0 and world == 1 and not args.no_configs:
@@ -417,6 +428,7 @@ def main():
     ap.add_argument("--sweep-m", type=int, default=16384)
     ap.add_argument("--sweep-reps", type=int, default=3)
     ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--no-sweep-points", action="store_true", help="only the m = 16384 point of the Stein-force sweep")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-configs", action="store_true")
     args = ap.parse_args()
