@@ -195,7 +195,7 @@ static int tc_dist_rows(const float* X, int m, int d, int row0, int rows, TcWs& 
   ga.nb = w.norms;
   ga.diag_shift = row0;
   ga.symmetric = (rows == m && row0 == 0) ? 1 : 0;
-  return launch_gemm<tc::EPI_GRAM>(w.Xh + (size_t)row0 * ldk, w.Xl + (size_t)row0 * ldk, rows, w.Xh, w.Xl, m,
+  return launch_gemm_stein<tc::EPI_GRAM>(w.Xh + (size_t)row0 * ldk, w.Xl + (size_t)row0 * ldk, rows, w.Xh, w.Xl, m,
                                    ldk, ga, st);
 }
 
@@ -222,7 +222,7 @@ static int tc_force_rows(const float* X, const float* G, int m, int d, int row0,
   ga.scal = w.scal;
   ga.lpart = w.lpart;
   SMI_CUDA_OK(cudaMemsetAsync(w.lpart, 0, 256 * sizeof(double), st));
-  return launch_gemm<tc::EPI_FORCE>(w.Kh, w.Kl, rows, w.Yh, w.Yl, d, ldm, ga, st);
+  return launch_gemm_stein<tc::EPI_FORCE>(w.Kh, w.Kl, rows, w.Yh, w.Yl, d, ldm, ga, st);
 }
 
 int smi_stein_tc_run(const float* X, const float* G, int m, int d, int row0, int rows, float c_att,

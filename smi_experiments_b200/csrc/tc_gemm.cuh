@@ -81,6 +81,116 @@ __device__ __forceinline__ void reg_inc() {
   asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS));
 }
 
+// Tile epilogue from the registers of one epilogue thread: `sum` holds row (tm * BM + 32 q + lane),
+// columns [tn * BN + half * kEpiCols, + kEpiCols) of the accumulated product.
+template <int EPI>
+__device__ __forceinline__ void tile_epilogue(const GemmArgs& args, int tm, int tn, int q, int half, int lane,
+                                              float c, float (&sum)[kEpiCols], double& sq) {
+  // ---- tile epilogue from registers ----
+  const int row = tm * BM + q * 32 + lane;
+  const bool row_ok = row < args.M;
+  const int colbase = tn * BN + half * kEpiCols;
+  if (EPI == EPI_CLS_H1) {
+    // columns are (draw, hidden unit); hdim % 4 == 0 keeps each float4 inside one draw
+    if (row_ok) {
+#pragma unroll
+      for (int j = 0; j < kEpiCols; j += 4) {
+        const int col = colbase + j;
+        if (col >= args.N) continue;
+        const int n = col / args.hdim, jj = col - n * args.hdim;
+        const float* bias = args.zin + (long long)n * args.zld + args.off_b + jj;
+        float v[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float pre = sum[j + e] + __ldg(bias + e);
+          v[e] = args.act == SMI_ACT_RELU ? fmaxf(pre, 0.f) : tanhf(pre);
+        }
+        *reinterpret_cast<float4*>(args.C + ((long long)n * args.M + row) * args.hdim + jj) =
+            make_float4(v[0], v[1], v[2], v[3]);
+      }
+    }
+    return;
+  }
+  if (EPI == EPI_CLS_DW1) {
+    // rows are (draw, hidden unit): the 32 lanes of a warp write 32 consecutive floats of dW1[i][:]
+    if (row_ok) {
+      const int n = row / args.hdim, jj = row - n * args.hdim;
+      const long long base = (long long)n * args.zld + args.off_w + jj;
+      // 16 independent loads of z in flight per thread before the 16 stores: with 8 epilogue warps
+      // per SM the read-modify-write is latency-bound otherwise
+#pragma unroll
+      for (int j0 = 0; j0 < kEpiCols; j0 += 16) {
+        float zv[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const int col = colbase + j0 + e;
+          zv[e] = col < args.N ? __ldcs(args.zin + base + (long long)col * args.hdim) : 0.f;
+        }
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const int col = colbase + j0 + e;
+          if (col < args.N) args.zout[base + (long long)col * args.hdim] = sum[j0 + e] - zv[e];   // N(0, 1) prior
+        }
+      }
+    }
+    return;
+  }
+  float ra = 0.f;
+  if (row_ok) ra = EPI == EPI_GRAM ? args.na[row] : c * args.rowsum[row];
+  float* crow = args.C + (long long)row * args.ldc;
+  const bool vec_ok = (args.ldc & 3) == 0;
+  if (EPI == EPI_GRAM) {
+    const int grow = row + args.diag_shift;   // global particle index of this row
+#pragma unroll
+    for (int j = 0; j < kEpiCols; ++j) {
+      const int col = colbase + j;
+      const float nbj = col < args.N ? __ldg(args.nb + col) : 0.f;
+      float v = fmaxf((ra + nbj) - 2.f * sum[j], 0.f);
+      // |x_i - x_i|^2 is exactly 0 in the difference form the reference's kernel uses
+      if (col == grow) v = 0.f;
+      sum[j] = v;
+    }
+    if (args.symmetric) {
+      // each unordered pair is produced once (by the tile holding column >= row) and written
+      // to both triangles: D2 is exactly symmetric and the lower tiles are never computed.
+#pragma unroll
+      for (int j = 0; j < kEpiCols; ++j) {
+        const int col = colbase + j;
+        // transposed store: the 32 lanes of a warp write 32 consecutive floats of row `col`
+        if (row_ok && col < args.N && col > grow) args.C[(long long)col * args.ldc + row] = sum[j];
+      }
+    }
+  } else {
+    const float* xrow = args.X + (long long)row * args.ldx;
+#pragma unroll
+    for (int j = 0; j < kEpiCols; ++j) {
+      const int col = colbase + j;
+      const bool ok = row_ok && col < args.N;
+      const float xv = ok ? __ldg(xrow + col) - __ldg(args.xmean + col) : 0.f;
+      const float v = fmaf(ra, xv, sum[j]);
+      sum[j] = v;
+      if (ok) sq += (double)v * (double)v;
+    }
+  }
+  if (row_ok) {
+    const int grow = row + args.diag_shift;
+#pragma unroll
+    for (int j = 0; j < kEpiCols; j += 4) {
+      const int col = colbase + j;
+      if (col >= args.N) continue;
+      if (EPI == EPI_GRAM && args.symmetric && col + 3 < grow) continue;   // lower triangle: mirrored
+      const bool lower_mix = EPI == EPI_GRAM && args.symmetric && col < grow;
+      if (vec_ok && col + 4 <= args.N && !lower_mix) {
+        *reinterpret_cast<float4*>(crow + col) = make_float4(sum[j], sum[j + 1], sum[j + 2], sum[j + 3]);
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (col + e < args.N && !(lower_mix && col + e < grow)) crow[col + e] = sum[j + e];
+      }
+    }
+  }
+}
+
 // The tensor core adds into its fp32 accumulator with truncation, so a long K loop drifts
 // linearly (measured: ~0.25 ulp per accumulation).  The K loop is therefore cut into chunks of
 // kChunkKB blocks; each chunk starts a fresh TMEM accumulator (two of them ping-pong) and the
@@ -241,109 +351,7 @@ gemm3xtf32_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_con
           acc_phase ^= 1;
         }
       }
-      // ---- tile epilogue from registers ----
-      const int row = tm * BM + q * 32 + lane;
-      const bool row_ok = row < args.M;
-      const int colbase = tn * BN + half * kEpiCols;
-      if (EPI == EPI_CLS_H1) {
-        // columns are (draw, hidden unit); hdim % 4 == 0 keeps each float4 inside one draw
-        if (row_ok) {
-#pragma unroll
-          for (int j = 0; j < kEpiCols; j += 4) {
-            const int col = colbase + j;
-            if (col >= args.N) continue;
-            const int n = col / args.hdim, jj = col - n * args.hdim;
-            const float* bias = args.zin + (long long)n * args.zld + args.off_b + jj;
-            float v[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const float pre = sum[j + e] + __ldg(bias + e);
-              v[e] = args.act == SMI_ACT_RELU ? fmaxf(pre, 0.f) : tanhf(pre);
-            }
-            *reinterpret_cast<float4*>(args.C + ((long long)n * args.M + row) * args.hdim + jj) =
-                make_float4(v[0], v[1], v[2], v[3]);
-          }
-        }
-        continue;
-      }
-      if (EPI == EPI_CLS_DW1) {
-        // rows are (draw, hidden unit): the 32 lanes of a warp write 32 consecutive floats of dW1[i][:]
-        if (row_ok) {
-          const int n = row / args.hdim, jj = row - n * args.hdim;
-          const long long base = (long long)n * args.zld + args.off_w + jj;
-          // 16 independent loads of z in flight per thread before the 16 stores: with 8 epilogue warps
-          // per SM the read-modify-write is latency-bound otherwise
-#pragma unroll
-          for (int j0 = 0; j0 < kEpiCols; j0 += 16) {
-            float zv[16];
-#pragma unroll
-            for (int e = 0; e < 16; ++e) {
-              const int col = colbase + j0 + e;
-              zv[e] = col < args.N ? __ldcs(args.zin + base + (long long)col * args.hdim) : 0.f;
-            }
-#pragma unroll
-            for (int e = 0; e < 16; ++e) {
-              const int col = colbase + j0 + e;
-              if (col < args.N) args.zout[base + (long long)col * args.hdim] = sum[j0 + e] - zv[e];   // N(0, 1) prior
-            }
-          }
-        }
-        continue;
-      }
-      float ra = 0.f;
-      if (row_ok) ra = EPI == EPI_GRAM ? args.na[row] : c * args.rowsum[row];
-      float* crow = args.C + (long long)row * args.ldc;
-      const bool vec_ok = (args.ldc & 3) == 0;
-      if (EPI == EPI_GRAM) {
-        const int grow = row + args.diag_shift;   // global particle index of this row
-#pragma unroll
-        for (int j = 0; j < kEpiCols; ++j) {
-          const int col = colbase + j;
-          const float nbj = col < args.N ? __ldg(args.nb + col) : 0.f;
-          float v = fmaxf((ra + nbj) - 2.f * sum[j], 0.f);
-          // |x_i - x_i|^2 is exactly 0 in the difference form the reference's kernel uses
-          if (col == grow) v = 0.f;
-          sum[j] = v;
-        }
-        if (args.symmetric) {
-          // each unordered pair is produced once (by the tile holding column >= row) and written
-          // to both triangles: D2 is exactly symmetric and the lower tiles are never computed.
-#pragma unroll
-          for (int j = 0; j < kEpiCols; ++j) {
-            const int col = colbase + j;
-            // transposed store: the 32 lanes of a warp write 32 consecutive floats of row `col`
-            if (row_ok && col < args.N && col > grow) args.C[(long long)col * args.ldc + row] = sum[j];
-          }
-        }
-      } else {
-        const float* xrow = args.X + (long long)row * args.ldx;
-#pragma unroll
-        for (int j = 0; j < kEpiCols; ++j) {
-          const int col = colbase + j;
-          const bool ok = row_ok && col < args.N;
-          const float xv = ok ? __ldg(xrow + col) - __ldg(args.xmean + col) : 0.f;
-          const float v = fmaf(ra, xv, sum[j]);
-          sum[j] = v;
-          if (ok) sq += (double)v * (double)v;
-        }
-      }
-      if (row_ok) {
-        const int grow = row + args.diag_shift;
-#pragma unroll
-        for (int j = 0; j < kEpiCols; j += 4) {
-          const int col = colbase + j;
-          if (col >= args.N) continue;
-          if (EPI == EPI_GRAM && args.symmetric && col + 3 < grow) continue;   // lower triangle: mirrored
-          const bool lower_mix = EPI == EPI_GRAM && args.symmetric && col < grow;
-          if (vec_ok && col + 4 <= args.N && !lower_mix) {
-            *reinterpret_cast<float4*>(crow + col) = make_float4(sum[j], sum[j + 1], sum[j + 2], sum[j + 3]);
-          } else {
-#pragma unroll
-            for (int e = 0; e < 4; ++e)
-              if (col + e < args.N && !(lower_mix && col + e < grow)) crow[col + e] = sum[j + e];
-          }
-        }
-      }
+      tile_epilogue<EPI>(args, tm, tn, q, half, lane, c, sum, sq);
     }
     if (EPI == EPI_FORCE) {
       sq = warp_sum(sq);

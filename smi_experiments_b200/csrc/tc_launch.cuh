@@ -6,6 +6,8 @@
 
 #include "common.cuh"
 #include "tc_gemm.cuh"
+#include "tc_gemm_pair.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -69,5 +71,62 @@ int launch_gemm(const float* Ah, const float* Al, long long a_rows, const float*
   return SMI_OK;
 }
 
+// CTA-pair (cta_group::2) launch of the same product: clusters of two CTAs, B maps with 128-row boxes.
+// SMI_TC_PAIR=0 in the environment keeps the one-CTA kernel (A/B timing, scripts/debug_tc.py).
+inline bool tc_pair_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("SMI_TC_PAIR");
+    on = (e && e[0] == '0') ? 0 : 1;
+  }
+  return on == 1;
+}
+
+template <int EPI>
+int launch_gemm_pair(const float* Ah, const float* Al, long long a_rows, const float* Bh, const float* Bl,
+                     long long b_rows, long long ldk, tc::GemmArgs ga, cudaStream_t st) {
+  CUtensorMap ma_h, ma_l, mb_h, mb_l;
+  int rc;
+  if ((rc = make_map(&ma_h, Ah, a_rows, ldk, tc::BM))) return rc;
+  if ((rc = make_map(&ma_l, Al, a_rows, ldk, tc::BM))) return rc;
+  if ((rc = make_map(&mb_h, Bh, b_rows, ldk, tc::BN / 2))) return rc;
+  if ((rc = make_map(&mb_l, Bl, b_rows, ldk, tc::BN / 2))) return rc;
+  ga.K = (int)ldk;
+  ga.tiles_m = (ga.M + tc::BM - 1) / tc::BM;
+  ga.tiles_n = (ga.N + tc::BN - 1) / tc::BN;
+  const int npairtiles = ((ga.tiles_m + 1) / 2) * ga.tiles_n;
+  const int maxpairs = smi_num_sms() / 2;
+  const int pairs = npairtiles < maxpairs ? npairtiles : maxpairs;
+  static bool attr_set[4] = {false, false, false, false};
+  if (!attr_set[EPI]) {
+    SMI_CUDA_OK(cudaFuncSetAttribute(tc::gemm3xtf32_pair_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)tc::kPairSmemBytes));
+    attr_set[EPI] = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * pairs);
+  cfg.blockDim = dim3(tc::kThreads);
+  cfg.dynamicSmemBytes = tc::kPairSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  SMI_PROF_BEGIN(st);
+  SMI_CUDA_OK(cudaLaunchKernelEx(&cfg, tc::gemm3xtf32_pair_kernel<EPI>, ma_h, ma_l, mb_h, mb_l, ga));
+  SMI_LAUNCH_OK_N("gemm3xtf32_kernel", st);
+  return SMI_OK;
+}
+
+// The Stein products (Gram, force) run on CTA pairs; the classifier epilogues stay on the one-CTA kernel.
+template <int EPI>
+int launch_gemm_stein(const float* Ah, const float* Al, long long a_rows, const float* Bh, const float* Bl,
+                      long long b_rows, long long ldk, tc::GemmArgs ga, cudaStream_t st) {
+  if (tc_pair_enabled()) return launch_gemm_pair<EPI>(Ah, Al, a_rows, Bh, Bl, b_rows, ldk, ga, st);
+  return launch_gemm<EPI>(Ah, Al, a_rows, Bh, Bl, b_rows, ldk, ga, st);
+}
 
 }  // namespace
