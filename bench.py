@@ -198,7 +198,7 @@ def bench_stein_sweep(torch, smi, dev, m, d, reps, flush, pk):
     ms = float(np.mean([a.elapsed_time(b) for a, b in evs]))
     W = 4.0 * m * m * d
     tf32_peak = 1100.0 * pk["bf16"] / 2250.0      # TF32 dense peak derived from the measured bf16 GEMM
-    gemm_ms = prof.get("gemm3xtf32_kernel", (1, 0.0))
+    gemm_ms = (1, sum(v[1] for k, v in prof.items() if k.startswith("gemm3xtf32")))
     out = dict(m=m, d=d, ms=ms, gflops=W / ms / 1e6, flop_per_step=W,
                roofline=dict(bound="tensor", achieved=W / ms / 1e9, peak=tf32_peak / 3.0, unit="TFLOP/s",
                              frac=(W / ms / 1e9) / (tf32_peak / 3.0),

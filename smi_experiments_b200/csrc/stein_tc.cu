@@ -164,6 +164,55 @@ size_t carve(SmiArena& ar, TcWs& w, int rows, int m, int d) {
 
 }  // namespace
 
+// Split-K of the Gram product for small particle sets: m = 1024 has 10 needed 256 x 256 pair tiles, each
+// with the whole K loop (313 blocks at d = 1e4) — 266 us on 20 of 148 SMs.  The segment count depends on
+// (m, d) ONLY (never on the rows of a shard), so every element is summed in the same order for every world
+// size and `h` stays bit-identical.  Cost model: waves of 74 pairs over needed tiles x segments.
+int gram_ksplit(int m, int d) {
+  if (!tc_pair_enabled() || m > 4096) return 1;
+  if (const char* e = getenv("SMI_GRAM_KSPLIT")) return atoi(e) > 0 ? atoi(e) : 1;   // experiments only
+  const int nchunks = (pad32(d) / tc::BK + tc::kChunkKB - 1) / tc::kChunkKB;
+  const int T = (m + 255) / 256, needed = T * (T + 1) / 2, pairs = smi_num_sms() / 2;
+  int cap = 2 + (int)((2LL * d) / m);          // partials live in the K / Y plane region: ks * m^2 <= 2 m^2 + 2 d m
+  if (cap > 8) cap = 8;
+  int best = 1;
+  double best_cost = (double)((needed + pairs - 1) / pairs);
+  for (int s = 2; s <= cap; ++s) {
+    if (nchunks / s < 4) break;                // segments of at least 4 chunks (1024 of K)
+    const double cost = (double)((needed * s + pairs - 1) / pairs) / s + 0.02 * s;   // + partial traffic
+    if (cost < 0.9 * best_cost) {
+      best = s;
+      best_cost = cost;
+    }
+  }
+  return best;
+}
+
+// D2[i][j] = max((n_i + n_j) - 2 sum_s part[s][i][j], 0), segments added in order; exact-zero diagonal.
+// Symmetric: both triangles take the value of the (min, max) orientation, as the fused epilogue's
+// mirror store does, so D2 is exactly symmetric.
+__global__ void __launch_bounds__(256)
+gram_finish_kernel(const float* __restrict__ part, int ks, long long stride, int ldp, int rows, int m,
+                   const float* __restrict__ na, const float* __restrict__ nb, int diag_shift, int symmetric,
+                   float* __restrict__ D2) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (j >= m || i >= rows) return;
+  const int gi = i + diag_shift;
+  float v = 0.f;
+  if (j != gi) {
+    int a = i, b = j;
+    if (symmetric && j < i) {
+      a = j;
+      b = i;
+    }
+    const float* p = part + (long long)a * ldp + b;
+    float acc = 0.f;
+    for (int s = 0; s < ks; ++s) acc += p[s * stride];
+    v = fmaxf((na[a] + nb[b]) - 2.f * acc, 0.f);
+  }
+  D2[(long long)i * m + j] = v;
+}
+
 // ---- orchestration ------------------------------------------------------------------------
 size_t smi_stein_tc_workspace_bytes(int rows, int m, int d) {
   SmiArena ar(nullptr, 0);
@@ -195,6 +244,26 @@ static int tc_dist_rows(const float* X, int m, int d, int row0, int rows, TcWs& 
   ga.nb = w.norms;
   ga.diag_shift = row0;
   ga.symmetric = (rows == m && row0 == 0) ? 1 : 0;
+  const int ks = gram_ksplit(m, d);
+  if (ks > 1) {
+    // split-K: raw partial tiles go into the K / Y plane region of the workspace (not in use before the select)
+    const int ldp = (m + 3) / 4 * 4;
+    const size_t span = (size_t)(((char*)w.Yl + (size_t)d * pad32(m) * sizeof(float)) - (char*)w.Kh) / sizeof(float);
+    if ((size_t)ks * rows * ldp > span) SMI_FAIL(SMI_ENOSPC, "split-K partials do not fit the plane region");
+    ga.ksplit = ks;
+    ga.part = w.Kh;
+    ga.part_stride = (long long)rows * ldp;
+    ga.part_ld = ldp;
+    int rc = launch_gemm_stein<tc::EPI_GRAM>(w.Xh + (size_t)row0 * ldk, w.Xl + (size_t)row0 * ldk, rows, w.Xh, w.Xl,
+                                             m, ldk, ga, st);
+    if (rc) return rc;
+    SMI_PROF_BEGIN(st);
+    dim3 g((m + 255) / 256, rows);
+    gram_finish_kernel<<<g, 256, 0, st>>>(w.Kh, ks, (long long)rows * ldp, ldp, rows, m, w.norms + row0, w.norms, row0,
+                                          ga.symmetric, D2);
+    SMI_LAUNCH_OK_N("gram_finish_kernel", st);
+    return SMI_OK;
+  }
   return launch_gemm_stein<tc::EPI_GRAM>(w.Xh + (size_t)row0 * ldk, w.Xl + (size_t)row0 * ldk, rows, w.Xh, w.Xl, m,
                                    ldk, ga, st);
 }

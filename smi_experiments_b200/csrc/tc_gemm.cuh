@@ -56,6 +56,13 @@ struct GemmArgs {
   float* zout;          // [ndraws x zld] d log p / d u
   long long zld;
   int hdim, off_b, off_w, act;
+  // split-K (pair kernel, EPI_GRAM): the K loop is cut into `ksplit` chunk-aligned segments, one work
+  // unit each; units store their raw partial tile to part[seg * part_stride + row * part_ld + col] and
+  // gram_finish_kernel (stein_tc.cu) sums the segments in order and applies the Gram epilogue.
+  int ksplit;           // 0 / 1: no split
+  float* part;
+  long long part_stride;
+  int part_ld;
 };
 
 __device__ __forceinline__ void tile_coords(int t, int tiles_m, int tiles_n, int& tm, int& tn) {

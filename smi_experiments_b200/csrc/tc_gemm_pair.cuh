@@ -39,26 +39,49 @@ __device__ __forceinline__ bool pair_tile_needed(const GemmArgs& a, int tp, int 
   return !a.symmetric || tn + 1 > tp;
 }
 
-// Walks the pair tiles in raster order and hands pair `pair` every npairs-th NEEDED tile: with the
-// symmetric Gram a fixed stride over all tiles left some pairs with up to twice the tiles of others
-// (ncu: SMs active 87 % of the launch), while the running count deals the needed tiles out evenly.
+// Walks the pair tiles in raster order and hands pair `pair` every npairs-th work unit of the NEEDED
+// tiles (unit = tile x K segment; one segment unless split-K): with the symmetric Gram a fixed stride
+// over all tiles left some pairs with up to twice the tiles of others (ncu: SMs active 87 % of the
+// launch), while the running count deals the units out evenly.
 struct PairTileIter {
-  int t, k, ntiles, tiles_p, tiles_n, pair, npairs;
+  int t, k, ntiles, tiles_p, tiles_n, pair, npairs, nseg, seg, ctp, ctn;
   __device__ __forceinline__ PairTileIter(const GemmArgs& a, int pair_, int npairs_)
-      : t(0), k(0), tiles_p((a.tiles_m + 1) >> 1), tiles_n(a.tiles_n), pair(pair_), npairs(npairs_) {
+      : t(0), k(0), tiles_p((a.tiles_m + 1) >> 1), tiles_n(a.tiles_n), pair(pair_), npairs(npairs_),
+        nseg(a.ksplit > 1 ? a.ksplit : 1), ctp(0), ctn(0) {
     ntiles = tiles_p * tiles_n;
+    seg = nseg;   // no current tile yet
   }
-  __device__ __forceinline__ bool next(const GemmArgs& a, int& tp, int& tn) {
-    while (t < ntiles) {
-      pair_tile_coords(t++, tiles_p, tiles_n, tp, tn);
-      if (!pair_tile_needed(a, tp, tn)) continue;
+  __device__ __forceinline__ bool next(const GemmArgs& a, int& tp, int& tn, int& sg) {
+    for (;;) {
+      if (seg == nseg) {
+        bool found = false;
+        while (t < ntiles) {
+          pair_tile_coords(t++, tiles_p, tiles_n, ctp, ctn);
+          if (pair_tile_needed(a, ctp, ctn)) {
+            found = true;
+            break;
+          }
+        }
+        if (!found) return false;
+        seg = 0;
+      }
       const bool mine = k == pair;
       if (++k == npairs) k = 0;
-      if (mine) return true;
+      sg = seg++;
+      if (mine) {
+        tp = ctp;
+        tn = ctn;
+        return true;
+      }
     }
-    return false;
   }
 };
+// Chunk range [c0, c1) of K segment sg.
+__device__ __forceinline__ void seg_chunks(const GemmArgs& a, int nchunks, int sg, int& c0, int& c1) {
+  const int ns = a.ksplit > 1 ? a.ksplit : 1;
+  c0 = (int)((long long)sg * nchunks / ns);
+  c1 = (int)((long long)(sg + 1) * nchunks / ns);
+}
 
 template <int EPI>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -116,11 +139,14 @@ gemm3xtf32_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
         int stage = 0;
         uint32_t phase = 0;
         PairTileIter it(args, pair, npairs);
-        int tp, tn;
-        while (it.next(args, tp, tn)) {
+        int tp, tn, sg;
+        while (it.next(args, tp, tn, sg)) {
           const int arow = (2 * tp + (int)rank) * BM;
           const int brow = tn * BN + (int)rank * (BN / 2);
-          for (int kb = 0; kb < nkb; ++kb) {
+          int c0, c1;
+          seg_chunks(args, nchunks, sg, c0, c1);
+          const int kb_last = min(nkb, c1 * kChunkKB);
+          for (int kb = c0 * kChunkKB; kb < kb_last; ++kb) {
             mbar_wait(empty + stage, phase ^ 1);   // local: the leader's commit reaches both CTAs
             uint8_t* sa = smem + stage * kPairStageBytes;
             if (rank == 0) mbar_arrive_expect_tx(full + stage, 2 * kPairStageBytes);
@@ -143,9 +169,11 @@ gemm3xtf32_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
         int stage = 0, acc = 0;
         uint32_t phase = 0, acc_phase = 0;
         PairTileIter it(args, pair, npairs);
-        int tp, tn;
-        while (it.next(args, tp, tn)) {
-          for (int ch = 0; ch < nchunks; ++ch) {
+        int tp, tn, sg;
+        while (it.next(args, tp, tn, sg)) {
+          int c0, c1;
+          seg_chunks(args, nchunks, sg, c0, c1);
+          for (int ch = c0; ch < c1; ++ch) {
             mbar_wait(tempty + acc, acc_phase ^ 1);
             tc_fence_after();
             const uint32_t d_tmem = tmem_base + (uint32_t)acc * BN;
@@ -192,13 +220,15 @@ gemm3xtf32_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
     double sq = 0.0;
     const float c = EPI == EPI_FORCE ? args.scal[1] : 0.f;
     PairTileIter it(args, pair, npairs);
-    int tp, tn;
-    while (it.next(args, tp, tn)) {
+    int tp, tn, sg;
+    while (it.next(args, tp, tn, sg)) {
       const int tm = 2 * tp + (int)rank;
+      int c0, c1;
+      seg_chunks(args, nchunks, sg, c0, c1);
       float sum[kEpiCols];
 #pragma unroll
       for (int j = 0; j < kEpiCols; ++j) sum[j] = 0.f;
-      for (int ch = 0; ch < nchunks; ++ch) {
+      for (int ch = c0; ch < c1; ++ch) {
         mbar_wait(tfull + acc, acc_phase);
         tc_fence_after();
 #pragma unroll
@@ -216,6 +246,21 @@ gemm3xtf32_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
           acc = 0;
           acc_phase ^= 1;
         }
+      }
+      if (EPI == EPI_GRAM && args.ksplit > 1) {
+        // raw partial tile of this K segment (part_ld % 4 == 0; columns past N are zero)
+        const int row = tm * BM + q * 32 + lane;
+        if (row < args.M) {
+          float* prow = args.part + (long long)sg * args.part_stride + (long long)row * args.part_ld;
+          const int colbase = tn * BN + half * kEpiCols;
+#pragma unroll
+          for (int j = 0; j < kEpiCols; j += 4) {
+            const int col = colbase + j;
+            if (col < args.part_ld)
+              *reinterpret_cast<float4*>(prow + col) = make_float4(sum[j], sum[j + 1], sum[j + 2], sum[j + 3]);
+          }
+        }
+        continue;
       }
       tile_epilogue<EPI>(args, tm, tn, q, half, lane, c, sum, sq);
     }

@@ -94,7 +94,7 @@ int launch_gemm_pair(const float* Ah, const float* Al, long long a_rows, const f
   ga.K = (int)ldk;
   ga.tiles_m = (ga.M + tc::BM - 1) / tc::BM;
   ga.tiles_n = (ga.N + tc::BN - 1) / tc::BN;
-  const int npairtiles = ((ga.tiles_m + 1) / 2) * ga.tiles_n;
+  const int npairtiles = ((ga.tiles_m + 1) / 2) * ga.tiles_n * (ga.ksplit > 1 ? ga.ksplit : 1);   // work units
   const int maxpairs = smi_num_sms() / 2;
   const int pairs = npairtiles < maxpairs ? npairtiles : maxpairs;
   static bool attr_set[4] = {false, false, false, false};
@@ -117,7 +117,7 @@ int launch_gemm_pair(const float* Ah, const float* Al, long long a_rows, const f
   cfg.numAttrs = 1;
   SMI_PROF_BEGIN(st);
   SMI_CUDA_OK(cudaLaunchKernelEx(&cfg, tc::gemm3xtf32_pair_kernel<EPI>, ma_h, ma_l, mb_h, mb_l, ga));
-  SMI_LAUNCH_OK_N("gemm3xtf32_kernel", st);
+  SMI_LAUNCH_OK_N(EPI == tc::EPI_GRAM ? "gemm3xtf32_pair_gram" : "gemm3xtf32_pair_force", st);
   return SMI_OK;
 }
 
