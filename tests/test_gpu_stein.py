@@ -134,7 +134,10 @@ def test_select_fp32_index_edge(cuda):
     assert ostein.median_ranks(m * m, 1) == (33554432, 33554432)
 
 
-@pytest.mark.parametrize("m,d", [(128, 64), (200, 100), (256, 1000), (1000, 333), (1024, 10000)])
+# (700, 2100), (1024, 4100), (1500, 2500), (2048, 2304): split-K Gram (segments of the K loop as separate work
+# units + gram_finish_kernel), ragged tile edges and an odd number of 128-row tiles (phantom half of a CTA pair)
+@pytest.mark.parametrize("m,d", [(128, 64), (200, 100), (256, 1000), (1000, 333), (1024, 10000), (700, 2100),
+                                 (1024, 4100), (1500, 2500), (2048, 2304)])
 def test_tc_sqdist(cuda, m, d):
     from smi_experiments_b200 import ops
     rng = np.random.default_rng(m + d)
@@ -148,6 +151,36 @@ def test_tc_sqdist(cuda, m, d):
     scale = (sq[:, None] + sq[None, :])
     assert np.max(np.abs(D2 - ref)[off] / scale[off]) <= 2e-6
     assert np.max(np.abs(D2)[~off] / scale[~off]) <= 2e-6
+    # the reference's difference form gives an exactly symmetric matrix with an exactly zero diagonal
+    assert (D2 == D2.T).all() and (np.diag(D2) == 0.0).all()
+
+
+def test_tc_pair_kernel_matches_one_cta_kernel(cuda):
+    """The CTA-pair GEMMs (cta_group::2) and the one-CTA kernel accumulate every element in the same order:
+    with split-K off, squared distances, bandwidth and force agree bit for bit (subprocess: the switch is
+    read once per process)."""
+    import os, subprocess, sys, tempfile
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, numpy as np, torch\n"
+        "sys.path.insert(0, %r)\n"
+        "from smi_experiments_b200 import ops\n"
+        "rng = np.random.default_rng(5)\n"
+        "x = torch.from_numpy(rng.standard_normal((777, 1300)).astype(np.float32)).cuda()\n"
+        "g = torch.from_numpy(rng.standard_normal((777, 1300)).astype(np.float32)).cuda()\n"
+        "D2 = ops.sqdist(x, path=ops.PATH_TC)\n"
+        "F, loss, h = ops.stein_force(x, g, path=ops.PATH_TC)\n"
+        "np.savez(sys.argv[1], D2=D2.cpu().numpy(), F=F.cpu().numpy(), loss=loss.cpu().numpy(), h=h.cpu().numpy())\n"
+    ) % root
+    outs = []
+    with tempfile.TemporaryDirectory() as td:
+        for pair in ("1", "0"):
+            f = os.path.join(td, "o%s.npz" % pair)
+            env = dict(os.environ, SMI_TC_PAIR=pair, SMI_GRAM_KSPLIT="1")
+            subprocess.run([sys.executable, "-c", code, f], check=True, env=env, cwd=root, timeout=300)
+            outs.append(dict(np.load(f)))
+    for k in ("D2", "F", "loss", "h"):
+        assert (outs[0][k].view(np.uint32) == outs[1][k].view(np.uint32)).all(), k
 
 
 @pytest.mark.parametrize("m,d", [(65, 40), (128, 64), (200, 100), (512, 2000), (1000, 333), (1024, 10000)])
