@@ -387,20 +387,24 @@ def run_gpu(args):
                     clocks=clocks, roofline=roof, kernels=kern, last_loss=last)
     # ---- Stein-force sweep point (BASELINE configs[4]) ----
     if not args.no_sweep:
+        # configs[4]'s sweep (m = 1k .. 16k at d = 1e4) in ascending order, the m = 16384 point last: the small
+        # points are launch/latency-bound and would otherwise be timed on clocks still power-capped by the big one
+        pts = []
+        if args.sweep_m == 16384 and not args.no_sweep_points:
+            for mm in (1024, 2048, 4096, 8192):
+                reps = args.sweep_reps * (4 if mm <= 4096 else 1)
+                if world == 1:
+                    p = bench_stein_sweep(torch, smi, dev, mm, 10000, reps, flush, pk)
+                else:
+                    from smi_experiments_b200.dist import bench_sharded_force
+                    p = bench_sharded_force(mm, 10000, reps, flush, pk)
+                pts.append(dict(m=mm, ms=p["ms"], tflops=p["roofline"]["achieved"], frac=p["roofline"]["frac"]))
         if world == 1:
             sw = bench_stein_sweep(torch, smi, dev, args.sweep_m, 10000, args.sweep_reps, flush, pk)
         else:
             from smi_experiments_b200.dist import bench_sharded_force
             sw = bench_sharded_force(args.sweep_m, 10000, args.sweep_reps, flush, pk)
-        # the rest of configs[4]'s sweep (m = 1k .. 16k at d = 1e4), same timing, compact entries
-        if args.sweep_m == 16384 and not args.no_sweep_points:
-            pts = []
-            for mm in (1024, 2048, 4096, 8192):
-                if world == 1:
-                    p = bench_stein_sweep(torch, smi, dev, mm, 10000, args.sweep_reps, flush, pk)
-                else:
-                    p = bench_sharded_force(mm, 10000, args.sweep_reps, flush, pk)
-                pts.append(dict(m=mm, ms=p["ms"], tflops=p["roofline"]["achieved"], frac=p["roofline"]["frac"]))
+        if pts:
             pts.append(dict(m=sw["m"], ms=sw["ms"], tflops=sw["roofline"]["achieved"], frac=sw["roofline"]["frac"]))
             sw["sweep"] = pts
         if rank == 0:
