@@ -57,12 +57,35 @@ split_rows_kernel(const float* __restrict__ X, const float* __restrict__ mean, i
   float* h = Xh + (size_t)row * ld;
   float* l = Xl + (size_t)row * ld;
   double s = 0.0;
-  for (int k = threadIdx.x; k < ld; k += blockDim.x) {
-    float v = k < d ? __ldg(x + k) - __ldg(mean + k) : 0.f, hi, lo;
-    split_tf32(v, hi, lo);
-    h[k] = hi;
-    l[k] = lo;
-    s += (double)v * (double)v;
+  if ((d & 3) == 0 && (ld & 3) == 0 && ((((uintptr_t)X) | ((uintptr_t)mean) | ((uintptr_t)Xh) | ((uintptr_t)Xl)) & 15) == 0) {
+    // 16-byte accesses (every row starts 16-byte aligned when d and ld are multiples of 4)
+    const float4* x4 = reinterpret_cast<const float4*>(x);
+    const float4* m4 = reinterpret_cast<const float4*>(mean);
+    float4* h4 = reinterpret_cast<float4*>(h);
+    float4* l4 = reinterpret_cast<float4*>(l);
+    const int d4 = d >> 2, ld4 = ld >> 2;
+    for (int k = threadIdx.x; k < ld4; k += blockDim.x) {
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f), hi, lo;
+      if (k < d4) {
+        const float4 a = __ldcs(x4 + k), b = __ldg(m4 + k);
+        v = make_float4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w);
+      }
+      split_tf32(v.x, hi.x, lo.x);
+      split_tf32(v.y, hi.y, lo.y);
+      split_tf32(v.z, hi.z, lo.z);
+      split_tf32(v.w, hi.w, lo.w);
+      h4[k] = hi;
+      l4[k] = lo;
+      s += ((double)v.x * (double)v.x + (double)v.y * (double)v.y) + ((double)v.z * (double)v.z + (double)v.w * (double)v.w);
+    }
+  } else {
+    for (int k = threadIdx.x; k < ld; k += blockDim.x) {
+      float v = k < d ? __ldg(x + k) - __ldg(mean + k) : 0.f, hi, lo;
+      split_tf32(v, hi, lo);
+      h[k] = hi;
+      l[k] = lo;
+      s += (double)v * (double)v;
+    }
   }
   s = block_sum(s, red);
   if (threadIdx.x == 0) norms[row] = (float)s;
@@ -79,13 +102,34 @@ kmat_rows_kernel(const float* __restrict__ D2, int m, int ldm, const float* __re
   float* kh = Kh + (size_t)row * ldm;
   float* kl = Kl + (size_t)row * ldm;
   double s = 0.0;
-  for (int j = threadIdx.x; j < ldm; j += blockDim.x) {
-    float kv = 0.f, hi, lo;
-    if (j < m) kv = expf(-__ldg(drow + j) / h);
-    split_tf32(kv, hi, lo);
-    kh[j] = hi;
-    kl[j] = lo;
-    s += (double)kv;
+  if ((m & 3) == 0 && (ldm & 3) == 0 && ((((uintptr_t)D2) | ((uintptr_t)Kh) | ((uintptr_t)Kl)) & 15) == 0) {
+    const float4* d4 = reinterpret_cast<const float4*>(drow);
+    float4* kh4 = reinterpret_cast<float4*>(kh);
+    float4* kl4 = reinterpret_cast<float4*>(kl);
+    const int m4 = m >> 2, ld4 = ldm >> 2;
+    for (int j = threadIdx.x; j < ld4; j += blockDim.x) {
+      float4 kv = make_float4(0.f, 0.f, 0.f, 0.f), hi, lo;
+      if (j < m4) {
+        const float4 a = __ldcs(d4 + j);
+        kv = make_float4(expf(-a.x / h), expf(-a.y / h), expf(-a.z / h), expf(-a.w / h));
+      }
+      split_tf32(kv.x, hi.x, lo.x);
+      split_tf32(kv.y, hi.y, lo.y);
+      split_tf32(kv.z, hi.z, lo.z);
+      split_tf32(kv.w, hi.w, lo.w);
+      kh4[j] = hi;
+      kl4[j] = lo;
+      s += ((double)kv.x + (double)kv.y) + ((double)kv.z + (double)kv.w);
+    }
+  } else {
+    for (int j = threadIdx.x; j < ldm; j += blockDim.x) {
+      float kv = 0.f, hi, lo;
+      if (j < m) kv = expf(-__ldg(drow + j) / h);
+      split_tf32(kv, hi, lo);
+      kh[j] = hi;
+      kl[j] = lo;
+      s += (double)kv;
+    }
   }
   s = block_sum(s, red);
   if (threadIdx.x == 0) rowsum[row] = (float)s;
