@@ -212,3 +212,49 @@ def test_tc_and_small_paths_agree(cuda):
     F2, l2, h2 = ops.stein_force(xt, gt, path=ops.PATH_TC)
     assert abs(float(h1.item()) - float(h2.item())) <= RTOL * float(h1.item())
     assert _rel(F2.cpu().numpy(), F1.cpu().numpy()) <= RTOL
+
+
+def test_full_size_sweep_point_properties(cuda):
+    """BASELINE configs[4] at its full size (m = 16384 particles x d = 10000) through size-independent
+    properties: exact symmetry / zero diagonal of the squared distances, sampled rows against float64, the
+    two order statistics of the radix select against torch.sort on the same matrix (bit-exact), linearity of
+    the force in the scores, and sampled force rows against the float64 definition at the device's bandwidth."""
+    from smi_experiments_b200 import ops
+    m, d = 16384, 10000
+    gen = torch.Generator(device=cuda).manual_seed(4)
+    X = torch.randn(m, d, device=cuda, generator=gen)
+    G = torch.randn(m, d, device=cuda, generator=gen)
+    D2 = ops.sqdist(X, path=ops.PATH_TC)
+    assert bool((D2.diagonal() == 0).all())
+    for r0 in range(0, m, 4096):                       # D2 == D2.T blockwise (keeps the temporaries small)
+        assert bool((D2[r0:r0 + 4096] == D2[:, r0:r0 + 4096].T).all())
+    rows = torch.tensor([0, 1, 127, 128, 255, 256, 4095, 8191, 8192, 12345, 16383], device=cuda)
+    X64 = X.double()
+    sq = (X64 * X64).sum(1)
+    ref = (sq[rows, None] + sq[None, :] - 2.0 * (X64[rows] @ X64.T)).clamp_min(0)
+    scale = sq[rows, None] + sq[None, :]
+    err = ((D2[rows].double() - ref).abs() / scale)
+    err[torch.arange(len(rows), device=cuda), rows] = 0
+    assert float(err.max()) <= 2e-6
+    # bandwidth: integer-exact order statistics of the m^2 values
+    h, ranks = ops.median_bandwidth(D2, 1)
+    keys = D2.reshape(-1).view(torch.int32)            # D2 >= 0: the bit patterns order like the values
+    lo, hi = ostein.median_ranks(m * m, 1)
+    srt = torch.sort(keys).values
+    want = torch.stack([srt[lo], srt[hi]])
+    del srt, keys
+    assert bool((ranks.view(torch.int32) == want).all())
+    # force: linear in the scores at fixed particles (h depends on X only), rows against float64
+    F1, _, h1 = ops.stein_force(X, G, path=ops.PATH_TC)
+    F0, _, h0 = ops.stein_force(X, torch.zeros_like(G), path=ops.PATH_TC)
+    F3, loss3, h3 = ops.stein_force(X, 3.0 * G, path=ops.PATH_TC)
+    assert float(h1) == float(h0) == float(h3) == float(h)
+    lin = (F3 - F0) - 3.0 * (F1 - F0)
+    assert float(lin.double().norm() / (3.0 * (F1 - F0)).double().norm()) <= RTOL
+    assert abs(float(loss3) - float(F3.double().norm())) <= RTOL * float(loss3)
+    hv = float(h1)
+    c = 2.0 / (hv * m)
+    Kr = torch.exp(-ref / hv)
+    Kr[torch.arange(len(rows), device=cuda), rows] = 1.0
+    Fref = Kr @ (G.double() - c * X64) + c * Kr.sum(1, keepdim=True) * X64[rows]
+    assert float((F1[rows].double() - Fref).norm() / Fref.norm()) <= RTOL
