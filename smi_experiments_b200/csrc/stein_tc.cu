@@ -287,9 +287,9 @@ gram_finish_kernel(const float* __restrict__ part, int ks, long long stride, int
   float v = 0.f;
   if (j != gi) {
     int a = i, b = j;
-    if (symmetric && j < i) {
-      a = j;
-      b = i;
+    if (symmetric && j >= diag_shift && j < gi) {   // lower triangle of the diagonal block: (local row, global column)
+      a = j - diag_shift;
+      b = gi;
     }
     const float* p = part + (long long)a * ldp + b;
     float acc = 0.f;
@@ -329,7 +329,8 @@ static int tc_dist_rows(const float* X, int m, int d, int row0, int rows, TcWs& 
   ga.na = w.norms + row0;
   ga.nb = w.norms;
   ga.diag_shift = row0;
-  ga.symmetric = (rows == m && row0 == 0) ? 1 : 0;
+  // a row shard contains its own diagonal block [row0, row0 + rows)^2, which is symmetric like the whole matrix
+  ga.symmetric = (row0 % 256 == 0) ? 1 : 0;
   const int ks = gram_ksplit(m, d);
   if (ks > 1) {
     // split-K: raw partial tiles go into the K / Y plane region of the workspace (not in use before the select)

@@ -41,7 +41,8 @@ struct GemmArgs {
   const float* na;      // [M] squared norms of the A rows
   const float* nb;      // [N] squared norms of the B rows
   int diag_shift;       // column of the diagonal element of row r is r + diag_shift (row0 when sharded)
-  int symmetric;        // A and B are the same particle set: compute tiles touching j >= i, mirror-write
+  int symmetric;        // the A rows are particles [diag_shift, diag_shift + M) of the B set (diag_shift % 256 == 0):
+                        // inside that diagonal block only tiles touching j >= i are computed, the rest is mirror-written
   // EPI_FORCE
   const float* X;       // [M x ldx] particles of the A rows
   const float* xmean;   // [N] column means: the epilogue uses X - mean (translation invariance)
@@ -76,7 +77,9 @@ __device__ __forceinline__ void tile_coords(int t, int tiles_m, int tiles_n, int
 }
 // Symmetric Gram: tile (tm, tn) is needed iff it holds an element with column >= row.
 __device__ __forceinline__ bool tile_needed(const GemmArgs& a, int tm, int tn) {
-  return !a.symmetric || (tn + 1) * BN > tm * BM;
+  if (!a.symmetric) return true;
+  const int cb = tn * BN - a.diag_shift;            // first column of the tile relative to the diagonal block
+  return cb < 0 || cb + BN > tm * BM;               // left of the block, or touching j >= i (right of the block too)
 }
 
 template <int REGS>
@@ -164,7 +167,8 @@ __device__ __forceinline__ void tile_epilogue(const GemmArgs& args, int tm, int 
       for (int j = 0; j < kEpiCols; ++j) {
         const int col = colbase + j;
         // transposed store: the 32 lanes of a warp write 32 consecutive floats of row `col`
-        if (row_ok && col < args.N && col > grow) args.C[(long long)col * args.ldc + row] = sum[j];
+        if (row_ok && col < args.N && col > grow && col - args.diag_shift < args.M)
+          args.C[(long long)(col - args.diag_shift) * args.ldc + grow] = sum[j];
       }
     }
   } else {
@@ -185,8 +189,10 @@ __device__ __forceinline__ void tile_epilogue(const GemmArgs& args, int tm, int 
     for (int j = 0; j < kEpiCols; j += 4) {
       const int col = colbase + j;
       if (col >= args.N) continue;
-      if (EPI == EPI_GRAM && args.symmetric && col + 3 < grow) continue;   // lower triangle: mirrored
-      const bool lower_mix = EPI == EPI_GRAM && args.symmetric && col < grow;
+      // lower triangle of the diagonal block: mirrored (diag_shift % 4 == 0: a float4 group is inside or outside)
+      const bool inblk = EPI == EPI_GRAM && args.symmetric && col >= args.diag_shift;
+      if (inblk && col + 3 < grow) continue;
+      const bool lower_mix = inblk && col < grow;
       if (vec_ok && col + 4 <= args.N && !lower_mix) {
         *reinterpret_cast<float4*>(crow + col) = make_float4(sum[j], sum[j + 1], sum[j + 2], sum[j + 3]);
       } else {

@@ -36,7 +36,9 @@ __device__ __forceinline__ void pair_tile_coords(int t, int tiles_p, int tiles_n
 // Symmetric Gram: tiles (2 tp, tn) and (2 tp + 1, tn) are needed or skipped together
 // ((tn + 1) * 256 > (2 tp + r) * 128  <=>  tn + 1 > tp for r = 0 and r = 1).
 __device__ __forceinline__ bool pair_tile_needed(const GemmArgs& a, int tp, int tn) {
-  return !a.symmetric || tn + 1 > tp;
+  if (!a.symmetric) return true;
+  const int tb = tn - a.diag_shift / BN;            // column tile relative to the diagonal block
+  return tb < 0 || tb + 1 > tp;
 }
 
 // Walks the pair tiles in raster order and hands pair `pair` every npairs-th work unit of the NEEDED
