@@ -17,6 +17,9 @@ import math
 import numpy as np
 
 EPS32 = float(np.finfo(np.float32).eps)  # 1.1920929e-07
+# numpyro stein_util.median_bandwidth adds "10 * jnp.finfo(dists.dtype).eps" to median^2 * factor [NP?]: the ONE place
+# this constant lives in the oracle (device side: kSmiBandwidthFloor in csrc/common.cuh).  Recalled, not verifiable here.
+BANDWIDTH_FLOOR = 10.0 * EPS32
 
 MEDIAN_EXACT_MIDPOINT = 0  # textbook midpoint of the two middle order statistics
 MEDIAN_JAX_FP32_INDEX = 1  # q = 0.5f * float32(n - 1) computed in float32 [NP?]
@@ -47,13 +50,13 @@ def median(values, mode=MEDIAN_JAX_FP32_INDEX):
 
 
 def bandwidth_from_dists(dists, m, mode=MEDIAN_JAX_FP32_INDEX):
-    """h = median(D)^2 * (1/ln m) + eps32 ; m == 1 => 1.0."""
+    """h = median(D)^2 * (1/ln m) + 10 eps32 ; m == 1 => 1.0."""
     dt = np.asarray(dists).dtype.type
     if m == 1:
         return dt(1.0)
     med = median(dists, mode)
     factor = dt(1.0 / math.log(m))
-    return dt(med * med * factor + dt(EPS32))
+    return dt(med * med * factor + dt(BANDWIDTH_FLOOR))
 
 
 def median_bandwidth(x, mode=MEDIAN_JAX_FP32_INDEX, dtype=np.float32):
@@ -111,3 +114,33 @@ def stein_force_direct(x, g, h, alpha=1.0, c_att=1.0):
             # grad wrt first argument x_j of k(x_j, x_i): -2 (x_j - x_i)/h * k
             f[i] += alpha / m * (-2.0 * diff / h * kij)
     return f
+
+
+def stein_force_torch(x, g, alpha=1.0, c_att=1.0, mode=MEDIAN_JAX_FP32_INDEX, threads=None, chunk=32):
+    """The same algorithm as stein_force() in float32 on ALL host threads (torch CPU ops): Gram-form distances +
+    full sort for the bandwidth, the kernel from DIFFERENCES (the m x m x d broadcast the reference's vmapped
+    `kernel(x, y)` performs, in row chunks), two products for the force.  bench.py's CPU leg for the Stein stage
+    (config C5) -- never the product path.  Returns (F, loss, h) as numpy / floats."""
+    import torch
+    if threads:
+        torch.set_num_threads(threads)
+    xt = torch.as_tensor(np.asarray(x, np.float32))
+    gt = torch.as_tensor(np.asarray(g, np.float32))
+    m = xt.shape[0]
+    if m == 1:
+        h = 1.0
+    else:
+        sq = (xt * xt).sum(1)
+        d = torch.sqrt(torch.clamp((sq[None, :] + sq[:, None]) - 2.0 * (xt @ xt.T), min=0.0))
+        a = torch.sort(d.reshape(-1)).values
+        lo, hi = median_ranks(m * m, mode)
+        med = (a[lo] + a[hi]) * 0.5
+        h = float(np.float32(med.item()) * np.float32(med.item()) * np.float32(1.0 / math.log(m)) + np.float32(BANDWIDTH_FLOOR))
+    k = torch.empty(m, m, dtype=torch.float32)
+    for i0 in range(0, m, chunk):
+        diff = xt[None, :, :] - xt[i0:i0 + chunk, None, :]
+        k[i0:i0 + chunk] = torch.exp(-(diff * diff).sum(-1) / h)
+    c = 2.0 * alpha / (h * m)
+    f = c_att * (k @ gt) + c * (xt * k.sum(1)[:, None] - k @ xt)
+    loss = float(torch.sqrt((f.double() ** 2).sum()))
+    return f.numpy(), loss, h

@@ -53,6 +53,10 @@ void smi_prof_end_(const char* name, cudaStream_t st);
     SMI_LAUNCH_OK();              \
   } while (0)
 
+// numpyro stein_util.median_bandwidth: h = median(D)^2 * factor + 10 * finfo(float32).eps [NP?].  The ONE place the
+// floor lives on the device (oracle: oracle/stein.py BANDWIDTH_FLOOR); recalled from NumPyro, not verifiable here.
+constexpr float kSmiBandwidthFloor = 10.f * 1.1920929e-07f;
+
 static inline size_t smi_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 // Bump allocator over the caller's workspace.

@@ -168,7 +168,7 @@ __global__ void select_finish(const unsigned* __restrict__ state, const unsigned
   const unsigned a = state[2];
   const unsigned b = rank_hi < *cnt_le ? a : *min_gt;
   const float med = (sqrtf(__uint_as_float(a)) + sqrtf(__uint_as_float(b))) * 0.5f;
-  const float h = __fadd_rn(__fmul_rn(__fmul_rn(med, med), factor), 1.1920929e-07f);
+  const float h = __fadd_rn(__fmul_rn(__fmul_rn(med, med), factor), kSmiBandwidthFloor);
   if (h_out) *h_out = h;
   if (scal) {
     scal[0] = h;

@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(kFinishThreads) stein_mid_finish(MidFinishArgs
       med[1] = k2 >= 0 ? sqrtf(__uint_as_float(radix_select_smem(keys, np, k2, hist, s_sel))) : 0.f;
     }
     const float mm = (med[0] + med[1]) * 0.5f;
-    h = __fadd_rn(__fmul_rn(__fmul_rn(mm, mm), a.factor), 1.1920929e-07f);
+    h = __fadd_rn(__fmul_rn(__fmul_rn(mm, mm), a.factor), kSmiBandwidthFloor);
   }
   if (threadIdx.x == 0) s_h = h;
   __syncthreads();

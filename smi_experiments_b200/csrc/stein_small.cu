@@ -185,7 +185,7 @@ __global__ void __launch_bounds__(1024) stein_small_finish(FinishArgs a) {
     bitonic_sort_smem(srt, P);
     if (threadIdx.x == 0) {
       const float med = (srt[a.rank_lo] + srt[a.rank_hi]) * 0.5f;
-      s_h = __fadd_rn(__fmul_rn(__fmul_rn(med, med), a.factor), 1.1920929e-07f);
+      s_h = __fadd_rn(__fmul_rn(__fmul_rn(med, med), a.factor), kSmiBandwidthFloor);
     }
   }
   __syncthreads();
@@ -505,7 +505,7 @@ __global__ void __launch_bounds__(kFusedThreads, 1) stein_cluster_kernel(FusedAr
     }
     __syncthreads();
     const float med = (s_med[0] + s_med[1]) * 0.5f;
-    h = __fadd_rn(__fmul_rn(__fmul_rn(med, med), a.factor), 1.1920929e-07f);
+    h = __fadd_rn(__fmul_rn(__fmul_rn(med, med), a.factor), kSmiBandwidthFloor);
   }
   TR(5);
   const float c = (2.0f * a.alpha) / (h * (float)m);

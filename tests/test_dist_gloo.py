@@ -70,7 +70,7 @@ class NumpyRows:
             b = a if hi < int(cnt) else np.array([int(mn)], np.uint32).view(np.float32)[0]
             self.sel = (a, b)
             med = np.float32((np.sqrt(a) + np.sqrt(b)) * np.float32(0.5))
-            self.hv = np.float32(med * med * np.float32(1.0 / np.log(self.m)) + np.float32(stein.EPS32))
+            self.hv = np.float32(med * med * np.float32(1.0 / np.log(self.m)) + np.float32(stein.BANDWIDTH_FLOOR))
         self.alpha = alpha
         return torch.tensor([self.hv])
 

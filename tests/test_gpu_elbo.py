@@ -40,7 +40,9 @@ def _run(cuda, md, psi, eps, idx, x, y, S, B, lik_scale, tau, row0=0, nrows=None
     return G.cpu().numpy(), E.cpu().numpy()
 
 
-@pytest.mark.parametrize("m,S,N,B,I", [(3, 4, 30, 7, 13), (5, 100, 455, 100, 13), (20, 8, 64, 64, 5), (36, 6, 64, 64, 5)])
+# (20, 100, 455, 100, 13) is the shape bench.py times (BASELINE configs[1]: 20 particles, 100 draws, minibatch 100 of 455 x 13)
+@pytest.mark.parametrize("m,S,N,B,I", [(3, 4, 30, 7, 13), (5, 100, 455, 100, 13), (20, 100, 455, 100, 13),
+                                       (20, 8, 64, 64, 5), (36, 6, 64, 64, 5)])
 def test_uci_bnn_smi(cuda, m, S, N, B, I):
     from smi_experiments_b200 import models
     pm, om = models.uci_bnn(I), omodels.uci_bnn(I)
@@ -100,7 +102,9 @@ def _gaussian_target_case(cuda, guide, m, S, dim):
         np.testing.assert_allclose(G, -tau * psi, rtol=1e-6)
 
 
+# (10, 55, 128, 784, 100, 10) is the C4 shape bench.py times (BASELINE configs[3]: 10 particles, 55 draws, batch 128)
 @pytest.mark.parametrize("m,S,B,I,H,O,scale255", [(2, 3, 16, 12, 8, 3, False), (3, 5, 128, 784, 100, 10, False),
+                                                  (10, 55, 128, 784, 100, 10, False),
                                                   (2, 2, 128, 784, 100, 10, True), (2, 2, 50, 30, 10, 4, False),
                                                   (3, 4, 40, 70, 20, 5, False), (2, 3, 100, 200, 36, 7, False)])
 def test_mnist_mlp_smi(cuda, m, S, B, I, H, O, scale255):

@@ -164,3 +164,41 @@ def test_subsample_rules(cuda, layout_name, rule, N, B):
     finally:
         ops.set_prng_layout(prev_l)
         ops.set_randint_rule(prev_r)
+
+
+# ---- external pin: the DEVICE PRNG against values printed in JAX's documentation (tests/jax_published.py) ----
+def _dev_split(cuda, key, n):
+    from smi_experiments_b200 import ops
+    out = torch.empty(n, 2, dtype=torch.int32, device=cuda)
+    ops.call("smi_prng_split", ops._ptr(_key(cuda, key)), n, ops._ptr(out), ops._stream())
+    return out.cpu().numpy().view(np.uint32)
+
+
+def _with_layout(code):
+    from smi_experiments_b200 import ops
+    return ops.set_prng_layout("partitionable" if code == 1 else "legacy")
+
+
+def test_device_prng_matches_jax_docs(cuda, lib):
+    import jax_published as jp
+    from smi_experiments_b200 import ops
+    prev = ops.set_prng_layout(None)
+    try:
+        for layout, seed, n, want in jp.SPLITS:
+            _with_layout(layout)
+            assert _dev_split(cuda, jp.key_of(seed), n).tolist() == want
+        for layout, seed, path, n, want in jp.NORMALS:
+            _with_layout(layout)
+            key = jp.key_of(seed)
+            for nsplit, i in path:
+                key = _dev_split(cuda, key, nsplit)[i]
+            z = torch.empty(n, dtype=torch.float32, device=cuda)
+            ops.call("smi_prng_normal_f32", ops._ptr(_key(cuda, key)), n, ops._ptr(z), ops._stream())
+            np.testing.assert_allclose(z.cpu().numpy(), np.asarray(want, np.float32), rtol=jp.NORMAL_RTOL, atol=0)
+        for layout, seed, want in jp.UNIFORMS:
+            _with_layout(layout)
+            u = torch.empty(1, dtype=torch.float32, device=cuda)
+            ops.call("smi_prng_uniform_f32", ops._ptr(_key(cuda, jp.key_of(seed))), 1, 0.0, 1.0, ops._ptr(u), ops._stream())
+            assert float(u.item()) == float(np.float32(want))
+    finally:
+        ops.set_prng_layout(prev)

@@ -115,7 +115,7 @@ def test_select_is_bit_exact(cuda, m, mode):
     want = np.array([a[lo], a[hi]], np.float32).view(np.uint32)
     assert (got == want).all()
     med = np.float32((np.sqrt(a[lo]) + np.sqrt(a[hi])) * np.float32(0.5))
-    hw = np.float32(med * med * np.float32(1.0 / np.log(m)) + np.float32(ostein.EPS32))
+    hw = np.float32(med * med * np.float32(1.0 / np.log(m)) + np.float32(ostein.BANDWIDTH_FLOOR))
     assert abs(float(h.item()) - float(hw)) <= 2e-7 * float(hw)
 
 
@@ -195,7 +195,7 @@ def test_tc_path_matches_oracle(cuda, m, d, alpha):
     d2 = np.maximum(sq[:, None] + sq[None, :] - 2.0 * (x64 @ x64.T), 0.0)
     a = np.sort(np.sqrt(d2).ravel())
     lo, hi = ostein.median_ranks(m * m, 1)
-    h64 = (0.5 * (a[lo] + a[hi])) ** 2 / np.log(m) + ostein.EPS32
+    h64 = (0.5 * (a[lo] + a[hi])) ** 2 / np.log(m) + ostein.BANDWIDTH_FLOOR
     assert abs(float(h.item()) - h64) <= RTOL * h64
     K = np.exp(-d2 / h64)
     c = 2.0 * alpha / (h64 * m)

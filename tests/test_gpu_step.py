@@ -95,7 +95,7 @@ def test_svgd_gaussian_run_matches_oracle(cuda):
     # run(): same trajectory from the same key, losses collected on the device
     res = eng.run(smi.PRNGKey(2), nsteps, progress_bar=False)
     assert res.losses.shape == (nsteps,)
-    np.testing.assert_allclose(res.losses.cpu().numpy(), losses, rtol=1e-4)
+    np.testing.assert_allclose(res.losses.cpu().numpy(), losses, rtol=1e-6)
     assert set(res.params) == {"x_auto_loc"} and res.params["x_auto_loc"].shape == (m, d)
     # resume from a state: the ring offset follows the step counter
     res2 = eng.run(smi.PRNGKey(2), 3, progress_bar=False, init_state=res.state)
@@ -233,3 +233,44 @@ def test_asvgd_graph_run_matches_host_scheduled_eager_loop(cuda):
         losses.append(float(l))
     np.testing.assert_allclose(res.losses.cpu().numpy(), np.asarray(losses, np.float32), rtol=2e-6)
     np.testing.assert_allclose(res.state.optim_state.x.cpu().numpy(), st.optim_state.x.cpu().numpy(), rtol=1e-5, atol=1e-7)
+
+
+# ---- the shapes bench.py times (BASELINE.json configs[1] and configs[3]), one full update each ----------------
+def test_c2_timed_shape_full_update(cuda):
+    """C2 exactly as bench.py runs it: 455 x 13 train rows, BNN 13-50-50-1, 20 particles, 100 draws, minibatch 100,
+    Adam 5e-3, CUDA-graph replay from the third call on (experiments/uci_benchmark.py:188-195)."""
+    import smi_experiments_b200 as smi
+    import bench
+    xt, yt = bench.make_uci()
+    c = bench.C2
+    m, S, B, N = c["m"], c["S"], c["B"], xt.shape[0]
+    model = smi.uci_bnn(c["in_dim"])
+    eng = smi.SteinVI(model, smi.AutoNormal(model, init_loc_fn=smi.init_to_uniform(radius=c["radius"])),
+                      smi.Adam(c["lr"]), smi.RBFKernel(), num_stein_particles=m, num_elbo_particles=S)
+    state = eng.init(smi.PRNGKey(1), x=xt, y=yt, subsample=B)
+    om = omodels.uci_bnn(c["in_dim"])
+    for it in range(3):          # eager, eager (warm), graph replay
+        snap = _snap(state)
+        state, loss = eng.update(state, x=xt, y=yt, subsample=B)
+        ref = _oracle_step(om, "normal", snap, m, S, xt, yt, N, B, 1.0, 1.0, "adam", c["lr"])
+        _check(state, loss, ref)
+    assert eng._graph is not None
+
+
+def test_c4_timed_shape_full_update(cuda):
+    """C4 as bench.py runs it: MLP 784-100-100-10 tanh, 10 particles, 55 draws, batch 128 of n = 60000, Adagrad 0.8
+    (experiments/img_classifier.py:66-73,170-177); pixel values scaled to [0, 1] as in bench.py."""
+    import smi_experiments_b200 as smi
+    model = smi.mnist_mlp()
+    m, S, B, n = 10, 55, 128, 60000
+    eng = smi.SteinVI(model, smi.AutoNormal(model, init_loc_fn=smi.init_to_uniform(radius=0.05)), smi.Adagrad(0.8),
+                      smi.RBFKernel(), num_stein_particles=m, num_elbo_particles=S)
+    rng = np.random.default_rng(0)
+    xb = (rng.integers(0, 256, (B, 784)).astype(np.float32) / 255.0)
+    yb = rng.integers(0, 10, B).astype(np.int32)
+    state = eng.init(smi.PRNGKey(4), xb, yb, n=n, batch_size=B)
+    snap = _snap(state)
+    state, loss = eng.update(state, xb, yb, n=n, batch_size=B)
+    om = omodels.mnist_mlp()
+    ref = _oracle_step(om, "normal", snap, m, S, xb, yb, n, B, 1.0, 1.0, "adagrad", 0.8, plate_only=True)
+    _check(state, loss, ref)

@@ -91,5 +91,5 @@ def test_bandwidth_formula_and_distance_form():
     ref = np.sqrt(((x[:, None, :].astype(np.float64) - x[None].astype(np.float64)) ** 2).sum(-1))
     np.testing.assert_allclose(D, ref, atol=2e-3)      # Gram form: diagonal is rounding noise, not 0
     h = stein.median_bandwidth(x)
-    want = np.float32(np.median(D)) ** 2 * np.float32(1 / math.log(m)) + np.float32(1.1920929e-07)
+    want = np.float32(np.median(D)) ** 2 * np.float32(1 / math.log(m)) + np.float32(stein.BANDWIDTH_FLOOR)
     assert h == np.float32(want)
