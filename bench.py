@@ -42,6 +42,16 @@ def make_uci(seed=1):
 
 
 C2 = dict(m=20, S=100, B=100, in_dim=13, lr=5e-3, radius=0.1)
+UNIT = "SMI steps/s"      # the SAME string in both arms (the driver divides them)
+
+
+def bench_config(world):
+    """`config` of the bench line, identical in the GPU arm and the --impl reference arm."""
+    return dict(workload="uci_boston_bnn_smi (BASELINE configs[1]): 455x13 train, BNN 13-50-50-1 ReLU, AutoNormal, "
+                         "minibatch 100, 100 ELBO draws, Adam",
+                particles_per_gpu=C2["m"], particles_total=C2["m"] * world, elbo_draws=C2["S"], minibatch=C2["B"],
+                unit_note="one unit = one SMI step on 20 particles; under weak scaling (--gpus N) a step updates "
+                          "20 N particles of one mixture and counts N units")
 
 
 def peaks():
@@ -51,6 +61,36 @@ def peaks():
             d = json.load(f)
         return dict(hbm=d["hbm_gbs"], bf16=d["bf16_tflops"], bf16_sus=d["bf16_tflops_sustained"], src="measured")
     return dict(hbm=6650.0, bf16=1590.0, bf16_sus=1400.0, src="fallback")
+
+
+_UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+
+
+def traffic_from_profile(relpath, kernel_substr):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the launches whose kernel name contains
+    `kernel_substr`, summed, read from a committed ncu summary under profiles/ (scripts/ncu_summary.py
+    format).  None when the file or the kernel is absent."""
+    path = os.path.join(ROOT, relpath)
+    if not os.path.exists(path):
+        return None
+    total, cur, found = 0.0, False, False
+    with open(path) as f:
+        for ln in f:
+            t = ln.split()
+            if not t:
+                continue
+            if ln.startswith("Kernel Name"):
+                cur = kernel_substr in ln
+                found |= cur
+            elif cur and t[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum") and len(t) >= 3:
+                total += float(t[1]) * _UNIT.get(t[2], 1.0)
+    return int(total) if found else None
+
+
+def tf32_peaks(pk):
+    """Dense TF32 tensor peak DERIVED from the measured bf16 GEMM (1100 / 2250 of it): burst and sustained;
+    a 3xTF32 kernel's logical FP32-equivalent peak is one third."""
+    return 1100.0 * pk["bf16"] / 2250.0, 1100.0 * pk["bf16_sus"] / 2250.0
 
 
 class ClockSampler:
@@ -103,9 +143,17 @@ class ClockSampler:
 
 
 # ---- CPU arm: the oracle port on the host cores --------------------------------------------
-def cpu_step_runner(threads=None):
+def cpu_step_runner(threads=None, world=1):
+    """One step of the reference algorithm on the host (oracle port, torch-CPU fp32, all threads).
+    world = 1: the full C2 step on 20 particles.  world = N > 1 (the weak-scaled workload, m = 20 N particles of one
+    mixture): ONE unit of it = what one rank does per step -- the ELBO gradients of 20 of the 20 N particles against
+    all 20 N mixture components, the Stein force (evaluated in full here: 0.1 % of the step at these m) and the
+    optimizer update of those 20 rows.  A bounded sample of the workload with no extrapolation: units / second."""
     import torch
+    from oracle import elbo as oelbo
     from oracle import models as omodels
+    from oracle import optim as ooptim
+    from oracle import stein as ostein
     from oracle import step as ostep
     if threads:
         torch.set_num_threads(threads)
@@ -113,22 +161,38 @@ def cpu_step_runner(threads=None):
     om = omodels.uci_bnn(C2["in_dim"])
     rows, L, d = omodels.layout(om, "normal")
     rng = np.random.default_rng(1)
-    m, S, B = C2["m"], C2["S"], C2["B"]
+    n, S, B = C2["m"], C2["S"], C2["B"]
+    m = n * world
     psi = rng.uniform(-C2["radius"], C2["radius"], (m, d)).astype(np.float32)
     for r in rows:
         psi[:, r["rho"]:r["rho"] + r["size"]] = np.log(np.expm1(0.1))
     st = dict(psi=psi, opt=(np.zeros_like(psi), np.zeros_like(psi)), it=0)
 
-    def step():
+    def noise():
         # noise drawn with numpy (the threefry chain in pure numpy is not what a JAX CPU run pays for)
-        eps = rng.standard_normal((m, S, L)).astype(np.float32)
-        idx = np.stack([rng.permutation(455)[:B] for _ in range(m * S)]).reshape(m, S, B).astype(np.int32)
+        eps = rng.standard_normal((n, S, L)).astype(np.float32)
+        idx = np.stack([rng.permutation(455)[:B] for _ in range(n * S)]).reshape(n, S, B).astype(np.int32)
+        return eps, idx
+
+    def step():
+        eps, idx = noise()
         out = ostep.smi_step(om, st["psi"], st["opt"], st["it"], eps, idx, xt, yt, 455, "normal", 1.0, 1.0, 1.0,
                              "adam", C2["lr"], dtype=np.float32)
         st["psi"], st["opt"], st["it"] = out["psi"], out["opt_state"], st["it"] + 1
         return float(out["loss"])
 
-    return step, torch.get_num_threads()
+    def unit():
+        eps, idx = noise()
+        Gr, _ = oelbo.elbo_grads(om, st["psi"], eps, idx, xt, yt, 455, 1.0, "normal", torch.float32, rows=(0, n))
+        G = np.tile(Gr, (world, 1))                    # the other ranks' scores: same shape, values irrelevant to the cost
+        F, loss, h, _ = ostein.stein_force(st["psi"], G, 1.0, 1.0, ostein.MEDIAN_JAX_FP32_INDEX, np.float32)
+        a, b = st["opt"]
+        x2, a2, b2 = ooptim.adam_update(st["it"], -F[:n], st["psi"][:n], a[:n], b[:n], C2["lr"])
+        st["psi"][:n], a[:n], b[:n] = x2, a2, b2
+        st["it"] += 1
+        return float(loss)
+
+    return (step if world == 1 else unit), torch.get_num_threads()
 
 
 def run_reference(args):
@@ -137,22 +201,30 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    step, cores = cpu_step_runner(os.cpu_count())
+    # the same workload as the GPU arm at this --gpus N: weak scaling = 20 particles per GPU, m = 20 N in ONE
+    # mixture; one unit = one rank's share of a step (20 particles); the GPU arm completes N units per step
+    world = max(args.gpus, 1)
+    m_total = C2["m"] * world
+    step, cores = cpu_step_runner(os.cpu_count(), world)
     for _ in range(max(args.warmup, 1)):
         step()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         step()
     dt = time.perf_counter() - t0
-    v = args.steps / dt
-    line = dict(metric=METRIC, value=v, unit="SMI steps/s", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
+    v = args.steps / dt         # units / s: a step of this arm is ONE unit (see cpu_step_runner)
+    line = dict(metric=METRIC, value=v, unit=UNIT, n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
                 ms_per_step=1e3 * dt / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
                 dtype="f32", data="synthetic", impl="reference",
-                config=dict(workload="uci_boston_bnn_smi (BASELINE configs[1])", particles=C2["m"],
-                            elbo_draws=C2["S"], minibatch=C2["B"], optimizer="adam"),
-                cpu_baseline=dict(value=v, unit="SMI steps/s", cores=cores, kind="port",
-                                  sample="%d full SMI steps of the C2 workload (oracle, torch-CPU fp32)" % args.steps),
-                e2e=dict(value=v, unit="SMI steps/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+                config=bench_config(world),
+                cpu_baseline=dict(value=v, unit=UNIT, cores=cores, kind="port",
+                                  sample=("%d full SMI steps of the C2 workload (20 particles; oracle port, torch-CPU "
+                                          "fp32, all host threads)" % args.steps) if world == 1 else
+                                         ("%d units of the weak-scaled workload at m = %d particles: per unit the ELBO "
+                                          "gradients of 20 particles against all %d mixture components + the Stein force "
+                                          "+ Adam on those rows = one rank's share of a step (oracle port, torch-CPU fp32, "
+                                          "all host threads)" % (args.steps, m_total, m_total))),
+                e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0))
     print(json.dumps(line), flush=True)
 
 
@@ -196,23 +268,114 @@ def bench_stein_sweep(torch, smi, dev, m, d, reps, flush, pk):
     lib.smi_profile(0)
     prof = profile_report(lib)
     ms = float(np.mean([a.elapsed_time(b) for a, b in evs]))
-    W = 4.0 * m * m * d
-    tf32_peak = 1100.0 * pk["bf16"] / 2250.0      # TF32 dense peak derived from the measured bf16 GEMM
-    gemm_ms = (1, sum(v[1] for k, v in prof.items() if k.startswith("gemm3xtf32")))
-    out = dict(m=m, d=d, ms=ms, gflops=W / ms / 1e6, flop_per_step=W,
-               roofline=dict(bound="tensor", achieved=W / ms / 1e9, peak=tf32_peak / 3.0, unit="TFLOP/s",
-                             frac=(W / ms / 1e9) / (tf32_peak / 3.0),
-                             # dram read + write bytes of the two CTA-pair GEMM launches (Gram 35.4 GB + force 66.8 GB)
-                             traffic=102233679000 if (m, d) == (16384, 10000) else None,
-                             traffic_source="profiles/r01i_ncu_gemm3xtf32_pair_m16384_d10000.txt",
-                             note="logical FP32-equivalent peak = TF32 peak / 3 (3xTF32); TF32 peak = 1100 x measured bf16 / 2250; "
-                                  "W counts the full Gram, the symmetric kernel executes about half of it, so frac can pass 1; "
-                                  "ncu: tensor pipe 95-96 % active in both GEMMs"),
-               kernels={k: dict(launches=v[0] // reps if reps else v[0], ms_per_step=v[1] / reps) for k, v in prof.items()})
-    gm = gemm_ms[1] / max(reps, 1)
+    out = stein_point(m, d, ms, 1, pk)
+    out["kernels"] = {k: dict(launches=v[0] // reps if reps else v[0], ms_per_step=v[1] / reps) for k, v in prof.items()}
+    gm = sum(v[1] for k, v in prof.items() if k.startswith("gemm3xtf32")) / max(reps, 1)
     if gm > 0:
-        out["gemm_only"] = dict(ms_per_step=gm, tflops=W / gm / 1e9, frac=(W / gm / 1e9) / (tf32_peak / 3.0))
+        W = out["flop_per_step"]
+        burst, sus = tf32_peaks(pk)
+        ex = executed_mma_flop(m, d)
+        out["gemm_only"] = dict(ms_per_step=gm, tflops=W / gm / 1e9, frac=(W / gm / 1e9) / (burst / 3.0),
+                                frac_sustained_peak=(W / gm / 1e9) / (sus / 3.0),
+                                executed_tf32_tflops=ex / gm / 1e9, executed_frac=(ex / gm / 1e9) / burst,
+                                executed_frac_sustained_peak=(ex / gm / 1e9) / sus)
+    # untimed correctness record of the timed point: h bits, loss, sampled force rows against the float64 definition
+    _, loss, h = smi.ops.stein_force(X, G, out=F, path=smi.ops.PATH_TC)
+    out["check"] = force_rows_check(torch, X, G, F, 0, float(h))
+    out["check"]["loss"] = float(loss)
     return out
+
+
+def sharded_point(torch, m, d, reps, flush, pk, world):
+    """The sweep point on N GPUs (strong scaling: m fixed, rows sharded).  Every rank generates the SAME full X, G
+    as the N = 1 run (seed 4), so h / loss are comparable across world sizes; the untimed check compares sampled
+    force rows of every rank with the float64 definition and all-reduces the worst error."""
+    import torch.distributed as dist
+    from smi_experiments_b200.dist import bench_sharded_force
+    r = bench_sharded_force(m, d, reps, flush)
+    out = stein_point(m, d, r["ms"], world, pk)
+    out["kernels"] = r["kernels"]
+    out["collectives"] = r["collectives"]
+    nv = 2.0 * (world - 1) / world * m * d * 4.0
+    burst, _ = tf32_peaks(pk)
+    out["roofline"].update(nvlink_bytes_per_rank=nv, t_comm_ms_at_770GBs=nv / 770e9 * 1e3,
+                           t_flop_ms=4.0 * m * m * d / world / (burst / 3.0 * 1e12) * 1e3)
+    chk = force_rows_check(torch, r["X"], r["G"], r["F_rows"], r["row0"], r["h"])
+    worst = torch.tensor([chk["force_rows_rel_err_vs_float64"]], dtype=torch.float64, device=r["X"].device)
+    dist.all_reduce(worst, op=dist.ReduceOp.MAX)
+    hb = torch.tensor([int(chk["h_bits"], 16)], dtype=torch.int64, device=r["X"].device)
+    hmin, hmax = hb.clone(), hb.clone()
+    dist.all_reduce(hmin, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hmax, op=dist.ReduceOp.MAX)
+    chk.update(force_rows_rel_err_vs_float64=float(worst), ok=bool(float(worst) <= 1e-5), loss=r["loss"],
+               h_bits_equal_on_all_ranks=bool(int(hmin) == int(hmax)), rows_checked=chk["rows_checked"] * world)
+    out["check"] = chk
+    return out
+
+
+def executed_mma_flop(m, d):
+    """TF32 MMA FLOPs the two pair GEMMs execute: 3 MMAs per product term (3xTF32), padded tiles; the symmetric Gram
+    computes only the 256 x 256 pair tiles touching j >= i."""
+    T = (m + 255) // 256
+    kd, km = (d + 31) // 32 * 32, (m + 31) // 32 * 32
+    gram = T * (T + 1) // 2 * 256 * 256 * 2.0 * kd
+    force = T * ((d + 255) // 256) * 256 * 256 * 2.0 * km
+    return 3.0 * (gram + force)
+
+
+def stein_point(m, d, ms, world, pk):
+    """Roofline record of one Stein-force evaluation (W = 4 m^2 d) on `world` GPUs."""
+    W = 4.0 * m * m * d
+    burst, sus = tf32_peaks(pk)
+    ach = W / ms / 1e9
+    ex = executed_mma_flop(m, d)
+    traffic = None
+    src = "profiles/r02_ncu_c5_pair_gemms.txt"
+    if (m, d, world) == (16384, 10000, 1):
+        traffic = traffic_from_profile(src, "gemm3xtf32_pair_kernel")
+        if traffic is None:
+            src = "profiles/r01i_ncu_gemm3xtf32_pair_m16384_d10000.txt"
+            traffic = traffic_from_profile(src, "gemm3xtf32_pair_kernel")
+    return dict(m=m, d=d, ms=ms, gflops=W / ms / 1e6, flop_per_step=W,
+                roofline=dict(bound="tensor", achieved=ach, peak=world * burst / 3.0, unit="TFLOP/s",
+                              frac=ach / (world * burst / 3.0),
+                              peak_sustained=world * sus / 3.0, frac_sustained_peak=ach / (world * sus / 3.0),
+                              executed_tf32_tflops=ex / ms / 1e9, executed_frac=(ex / ms / 1e9) / (world * burst),
+                              executed_frac_sustained_peak=(ex / ms / 1e9) / (world * sus),
+                              traffic=traffic, traffic_source=src if traffic is not None else None,
+                              peak_source=pk["src"],
+                              note="logical FP32-equivalent peak = TF32 peak / 3 (3xTF32); TF32 peak DERIVED = 1100 x measured "
+                                   "bf16 / 2250 (burst: frac; sustained: frac_sustained_peak); W = 4 m^2 d counts the full Gram, "
+                                   "the symmetric kernel executes about half of it, so frac can pass 1 -- executed_* count the "
+                                   "TF32 MMA FLOPs actually issued (3 per term, symmetric Gram) over the WHOLE evaluation; "
+                                   "traffic = DRAM read + write bytes of the two GEMM launches from the named ncu summary"))
+
+
+def force_rows_check(torch, X, G, F_rows, row0, h, nsample=16, alpha=1.0, c_att=1.0):
+    """Relative error of `nsample` of the force rows this rank holds against the float64 DEFINITION
+    F_i = c_att sum_j K_ij g_j + (2 alpha / (h m)) (x_i sum_j K_ij - sum_j K_ij x_j), K_ij = exp(-|x_i - x_j|^2 / h)
+    evaluated with torch float64 on the device at the bandwidth the kernels selected (not an oracle/ import:
+    a definition check, as tests/test_gpu_stein.py::test_full_size_sweep_point_properties)."""
+    m, d = X.shape
+    n = F_rows.shape[0]
+    loc = torch.linspace(0, n - 1, min(nsample, n), device=X.device).round().long().unique()
+    rows = loc + row0
+    xr = X[rows].double()
+    d2 = torch.empty(len(rows), m, dtype=torch.float64, device=X.device)
+    for j0 in range(0, m, 2048):
+        xb = X[j0:j0 + 2048].double()
+        d2[:, j0:j0 + 2048] = ((xr * xr).sum(1)[:, None] + (xb * xb).sum(1)[None, :] - 2.0 * (xr @ xb.T)).clamp_min(0)
+    d2[torch.arange(len(rows), device=X.device), rows] = 0.0
+    K = torch.exp(-d2 / h)
+    c = 2.0 * alpha / (h * m)
+    Fref = torch.zeros(len(rows), d, dtype=torch.float64, device=X.device)
+    for j0 in range(0, m, 2048):
+        Fref += K[:, j0:j0 + 2048] @ (c_att * G[j0:j0 + 2048].double() - c * X[j0:j0 + 2048].double())
+    Fref += c * K.sum(1, keepdim=True) * xr
+    err = float((F_rows[loc].double() - Fref).norm() / Fref.norm())
+    import struct
+    return dict(h=h, h_bits="0x%08x" % struct.unpack("<I", struct.pack("<f", h))[0], rows_checked=len(rows),
+                force_rows_rel_err_vs_float64=err, ok=bool(err <= 1e-5))
 
 
 def bench_other_configs(torch, smi, dev, flush):
@@ -355,33 +518,36 @@ def run_gpu(args):
         dom_avg_ms = dom_ms / dom_cnt
         S, B, I, H = C2["S"], C2["B"], C2["in_dim"], 50
         roof = None
+        burst, sus = tf32_peaks(pk)
         if dom_name.startswith("bnn_reg"):
             # layer products, forward + backward: 3 x 2 x (B I H + B H H + B H) per draw
             flop = 3.0 * 2.0 * (B * I * H + B * H * H + B * H) * m_local * S
-            tf32_peak = 1100.0 * pk["bf16"] / 2250.0
-            roof = dict(kernel=dom_name, bound="tensor", achieved=flop / dom_avg_ms / 1e9, peak=tf32_peak / 3.0,
-                        unit="TFLOP/s", frac=(flop / dom_avg_ms / 1e9) / (tf32_peak / 3.0),
-                        traffic=27392768 if world == 1 else None,   # dram read + write bytes per launch, ncu capture
-                        traffic_source="profiles/r01g_ncu_bnn_reg_mma3_ct_kernel_C2.txt",
+            tc = dom_name.startswith("bnn_reg_tc")
+            src = "profiles/r02_ncu_bnn_reg_tc_kernel_C2.txt" if tc else "profiles/r01g_ncu_bnn_reg_mma3_ct_kernel_C2.txt"
+            roof = dict(kernel=dom_name, bound="tensor", achieved=flop / dom_avg_ms / 1e9, peak=burst / 3.0,
+                        unit="TFLOP/s", frac=(flop / dom_avg_ms / 1e9) / (burst / 3.0),
+                        peak_sustained=sus / 3.0, frac_sustained_peak=(flop / dom_avg_ms / 1e9) / (sus / 3.0),
+                        traffic=traffic_from_profile(src, "bnn_reg") if world == 1 else None, traffic_source=src,
                         algorithmic_flop=flop, peak_source=pk["src"],
-                        note="warp-level mma.sync 3xTF32 kernel (one CTA per ELBO draw, per-draw weights) against the "
-                             "tcgen05 3xTF32 roofline the north star names: peak = 1100 x measured bf16 / 2250 / 3")
+                        note=("tcgen05 3xTF32 per-draw kernel" if tc else "warp-level mma.sync 3xTF32 kernel") +
+                             " against the tcgen05 3xTF32 roofline the north star names: peak = 1100 x measured bf16 / 2250 / 3")
         else:
-            d_ = eng.layout.particle_dim
             L_ = eng.layout.latent_dim
             byt = 4.0 * (m_local * S * L_ * 3)
             roof = dict(kernel=dom_name, bound="hbm", achieved=byt / dom_avg_ms / 1e6, peak=pk["hbm"], unit="GB/s",
                         frac=(byt / dom_avg_ms / 1e6) / pk["hbm"], traffic=None, algorithmic_bytes=byt,
                         peak_source=pk["src"])
-        line = dict(metric=METRIC, value=value, unit="SMI steps/s (20-particle step units; x N under weak scaling)",
+        # whole step against the same tensor roofline (3.84 GFLOP of layer products per step)
+        step_flop = 3.0 * 2.0 * (B * I * H + B * H * H + B * H) * m_local * S
+        roof["step_frac"] = (step_flop / (dev_ms / steps) / 1e9) / (burst / 3.0)
+        cfg = bench_config(world)
+        cfg.update(l2="flushed between steps (256 MiB memset, untimed)", timing="cuda events per step, max over ranks",
+                   cuda_graph=bool(eng.use_cuda_graph))
+        line = dict(metric=METRIC, value=value, unit=UNIT,
                     n_gpus=world, steps=steps, warmup=max(args.warmup, 3), ms_per_step=dev_ms / steps,
                     higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
-                    config=dict(workload="uci_boston_bnn_smi (BASELINE configs[1]): 455x13 train, BNN 13-50-50-1 ReLU, "
-                                         "AutoNormal, minibatch 100, 100 ELBO draws, Adam",
-                                particles_per_gpu=m_local, particles_total=m_total, elbo_draws=S, minibatch=B,
-                                l2="flushed between steps (256 MiB memset, untimed)", timing="cuda events per step, max over ranks",
-                                cuda_graph=True),
-                    e2e=dict(value=e2e_v, unit="SMI steps/s", h2d_bytes_per_step=int(h2d), d2h_bytes_per_step=4,
+                    config=cfg,
+                    e2e=dict(value=e2e_v, unit=UNIT, h2d_bytes_per_step=int(h2d), d2h_bytes_per_step=4,
                              ms_per_step=e2e_ms / steps),
                     gpu_launches=int(launches * steps), launches_per_step=int(launches),
                     clocks=clocks, roofline=roof, kernels=kern, last_loss=last)
@@ -396,14 +562,12 @@ def run_gpu(args):
                 if world == 1:
                     p = bench_stein_sweep(torch, smi, dev, mm, 10000, reps, flush, pk)
                 else:
-                    from smi_experiments_b200.dist import bench_sharded_force
-                    p = bench_sharded_force(mm, 10000, reps, flush, pk)
+                    p = sharded_point(torch, mm, 10000, reps, flush, pk, world)
                 pts.append(dict(m=mm, ms=p["ms"], tflops=p["roofline"]["achieved"], frac=p["roofline"]["frac"]))
         if world == 1:
             sw = bench_stein_sweep(torch, smi, dev, args.sweep_m, 10000, args.sweep_reps, flush, pk)
         else:
-            from smi_experiments_b200.dist import bench_sharded_force
-            sw = bench_sharded_force(args.sweep_m, 10000, args.sweep_reps, flush, pk)
+            sw = sharded_point(torch, args.sweep_m, 10000, args.sweep_reps, flush, pk, world)
         if pts:
             pts.append(dict(m=sw["m"], ms=sw["ms"], tflops=sw["roofline"]["achieved"], frac=sw["roofline"]["frac"]))
             sw["sweep"] = pts
@@ -420,8 +584,26 @@ def run_gpu(args):
             step()
             n += 1
         dt = time.perf_counter() - t0
-        line["cpu_baseline"] = dict(value=n / dt, unit="SMI steps/s", cores=cores, kind="port",
+        line["cpu_baseline"] = dict(value=n / dt, unit=UNIT, cores=cores, kind="port",
                                     sample="%d full SMI steps of the same C2 workload (oracle port, torch-CPU fp32)" % n)
+    if rank == 0 and world == 1 and not args.no_cpu and not args.no_sweep:
+        # CPU baseline of the Stein stage: the oracle's algorithm (difference-form kernel) in
+        # torch fp32 on all host threads at m = 1024, d = 1e4; larger m extrapolated with m^2 (labelled)
+        from oracle import stein as ostein
+        rng = np.random.default_rng(4)
+        mc = 1024
+        Xc = rng.standard_normal((mc, 10000)).astype(np.float32)
+        Gc = rng.standard_normal((mc, 10000)).astype(np.float32)
+        t0 = time.perf_counter()
+        ostein.stein_force_torch(Xc, Gc, threads=os.cpu_count())
+        dt = time.perf_counter() - t0
+        sw = line["stein_force"]
+        scale = (sw["m"] / mc) ** 2
+        line["stein_force"]["cpu_baseline"] = dict(
+            value=4.0 * mc * mc * 10000 / dt / 1e9, unit="GFLOP/s (W = 4 m^2 d)", cores=os.cpu_count(), kind="port",
+            sample="one Stein-force evaluation at m = 1024, d = 10000 (oracle algorithm, torch-CPU fp32): %.2f s" % dt,
+            ms_at_m1024=dt * 1e3, ms_at_bench_m_extrapolated=dt * 1e3 * scale,
+            extrapolation="time ~ m^2 at fixed d (labelled extrapolation, BASELINE.md section 3)")
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:

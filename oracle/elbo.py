@@ -80,9 +80,11 @@ def particle_elbo(spec, psi, i, eps_i, idx_i, x, y, n_total, tau=1.0, guide="nor
 
 
 def elbo_grads(spec, psi, eps, idx, x=None, y=None, n_total=None, tau=1.0, guide="normal",
-               dtype=torch.float32):
+               dtype=torch.float32, rows=None):
     """G (m, d) = vmap_i grad_{psi_i} mean_s ELBO_is  and  elbo (m,).
-    psi (m, d); eps (m, S, L) or None; idx (m, S, B) or None."""
+    psi (m, d); eps (m, S, L) or None; idx (m, S, B) or None.
+    rows = (row0, nrows): only those particles' gradients (a row shard); eps / idx then hold
+    the shard's rows only and the results have nrows rows."""
     psi_t = torch.as_tensor(np.asarray(psi)).to(dtype)
     m, d = psi_t.shape
     x_t = None if x is None else torch.as_tensor(np.asarray(x)).to(dtype)
@@ -91,14 +93,16 @@ def elbo_grads(spec, psi, eps, idx, x=None, y=None, n_total=None, tau=1.0, guide
     else:
         y_np = np.asarray(y)
         y_t = torch.as_tensor(y_np).to(dtype) if spec.kind != "bnn_cls" else torch.as_tensor(y_np).long()
-    G = torch.zeros(m, d, dtype=dtype)
-    E = torch.zeros(m, dtype=dtype)
-    for i in range(m):
+    row0, nrows = (0, m) if rows is None else rows
+    G = torch.zeros(nrows, d, dtype=dtype)
+    E = torch.zeros(nrows, dtype=dtype)
+    for r in range(nrows):
+        i = row0 + r
         leaf = psi_t[i].clone().requires_grad_(True)
-        eps_i = None if eps is None else torch.as_tensor(np.asarray(eps[i])).to(dtype)
-        idx_i = None if idx is None else torch.as_tensor(np.asarray(idx[i])).long()
+        eps_i = None if eps is None else torch.as_tensor(np.asarray(eps[r])).to(dtype)
+        idx_i = None if idx is None else torch.as_tensor(np.array(idx[r])).long()
         val = particle_elbo(spec, psi_t, i, eps_i, idx_i, x_t, y_t, n_total, tau, guide, psi_i=leaf)
         (g,) = torch.autograd.grad(val, leaf)
-        G[i] = g
-        E[i] = val.detach()
+        G[r] = g
+        E[r] = val.detach()
     return G.numpy(), E.numpy()

@@ -203,20 +203,25 @@ class ShardedSteinVI(SteinVI):
             dist.all_gather_into_tensor(X, X[r0:r0 + n], group=self.group)      # in place
 
 
-def bench_sharded_force(m, d, reps, flush, pk):
-    """bench.py's Stein-force sweep point at N > 1: rank r holds rows of X, G; one timed unit =
-    all-gather X, all-gather G (overlapped), row-sharded force.  Max over ranks."""
+def bench_sharded_force(m, d, reps, flush):
+    """bench.py's Stein-force sweep point at N > 1: rank r owns rows [r0, r0 + n) of X, G; one timed unit =
+    all-gather X, all-gather G (overlapped), row-sharded force.  Max over ranks.  Every rank draws the SAME
+    full X, G (seed 4, as the N = 1 point does), so h and the loss are those of the N = 1 problem."""
     import numpy as np
     world, rank = dist.get_world_size(), dist.get_rank()
     dev = torch.device("cuda", torch.cuda.current_device())
     r0, n = partition(m, world, rank)
-    gen = torch.Generator(device=dev).manual_seed(4 + rank)
-    X = torch.empty(m, d, device=dev)
-    G = torch.empty(m, d, device=dev)
-    X[r0:r0 + n] = torch.randn(n, d, device=dev, generator=gen)
-    G[r0:r0 + n] = torch.randn(n, d, device=dev, generator=gen)
+    gen = torch.Generator(device=dev).manual_seed(4)
+    X = torch.randn(m, d, device=dev, generator=gen)
+    G = torch.randn(m, d, device=dev, generator=gen)
+    keep = (X[r0:r0 + n].clone(), G[r0:r0 + n].clone())
     be = LibsmiRows(m, d, r0, n, dev)
     side = torch.cuda.Stream(device=dev)
+
+    def scrub():
+        # only the local rows are valid before the unit: the gathers must deliver the rest
+        X.zero_(), G.zero_()
+        X[r0:r0 + n], G[r0:r0 + n] = keep
 
     def unit():
         cur = torch.cuda.current_stream()
@@ -227,11 +232,13 @@ def bench_sharded_force(m, d, reps, flush, pk):
         return stein_force_rows(be, X, G, wait_G=lambda: cur.wait_stream(side))
 
     for _ in range(2):
+        scrub()
         unit()
     torch.cuda.synchronize()
     dist.barrier()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
     for a, b in evs:
+        scrub()
         flush()
         dist.barrier()
         a.record()
@@ -244,7 +251,6 @@ def bench_sharded_force(m, d, reps, flush, pk):
     unit()
     torch.cuda.synchronize()
     lib.smi_profile(0)
-    import ctypes as C
     buf = C.create_string_buffer(1 << 16)
     lib.smi_profile_report(buf, len(buf))
     kern = {}
@@ -253,15 +259,7 @@ def bench_sharded_force(m, d, reps, flush, pk):
         kern[nm] = dict(launches=int(cnt), ms_per_step=float(tms))
     ms = torch.tensor([float(np.mean([a.elapsed_time(b) for a, b in evs]))], dtype=torch.float64, device=dev)
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms = float(ms)
-    W = 4.0 * m * m * d
-    tf32_peak = 1100.0 * pk["bf16"] / 2250.0
-    peak = world * tf32_peak / 3.0
-    nv_bytes = 2.0 * (world - 1) / world * m * d * 4.0          # received per rank per step
-    t_comm = nv_bytes / 770e9 * 1e3
-    t_flop = W / world / (tf32_peak / 3.0 * 1e12) * 1e3
-    return dict(m=m, d=d, ms=ms, gflops=W / ms / 1e6, flop_per_step=W, loss=float(loss), h=float(h), kernels=kern,
-                roofline=dict(bound="tensor", achieved=W / ms / 1e9, peak=peak, unit="TFLOP/s",
-                              frac=(W / ms / 1e9) / peak, traffic=None,
-                              nvlink_bytes_per_rank=nv_bytes, t_comm_ms_at_770GBs=t_comm, t_flop_ms=t_flop,
-                              note="N x (TF32 peak / 3); fused target = max(t_flop, t_comm)"))
+    return dict(ms=float(ms), loss=float(loss), h=float(h), kernels=kern, X=X, G=G, F_rows=F, row0=r0,
+                collectives="ncclAllGather(X) blocking, ncclAllGather(G) on a side stream, 3 x ncclAllReduce(SUM, "
+                            "2048 x int32 histogram), ncclAllReduce(SUM count) + ncclAllReduce(MIN), ncclAllReduce(SUM, "
+                            "double sum F^2)")

@@ -161,10 +161,20 @@ def asvgd_tau(step, step0, num_steps, num_cycles, trans_speed, m, out):
 PRNG_LAYOUTS = {"partitionable": 1, "legacy": 0}   # SMI_PRNG_PARTITIONABLE / SMI_PRNG_LEGACY
 
 
+_prng_gen = [0]
+
+
+def prng_generation():
+    """Bumped whenever a process-wide PRNG switch changes: part of the engines' CUDA-graph signature."""
+    return _prng_gen[0]
+
+
 def set_prng_layout(layout):
     """Threefry stream layout of every PRNG launch (jax_threefry_partitionable on / off; JAX >= 0.5 / older).
     Process-wide.  Returns the previous layout's name; ``None`` only queries."""
     code = load().smi_prng_layout(-1 if layout is None else PRNG_LAYOUTS[layout])
+    if layout is not None:
+        _prng_gen[0] += 1
     return "partitionable" if code == 1 else "legacy"
 
 
@@ -177,6 +187,8 @@ def set_randint_rule(rule):
     (jax.random.choice without replacement = sort-based permutation, its branch on any other backend).
     Process-wide.  Returns the previous rule's name; ``None`` only queries."""
     code = load().smi_prng_randint(-1 if rule is None else SUBSAMPLE_RULES[rule])
+    if rule is not None:
+        _prng_gen[0] += 1
     return {v: k for k, v in SUBSAMPLE_RULES.items()}[code]
 
 

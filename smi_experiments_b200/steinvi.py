@@ -330,24 +330,34 @@ class SteinVI:
         ring = getattr(self, "_ring", None)
         if not self.use_cuda_graph or not self._graphable():
             self._eager(st, b, data, ring)
-            return st, b["loss"].reshape(())
+            return st, self._loss_out(b)
+        # everything the captured launches bake in: buffer addresses AND the host scalars / process-wide PRNG
+        # switches (the reference assigns engine.loss_temperature per step, src/engine_run.py:24: a changed
+        # scalar re-captures instead of silently replaying the old value)
         sig = (data["x"].data_ptr() if data["x"] is not None else 0,
                data["y"].data_ptr() if data["y"] is not None else 0, data["lik_scale"],
                ring.data_ptr() if ring is not None else 0,
-               self._es["avg"].data_ptr() if getattr(self, "_es", None) is not None else 0)
+               self._es["avg"].data_ptr() if getattr(self, "_es", None) is not None else 0,
+               self.loss_temperature, self.repulsion_temperature, self.c_att, self.kernel_fn.median_mode,
+               self.kernel_fn.h_fixed, ops.prng_generation())
         if self._graph is None or self._graph_sig != sig:
             if getattr(self, "_warm_sig", None) != sig:
                 # first call with these buffers: run eagerly (sets kernel attributes), capture next time
                 self._warm_sig = sig
                 self._eager(st, b, data, ring)
-                return st, b["loss"].reshape(())
+                return st, self._loss_out(b)
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
                 self._launch(st, b, data, True, ring)
             self._graph, self._graph_sig = g, sig
             # capture does not execute: fall through to the replay for this step
         self._graph.replay()
-        return st, b["loss"].reshape(())
+        return st, self._loss_out(b)
+
+    def _loss_out(self, b):
+        """The step's loss as its OWN device scalar: `losses.append(loss)` keeps every value (the single
+        loss buffer is overwritten by the next step; run() collects through the device ring instead)."""
+        return b["loss"].clone().reshape(())
 
     def _graphable(self):
         return True
