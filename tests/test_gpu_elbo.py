@@ -52,7 +52,14 @@ def test_uci_bnn_smi(cuda, m, S, N, B, I):
     idx = None if B == N else np.stack([rng.permutation(N)[:B] for _ in range(m * S)]).reshape(m, S, B).astype(np.int32)
     G, E = _run(cuda, md, psi, eps, idx, x, y, S, B, N / B, 1.0)
     G64, E64 = oelbo.elbo_grads(om, psi.astype(np.float64), eps, idx, x, y, N, 1.0, "normal", torch.float64)
-    assert _rel(G, G64) <= RTOL
+    tol = RTOL
+    if m * S * B >= 100000:
+        # full-size C2: 2 x 10^7 ReLU pre-activations per evaluation, a few of them within fp32 rounding of the kink;
+        # each flips one 0/1 derivative, so fp32 itself is ill-conditioned there (the fp32 oracle is up to 1.5e-5 from
+        # float64).  Calibrate with the fp32 oracle's own distance to float64, as for raw pixels below.
+        G32, _ = oelbo.elbo_grads(om, psi, eps, idx, x, y, N, 1.0, "normal", torch.float32)
+        tol = max(RTOL, 2.0 * _rel(G32, G64))
+    assert _rel(G, G64) <= tol
     assert np.max(np.abs(E - E64) / np.abs(E64)) <= RTOL
 
 

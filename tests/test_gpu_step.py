@@ -28,7 +28,7 @@ def _snap(state):
                 key=state.rng_key.cpu().numpy().view(np.uint32).copy())
 
 
-def _oracle_step(om, guide, snap, m, S, x, y, N, B, tau, alpha, optimizer, lr, plate_only=False):
+def _oracle_step(om, guide, snap, m, S, x, y, N, B, tau, alpha, optimizer, lr, plate_only=False, dtype=np.float64):
     next_key, attractive = ostep.draw_keys(snap["key"])
     if plate_only:      # a subsampling plate that consumes its subkey but whose indices are unused
         eps, _ = ostep.draw_noise(attractive, m, S, om, guide, N, 1)
@@ -36,17 +36,26 @@ def _oracle_step(om, guide, snap, m, S, x, y, N, B, tau, alpha, optimizer, lr, p
     else:
         eps, idx = ostep.draw_noise(attractive, m, S, om, guide, N if (B and B < N) else None,
                                     B if (B and B < N) else None)
-    out = ostep.smi_step(om, snap["psi"], (snap["a"], snap["b"]), snap["it"], eps, idx, x, y, N, guide, tau, alpha,
-                         1.0, optimizer, lr, dtype=np.float64)
+    out = ostep.smi_step(om, snap["psi"].astype(dtype), (snap["a"].astype(dtype), snap["b"].astype(dtype)), snap["it"], eps,
+                         idx, x, y, N, guide, tau, alpha, 1.0, optimizer, lr, dtype=dtype)
     out["key"] = next_key
     return out
 
 
-def _check(state, loss, ref):
-    assert abs(float(loss) - float(ref["loss"])) <= RTOL * float(ref["loss"])
-    assert _rel(state.optim_state.x.cpu().numpy(), ref["psi"]) <= RTOL
-    assert _rel(state.optim_state.a.cpu().numpy(), ref["opt_state"][0]) <= RTOL
-    assert _rel(state.optim_state.b.cpu().numpy(), ref["opt_state"][1]) <= 2 * RTOL
+def _check(state, loss, ref, r32=None):
+    """r32: the float32 oracle's result of the same step.  Where fp32 itself is ill-conditioned (ReLU kinks at the
+    full C2 size: 2 x 10^7 pre-activations per step, a few of them within rounding of zero, each flipping one
+    0/1 derivative -- the fp32 oracle differs from float64 by ~1.5e-5 there) the tolerance is
+    max(1e-5, 2 x the fp32 oracle's own distance to float64), as for the raw-pixel classifier inputs."""
+    def tol(a32, a64, base=RTOL):
+        return base if r32 is None else max(base, 2.0 * _rel(a32, a64))
+    tl = RTOL if r32 is None else max(RTOL, 2.0 * abs(float(r32["loss"]) - float(ref["loss"])) / float(ref["loss"]))
+    assert abs(float(loss) - float(ref["loss"])) <= tl * float(ref["loss"])
+    assert _rel(state.optim_state.x.cpu().numpy(), ref["psi"]) <= tol(r32["psi"] if r32 else None, ref["psi"])
+    assert _rel(state.optim_state.a.cpu().numpy(), ref["opt_state"][0]) <= tol(r32["opt_state"][0] if r32 else None,
+                                                                              ref["opt_state"][0])
+    assert _rel(state.optim_state.b.cpu().numpy(), ref["opt_state"][1]) <= tol(r32["opt_state"][1] if r32 else None,
+                                                                              ref["opt_state"][1], 2 * RTOL)
     assert (state.rng_key.cpu().numpy().view(np.uint32) == ref["key"]).all()
 
 
@@ -253,7 +262,8 @@ def test_c2_timed_shape_full_update(cuda):
         snap = _snap(state)
         state, loss = eng.update(state, x=xt, y=yt, subsample=B)
         ref = _oracle_step(om, "normal", snap, m, S, xt, yt, N, B, 1.0, 1.0, "adam", c["lr"])
-        _check(state, loss, ref)
+        r32 = _oracle_step(om, "normal", snap, m, S, xt, yt, N, B, 1.0, 1.0, "adam", c["lr"], dtype=np.float32)
+        _check(state, loss, ref, r32)
     assert eng._graph is not None
 
 
