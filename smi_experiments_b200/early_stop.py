@@ -122,6 +122,7 @@ class OnlineEarlyStop:
             if 0 < done < num_steps:
                 losses[done:] = losses[done - 1]
             self.steps_run = done
+            e._host_step = start + done        # the device counter froze at the stop: re-sync the host mirror
             self.stopped_early = bool(int(es["skip"].item()))
         finally:
             e._ring = None

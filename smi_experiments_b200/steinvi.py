@@ -239,6 +239,7 @@ class SteinVI:
                        os_.a.to(dev).clone(), os_.b.to(dev).clone()),
             _key_tensor(state.rng_key, dev))
         self._graph = None
+        self._host_step = int(self._state.optim_state.step.item())
         return self._state
 
     # ---- the step --------------------------------------------------------------------------
@@ -298,6 +299,7 @@ class SteinVI:
                 psi[:, r["rho"]:r["rho"] + r["size"]] = models.softplus_inv(self.guide.init_scale)
         self._state = SteinVIState(self.optim.init(psi), keys5[0].clone())
         self._graph = None
+        self._host_step = 0
         return self._state
 
     def get_params(self, state):
@@ -328,9 +330,15 @@ class SteinVI:
         data = self._bind(args, kwargs)
         b = self._alloc(data)
         ring = getattr(self, "_ring", None)
+        if ring is None:
+            # loss history on the device: the commit kernel stores every step's loss in its own slot, so the
+            # returned scalar is not overwritten by later steps and costs no extra launch
+            if getattr(self, "_hist", None) is None:
+                self._hist = torch.zeros(self.LOSS_HISTORY, dtype=torch.float32, device=self.device)
+            ring = self._hist
         if not self.use_cuda_graph or not self._graphable():
             self._eager(st, b, data, ring)
-            return st, self._loss_out(b)
+            return st, self._loss_out(b, ring)
         # everything the captured launches bake in: buffer addresses AND the host scalars / process-wide PRNG
         # switches (the reference assigns engine.loss_temperature per step, src/engine_run.py:24: a changed
         # scalar re-captures instead of silently replaying the old value)
@@ -345,19 +353,26 @@ class SteinVI:
                 # first call with these buffers: run eagerly (sets kernel attributes), capture next time
                 self._warm_sig = sig
                 self._eager(st, b, data, ring)
-                return st, self._loss_out(b)
+                return st, self._loss_out(b, ring)
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
                 self._launch(st, b, data, True, ring)
             self._graph, self._graph_sig = g, sig
             # capture does not execute: fall through to the replay for this step
         self._graph.replay()
-        return st, self._loss_out(b)
+        return st, self._loss_out(b, ring)
 
-    def _loss_out(self, b):
-        """The step's loss as its OWN device scalar: `losses.append(loss)` keeps every value (the single
-        loss buffer is overwritten by the next step; run() collects through the device ring instead)."""
-        return b["loss"].clone().reshape(())
+    LOSS_HISTORY = 1 << 20     # slots of the default loss ring (4 MB); a returned loss lives until the ring wraps
+
+    def _loss_out(self, b, ring):
+        """The step's loss as its OWN device scalar: `losses.append(loss)` keeps every value.  The commit kernel
+        wrote it to ring[t mod len] with t = the step counter before the update, which the host mirrors
+        (`_host_step`); with an early-stop flag the device counter may freeze, so that path clones instead."""
+        t = self._host_step
+        self._host_step = t + 1
+        if getattr(self, "_es", None) is not None:
+            return b["loss"].clone().reshape(())
+        return ring[t % ring.numel()]
 
     def _graphable(self):
         return True
