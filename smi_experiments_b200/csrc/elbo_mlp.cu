@@ -430,6 +430,10 @@ size_t reg_smem_bytes(int L, int I, int H, int B) {
 int smi_bnn_reg_mma_launch(const SmiModelDesc& md, const float* Z, const int32_t* idx, const float* x, const float* y,
                            int ndraws, int B, float lik_scale, const int* off7, float* DZ, float* LOGP,
                            cudaStream_t st);
+bool smi_bnn_reg_tc_eligible(const SmiModelDesc& md, int B, size_t* smem_bytes);
+int smi_bnn_reg_tc_launch(const SmiModelDesc& md, const float* Z, const int32_t* idx, const float* x, const float* y,
+                          int ndraws, int B, float lik_scale, const int* off7, float* DZ, float* LOGP,
+                          cudaStream_t st);
 int smi_model_cls_logp_grad(const SmiModelDesc& md, const float* Z, const float* x, const int32_t* y, int ndraws,
                             int B, float lik_scale, float* DZ, float* LOGP, cudaStream_t st);
 
@@ -464,6 +468,10 @@ int smi_model_logp_grad(const SmiModelDesc& md, const float* Z, const int32_t* i
     static const bool use_fma = getenv("SMI_BNN_FMA") != nullptr;
     if (!use_fma) {
       const int off7[7] = {o.prec, o.w1, o.b1, o.w2, o.b2, o.w3, o.b3};
+      // tcgen05 per-draw kernel (elbo_bnn_tc.cu) for every shape of the reference's regression experiments
+      // (I <= 15 inputs, H <= 55 hidden units, minibatch <= 128); the warp-level mma.sync kernel beyond
+      if (smi_bnn_reg_tc_eligible(md, B, nullptr))
+        return smi_bnn_reg_tc_launch(md, Z, idx, x, (const float*)y, ndraws, B, lik_scale, off7, DZ, LOGP, st);
       return smi_bnn_reg_mma_launch(md, Z, idx, x, (const float*)y, ndraws, B, lik_scale, off7, DZ, LOGP, st);
     }
   }
