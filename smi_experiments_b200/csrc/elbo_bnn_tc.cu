@@ -179,7 +179,7 @@ bnn_reg_tc_kernel(const float* __restrict__ Z, const int32_t* __restrict__ idx, 
   float* rawbuf[2] = {(float*)(smem + oRaw), (float*)(smem + oRaw + raw_bytes)};
   Small& sm = *(Small*)(smem + oRaw + 2 * raw_bytes);
 #ifdef SMI_BNN_TRACE
-  __shared__ unsigned long long tr[16];
+  unsigned long long tr[12];   // registers: the 227 KB of shared memory are spoken for
 #endif
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -611,7 +611,11 @@ bnn_reg_tc_kernel(const float* __restrict__ Z, const int32_t* __restrict__ idx, 
 }  // namespace
 
 bool smi_bnn_reg_tc_eligible(const SmiModelDesc& md, int B, size_t* smem_bytes) {
-  static const bool off = getenv("SMI_BNN_TC") && getenv("SMI_BNN_TC")[0] == '0';   // comparison runs: mma.sync kernel
+  // Measured on B200 at the C2 shape (profiles/r02c_*): 230 us per launch against 162 us for the warp-level mma.sync
+  // kernel (elbo_bnn_mma.cu) -- one draw per SM at a time, 16.6 us per draw of barrier-separated phases, against three
+  // co-resident draws per SM there.  Until it wins it is opt-in: SMI_BNN_TC=1 (read per call, so tests can switch it).
+  const char* e = getenv("SMI_BNN_TC");
+  const bool off = !(e && e[0] == '1');
   const size_t raw_bytes = smi_align_up((size_t)md.latent_dim * sizeof(float), 256);
   const size_t need = oRaw + 2 * raw_bytes + sizeof(Small);
   if (smem_bytes) *smem_bytes = need;

@@ -183,3 +183,28 @@ def test_row_sharding(cuda):
     G, E = _run(cuda, md, psi, eps, None, x, y, S, B, 1.0, 1.0)
     G2, E2 = _run(cuda, md, psi, eps[2:5], None, x, y, S, B, 1.0, 1.0, row0=2, nrows=3)
     assert np.array_equal(G2, G[2:5]) and np.array_equal(E2, E[2:5])
+
+
+@pytest.mark.parametrize("m,S,N,B,I,act,noise", [(3, 4, 30, 7, 13, "relu", "gamma"), (5, 100, 455, 100, 13, "tanh", "gamma"),
+                                                 (4, 9, 64, 64, 5, "tanh", "fixed"), (2, 5, 128, 128, 1, "tanh", "fixed"),
+                                                 (3, 150, 40, 33, 15, "relu", "gamma")])
+def test_bnn_reg_tcgen05_kernel(cuda, monkeypatch, m, S, N, B, I, act, noise):
+    """The per-draw tcgen05 kernel (csrc/elbo_bnn_tc.cu; opt-in with SMI_BNN_TC=1 while it is slower than the
+    mma.sync kernel) against the float64 oracle: ragged minibatches, one input, more draws than SMs.  The large
+    case uses tanh so that the strict 1e-5 bar applies (no ReLU-kink flips, see test_uci_bnn_smi)."""
+    from smi_experiments_b200 import models
+    monkeypatch.setenv("SMI_BNN_TC", "1")
+    pm = models.BNNRegression(I, 50, act, noise)
+    om = omodels.ModelSpec("bnn_reg", I, 50, 1, act, noise)
+    md, psi, eps, rng, L, d = _setup(pm, om, "normal", m, S, seed=m + S + I)
+    x = rng.standard_normal((N, I)).astype(np.float32)
+    y = (x @ rng.standard_normal(I) * 0.3 + 0.1 * rng.standard_normal(N)).astype(np.float32)
+    idx = None if B == N else np.stack([rng.permutation(N)[:B] for _ in range(m * S)]).reshape(m, S, B).astype(np.int32)
+    G, E = _run(cuda, md, psi, eps, idx, x, y, S, B, N / B, 1.0)
+    G64, E64 = oelbo.elbo_grads(om, psi.astype(np.float64), eps, idx, x, y, N, 1.0, "normal", torch.float64)
+    tol = RTOL
+    if act == "relu" and m * S * B >= 40000:
+        G32, _ = oelbo.elbo_grads(om, psi, eps, idx, x, y, N, 1.0, "normal", torch.float32)
+        tol = max(RTOL, 4.0 * _rel(G32, G64))
+    assert _rel(G, G64) <= tol
+    assert np.max(np.abs(E - E64) / np.abs(E64)) <= RTOL
