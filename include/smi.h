@@ -146,6 +146,19 @@ size_t smi_median_bandwidth_workspace_bytes(int m);
 int smi_median_bandwidth_f32(const float* D2, int m, int median_mode, float* h, uint32_t* rank_out,
                              void* ws, size_t ws_bytes, void* stream);
 
+/* No-allocation variant of smi_median_bandwidth_f32.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops,
+ * harnesses that forbid it).  Same inputs / outputs, no workspace argument: the 8.7 KB of select scratch live in a
+ * file-scope device array of libsmi.so (16 KB per GPU that loads the library, held until exit), resolved once per
+ * device with cudaGetSymbolAddress.  Limit: m <= SMI_NOALLOC_MAX_M, larger m returns SMI_ELIMIT with a message.
+ * Calls no cudaMalloc / cudaFree / allocating routine.  All calls on a device share the one array (it keeps the
+ * previous call's contents; what must start at zero is cleared on the stream by every call): calls that OVERLAP on
+ * the same GPU race -- serialise them on one stream.                                                           */
+#define SMI_NOALLOC_MAX_M 32768
+int smi_median_bandwidth_noalloc_max_m(void);
+int smi_median_bandwidth_noalloc_f32(const float* D2, int m, int median_mode, float* h, uint32_t* rank_out,
+                                     void* stream);
+
 /* ---- Row-sharded Stein force (no counterpart in the single-device reference).
  *   One process per GPU owns particle rows [row0, row0 + rows).  X and G hold ALL m particles
  *   (the caller all-gathers them over NCCL).  Stages, with the caller's collectives between:

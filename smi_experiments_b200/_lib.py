@@ -68,6 +68,8 @@ PROTOTYPES = {
     "smi_sqdist_f32": (_I, [_P, _I, _I, _I, _P, _P, _Z, _P]),
     "smi_median_bandwidth_workspace_bytes": (_Z, [_I]),
     "smi_median_bandwidth_f32": (_I, [_P, _I, _I, _P, _P, _P, _Z, _P]),
+    "smi_median_bandwidth_noalloc_max_m": (_I, []),
+    "smi_median_bandwidth_noalloc_f32": (_I, [_P, _I, _I, _P, _P, _P]),
     "smi_stein_rows_workspace_bytes": (_Z, [_I, _I, _I]),
     "smi_stein_rows_dist": (_I, [_P, _I, _I, _I, _I, _P, _Z, _P]),
     "smi_stein_rows_hist": (_I, [_I, _I, _I, _I, _I, _P, _P, _Z, _P]),

@@ -275,3 +275,46 @@ SMI_API int smi_median_bandwidth_f32(const float* D2, int m, int median_mode, fl
   return smi_select_bandwidth(D2, m, median_mode, 1.0f, h, nullptr, rank_out, ws, ws_bytes,
                               (cudaStream_t)stream);
 }
+
+// ---- no-allocation variant (no counterpart in the reference) ------
+// smi_median_bandwidth_f32 takes its scratch (8.7 KB of radix-select state + histogram) from the caller, who
+// normally gets it from cudaMalloc / torch.  Callers that cannot allocate -- code under CUDA-graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc -- use this entry point instead: the scratch is a file-scope
+// device array that every GPU loading libsmi.so holds until exit (16 KB).  The array's name is a host-side stand-in
+// in host code, NOT a device address: its address is resolved with cudaGetSymbolAddress once per device, with that
+// device current, and only that pointer is handed to the kernels.
+//   * limit: m <= SMI_NOALLOC_MAX_M (32768 particles: m^2 = 2^30 keys stay inside the 32-bit counters);
+//   * calls no cudaMalloc / cudaFree / allocating routine; inputs and outputs stay caller-owned;
+//   * every call on a device shares the ONE array, which keeps the previous call's contents: the part that must
+//     start at zero (the histogram) is cleared on the stream at the start of every call, the select state is
+//     re-initialised by the first scan; two calls that OVERLAP on the same GPU (different streams) race.
+constexpr size_t kNoAllocScratchBytes = 16384;
+static __device__ __align__(256) unsigned char g_select_noalloc_scratch[kNoAllocScratchBytes];
+constexpr int kNoAllocMaxDevices = 64;
+static void* g_noalloc_ptr[kNoAllocMaxDevices];   // device address of the array, per device ordinal
+
+SMI_API int smi_median_bandwidth_noalloc_max_m(void) { return SMI_NOALLOC_MAX_M; }
+
+SMI_API int smi_median_bandwidth_noalloc_f32(const float* D2, int m, int median_mode, float* h, uint32_t* rank_out,
+                                             void* stream) {
+  if (!D2 || !h) SMI_FAIL(SMI_EINVAL, "smi_median_bandwidth_noalloc_f32: null pointer");
+  if (m < 1) SMI_FAIL(SMI_EINVAL, "smi_median_bandwidth_noalloc_f32: m=%d", m);
+  if (m > SMI_NOALLOC_MAX_M)
+    SMI_FAIL(SMI_ELIMIT, "smi_median_bandwidth_noalloc_f32: m=%d exceeds the no-allocation limit of %d particles "
+                         "(use smi_median_bandwidth_f32 with a caller-owned workspace)", m, SMI_NOALLOC_MAX_M);
+  if (((uintptr_t)D2 & 15) != 0) SMI_FAIL(SMI_EINVAL, "smi_median_bandwidth_noalloc_f32: D2 must be 16-byte aligned");
+  static_assert(kNoAllocScratchBytes >= 256 + kBins * sizeof(unsigned) + 256 + 512, "scratch array too small");
+  int dev = -1;
+  SMI_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) SMI_FAIL(SMI_ELIMIT, "smi_median_bandwidth_noalloc_f32: device %d", dev);
+  void* p = g_noalloc_ptr[dev];
+  if (!p) {   // set-up, once per device, with that device current
+    SMI_CUDA_OK(cudaGetSymbolAddress((void**)&p, g_select_noalloc_scratch));
+    if (!p) SMI_FAIL(SMI_ECUDA, "cudaGetSymbolAddress returned a null scratch address");
+    g_noalloc_ptr[dev] = p;
+  }
+  if (kNoAllocScratchBytes < smi_select_workspace_bytes()) SMI_FAIL(SMI_ENOSPC, "scratch array too small");
+  // smi_select_bandwidth clears the histogram (cudaMemsetAsync on the stream) before the first pass
+  return smi_select_bandwidth(D2, m, median_mode, 1.0f, h, nullptr, rank_out, p, kNoAllocScratchBytes,
+                              (cudaStream_t)stream);
+}
