@@ -184,6 +184,30 @@ int smi_stein_rows_bandwidth(int m, int d, int row0, int rows, int median_mode, 
 int smi_stein_rows_force(const float* X, const float* G, int m, int d, int row0, int rows, float c_att,
                          float* F_rows, double* sumsq, void* ws, size_t ws_bytes, void* stream);
 
+/* ---- Block-symmetric variant of the row-sharded distance stage ("must overlap"; no counterpart in
+ *   the single-device reference).  The world is a ring of row blocks: rank i computes its own diagonal block
+ *   (upper tiles + mirror) and the `right` = world / 2 blocks after it, and receives the blocks to its left as the
+ *   transposes of what the ranks before it computed, so every unordered block pair is computed once, as on one GPU.
+ *   Only the particles of half the ring are needed before the Gram; the rest may arrive until smi_stein_rows_force.
+ *     smi_stein_sym_colsum -> all-gather `part` (64 x d doubles, slab-ordered) -> smi_stein_sym_mean
+ *     smi_stein_sym_split(own rows), smi_stein_sym_split(each right block as it arrives) -> smi_stein_sym_gram
+ *     per right block o < world / 2 (and o = world / 2 for odd worlds): smi_stein_sym_pack_t -> send to rank i + o;
+ *     per left block received from rank i - o: smi_stein_sym_unpack
+ *     then smi_stein_rows_hist / scan / tail / bandwidth / force exactly as above (same workspace).
+ *   h keeps the bits of the single-GPU path (slab-ordered mean, same accumulation sequence per particle pair).
+ *   smi_stein_sym_supported: rows % 256 == 0, rows a multiple of m / 64, no split-K shape; else use the API above. */
+int smi_stein_sym_supported(int m, int d, int rows);
+int smi_stein_sym_colsum(const float* X, int m, int d, int row0, int rows, double* part, void* ws, size_t ws_bytes,
+                         void* stream);
+int smi_stein_sym_mean(const double* part, int m, int d, int row0, int rows, void* ws, size_t ws_bytes, void* stream);
+int smi_stein_sym_split(const float* X, int m, int d, int row0, int rows, int r0, int nr, void* ws, size_t ws_bytes,
+                        void* stream);
+int smi_stein_sym_gram(int m, int d, int row0, int rows, int right, void* ws, size_t ws_bytes, void* stream);
+int smi_stein_sym_pack_t(int m, int d, int row0, int rows, int col0, float* out, void* ws, size_t ws_bytes,
+                         void* stream);
+int smi_stein_sym_unpack(const float* in, int m, int d, int row0, int rows, int col0, void* ws, size_t ws_bytes,
+                         void* stream);
+
 /* ---- Optimizers (row a8).  `grad_sign` multiplies F before use: the Stein step hands the
  *      optimizer -F, so pass -1.  `step` is a device int32 holding the number of updates
  *      applied so far; it is read, and incremented by one when `bump_step` is non-zero.

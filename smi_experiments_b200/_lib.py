@@ -77,6 +77,13 @@ PROTOTYPES = {
     "smi_stein_rows_tail": (_I, [_I, _I, _I, _I, _P, _P, _Z, _P]),
     "smi_stein_rows_bandwidth": (_I, [_I, _I, _I, _I, _I, _F, _F, _P, _P, _P, _P, _Z, _P]),
     "smi_stein_rows_force": (_I, [_P, _P, _I, _I, _I, _I, _F, _P, _P, _P, _Z, _P]),
+    "smi_stein_sym_supported": (_I, [_I, _I, _I]),
+    "smi_stein_sym_colsum": (_I, [_P, _I, _I, _I, _I, _P, _P, _Z, _P]),
+    "smi_stein_sym_mean": (_I, [_P, _I, _I, _I, _I, _P, _Z, _P]),
+    "smi_stein_sym_split": (_I, [_P, _I, _I, _I, _I, _I, _I, _P, _Z, _P]),
+    "smi_stein_sym_gram": (_I, [_I, _I, _I, _I, _I, _P, _Z, _P]),
+    "smi_stein_sym_pack_t": (_I, [_I, _I, _I, _I, _I, _P, _P, _Z, _P]),
+    "smi_stein_sym_unpack": (_I, [_P, _I, _I, _I, _I, _I, _P, _Z, _P]),
     "smi_adam_f32": (_I, [_P, _P, _P, _P, _F, _P, _I, _D, _D, _D, _D, _Z, _P]),
     "smi_adagrad_f32": (_I, [_P, _P, _P, _P, _F, _P, _I, _D, _D, _Z, _P]),
     "smi_elbo_grad_workspace_bytes": (_Z, [_MD, _I, _I, _I, _I]),

@@ -29,14 +29,15 @@ __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
 // form |a|^2 + |b|^2 - 2ab from cancelling when the particles share a large common offset.
 constexpr int kMeanSlabs = 64;
 __global__ void __launch_bounds__(256)
-colsum_kernel(const float* __restrict__ X, int m, int d, double* __restrict__ part) {
+colsum_kernel(const float* __restrict__ X, int m, int d, double* __restrict__ part, int slab0 = 0) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= d) return;
+  const int slab = slab0 + blockIdx.y;     // a row shard sums only its own slabs (slab0 > 0)
   const int per = (m + kMeanSlabs - 1) / kMeanSlabs;
-  const int r0 = blockIdx.y * per, r1 = min(m, r0 + per);
+  const int r0 = slab * per, r1 = min(m, r0 + per);
   double s = 0.0;
   for (int r = r0; r < r1; ++r) s += (double)__ldg(X + (size_t)r * d + k);
-  part[(size_t)blockIdx.y * d + k] = s;
+  part[(size_t)slab * d + k] = s;
 }
 __global__ void __launch_bounds__(256)
 colmean_kernel(const double* __restrict__ part, int m, int d, float* __restrict__ mean) {
@@ -495,5 +496,126 @@ SMI_API int smi_stein_rows_force(const float* X, const float* G, int m, int d, i
   SMI_PROF_BEGIN(st);
   sumsq_finish_kernel<<<1, 256, 0, st>>>(w.lpart, 256, sumsq);
   SMI_LAUNCH_OK_N("sumsq_finish_kernel", st);
+  return SMI_OK;
+}
+
+
+// ---- block-symmetric staged API (no counterpart in the single-device reference) -------------------
+// The row-sharded path above has every rank compute ALL m columns of its D2 rows (8 x 2.69 ms of Gram GPU-time at
+// m = 16384 on 8 GPUs against 13 ms on one, which only computes the upper triangle) after a blocking all-gather of
+// every particle, and repeat the column mean and the operand planes for all m rows.  Here the world is a ring of row
+// blocks: rank i computes its own (symmetric) diagonal block and the blocks (i, i+1) ... (i, i+half) to its right,
+// half = world / 2, and RECEIVES the blocks to its left as the transposes of what ranks i-1 ... computed -- every
+// unordered block pair is computed once, as on one GPU (for even worlds the antipodal block is computed by both).
+// It therefore needs the particles of half the ring before the Gram (the rest only for the Y planes, much later),
+// splits only those rows, and sums only its own slabs of the column mean (the slab partials are all-gathered, 5 MB,
+// and added in slab order on every rank: the mean, the distances and h keep the bits of the single-GPU path).
+//   colsum -> [all-gather 64 x d slab partials] -> mean -> split(own + right blocks) -> gram
+//          -> pack_t(block) [send to its other owner] ... unpack(block) [received] -> hist / scan / tail / bandwidth / force
+// Requirements (smi_stein_sym_supported): rows % 256 == 0, rows a multiple of the mean's slab height, no split-K.
+SMI_API int smi_stein_sym_supported(int m, int d, int rows) {
+  if (rows < 256 || rows % 256 != 0 || m % rows != 0 || m / rows < 2) return 0;
+  const int per = (m + kMeanSlabs - 1) / kMeanSlabs;
+  if (m % kMeanSlabs != 0 || rows % per != 0) return 0;
+  if (!tc_pair_enabled() || gram_ksplit(m, d) != 1) return 0;
+  return 1;
+}
+
+#define SYM_PROLOGUE()                                                                  \
+  ROWS_PROLOGUE();                                                                      \
+  if (!smi_stein_sym_supported(m, d, rows)) SMI_FAIL(SMI_ELIMIT, "stein_sym: (m=%d, d=%d, rows=%d) not supported", m, d, rows)
+
+// part: caller-owned [64 x d] doubles (all-gathered in place between the ranks); this call fills the local slabs.
+SMI_API int smi_stein_sym_colsum(const float* X, int m, int d, int row0, int rows, double* part, void* ws,
+                                 size_t ws_bytes, void* stream) {
+  SYM_PROLOGUE();
+  const int per = m / kMeanSlabs;
+  dim3 g((d + 255) / 256, rows / per);
+  SMI_PROF_BEGIN(st);
+  colsum_kernel<<<g, 256, 0, st>>>(X, m, d, part, row0 / per);
+  SMI_LAUNCH_OK_N("colsum_kernel", st);
+  return SMI_OK;
+}
+
+SMI_API int smi_stein_sym_mean(const double* part, int m, int d, int row0, int rows, void* ws, size_t ws_bytes,
+                               void* stream) {
+  SYM_PROLOGUE();
+  SMI_PROF_BEGIN(st);
+  colmean_kernel<<<(d + 255) / 256, 256, 0, st>>>(part, m, d, w.mean);
+  SMI_LAUNCH_OK_N("colmean_kernel", st);
+  return SMI_OK;
+}
+
+// Operand planes + squared norms of particle rows [r0, r0 + nr) (any rows that have arrived).
+SMI_API int smi_stein_sym_split(const float* X, int m, int d, int row0, int rows, int r0, int nr, void* ws,
+                                size_t ws_bytes, void* stream) {
+  SYM_PROLOGUE();
+  if (r0 < 0 || nr < 1 || r0 + nr > m) SMI_FAIL(SMI_EINVAL, "stein_sym_split: rows [%d, %d)", r0, r0 + nr);
+  const int ldk = pad32(d);
+  SMI_PROF_BEGIN(st);
+  split_rows_kernel<<<nr, 256, 0, st>>>(X + (size_t)r0 * d, w.mean, d, ldk, w.Xh + (size_t)r0 * ldk,
+                                        w.Xl + (size_t)r0 * ldk, w.norms + r0);
+  SMI_LAUNCH_OK_N("split_rows_kernel", st);
+  return SMI_OK;
+}
+
+// D2 of the local rows against the own block and the `right` blocks after it (ring order, wrapping).
+SMI_API int smi_stein_sym_gram(int m, int d, int row0, int rows, int right, void* ws, size_t ws_bytes, void* stream) {
+  SYM_PROLOGUE();
+  if (right < 0 || (right + 1) * rows > m) SMI_FAIL(SMI_EINVAL, "stein_sym_gram: right=%d", right);
+  const int ldk = pad32(d);
+  tc::GemmArgs ga = {};
+  ga.M = rows;
+  ga.N = m;
+  ga.C = w.D2;
+  ga.ldc = m;
+  ga.na = w.norms + row0;
+  ga.nb = w.norms;
+  ga.diag_shift = row0;
+  ga.symmetric = 1;
+  ga.col_tile0 = row0 / tc::BN;
+  ga.col_tiles = (right + 1) * (rows / tc::BN);
+  ga.orient = 1;
+  return launch_gemm_pair<tc::EPI_GRAM>(w.Xh + (size_t)row0 * ldk, w.Xl + (size_t)row0 * ldk, rows, w.Xh, w.Xl, m, ldk,
+                                        ga, st);
+}
+
+// out[c][r] = D2[r][col0 + c]: the transposed (rows x rows) block at columns [col0, col0 + rows), contiguous.
+__global__ void __launch_bounds__(256)
+sym_pack_t_kernel(const float* __restrict__ D2, int m, int rows, int col0, float* __restrict__ out) {
+  __shared__ float tile[32][33];
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int i = ty; i < 32; i += 8) tile[i][tx] = D2[(size_t)(r0 + i) * m + col0 + c0 + tx];
+  __syncthreads();
+  for (int i = ty; i < 32; i += 8) out[(size_t)(c0 + i) * rows + r0 + tx] = tile[tx][i];
+}
+// D2[r][col0 + c] = in[r][c]
+__global__ void __launch_bounds__(256)
+sym_unpack_kernel(const float* __restrict__ in, int m, int rows, int col0, float* __restrict__ D2) {
+  const int r = blockIdx.y;
+  for (int c = (blockIdx.x * blockDim.x + threadIdx.x) * 4; c < rows; c += gridDim.x * blockDim.x * 4)
+    *reinterpret_cast<float4*>(D2 + (size_t)r * m + col0 + c) = *reinterpret_cast<const float4*>(in + (size_t)r * rows + c);
+}
+
+SMI_API int smi_stein_sym_pack_t(int m, int d, int row0, int rows, int col0, float* out, void* ws, size_t ws_bytes,
+                                 void* stream) {
+  SYM_PROLOGUE();
+  if (!out || col0 < 0 || col0 + rows > m || col0 % 4) SMI_FAIL(SMI_EINVAL, "stein_sym_pack_t: col0=%d", col0);
+  dim3 g(rows / 32, rows / 32);
+  SMI_PROF_BEGIN(st);
+  sym_pack_t_kernel<<<g, 256, 0, st>>>(w.D2, m, rows, col0, out);
+  SMI_LAUNCH_OK_N("sym_pack_t_kernel", st);
+  return SMI_OK;
+}
+
+SMI_API int smi_stein_sym_unpack(const float* in, int m, int d, int row0, int rows, int col0, void* ws,
+                                 size_t ws_bytes, void* stream) {
+  SYM_PROLOGUE();
+  if (!in || col0 < 0 || col0 + rows > m || col0 % 4 || ((uintptr_t)in & 15)) SMI_FAIL(SMI_EINVAL, "stein_sym_unpack: col0=%d", col0);
+  dim3 g((rows / 4 + 255) / 256, rows);
+  SMI_PROF_BEGIN(st);
+  sym_unpack_kernel<<<g, 256, 0, st>>>(in, m, rows, col0, w.D2);
+  SMI_LAUNCH_OK_N("sym_unpack_kernel", st);
   return SMI_OK;
 }

@@ -64,7 +64,23 @@ struct GemmArgs {
   float* part;
   long long part_stride;
   int part_ld;
+  // column window (pair kernel, EPI_GRAM; block-symmetric row sharding, dist.py): only `col_tiles` column tiles are
+  // computed, starting at tile `col_tile0` = diag_shift / BN (the shard's own diagonal block first) and wrapping
+  // modulo the ceil(N / BN) tiles of the full matrix.  0 = all column tiles in natural order.
+  int col_tile0, col_tiles;
+  // orient = 1: in tiles that lie entirely LEFT of the diagonal block the two cross products are issued as
+  // hi*lo then lo*hi, so that every unordered particle pair {a < b} sees the accumulation sequence
+  // a_lo b_hi, a_hi b_lo, a_hi b_hi of the single-GPU upper-triangle tile, whichever rank computes it.
+  int orient;
 };
+
+// Actual column tile of the enumerated tile index tn (column-window mode wraps around the matrix).
+__device__ __forceinline__ int actual_col_tile(const GemmArgs& a, int tn) {
+  if (a.col_tiles <= 0) return tn;
+  const int total = (a.N + BN - 1) / BN;
+  int t = a.col_tile0 + tn;
+  return t >= total ? t - total : t;
+}
 
 __device__ __forceinline__ void tile_coords(int t, int tiles_m, int tiles_n, int& tm, int& tn) {
   const int per_group = kGroupM * tiles_n;

@@ -37,7 +37,8 @@ __device__ __forceinline__ void pair_tile_coords(int t, int tiles_p, int tiles_n
 // ((tn + 1) * 256 > (2 tp + r) * 128  <=>  tn + 1 > tp for r = 0 and r = 1).
 __device__ __forceinline__ bool pair_tile_needed(const GemmArgs& a, int tp, int tn) {
   if (!a.symmetric) return true;
-  const int tb = tn - a.diag_shift / BN;            // column tile relative to the diagonal block
+  // column tile relative to the diagonal block (column-window mode enumerates from the block itself)
+  const int tb = a.col_tiles > 0 ? tn : tn - a.diag_shift / BN;
   return tb < 0 || tb + 1 > tp;
 }
 
@@ -144,7 +145,7 @@ gemm3xtf32_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
         int tp, tn, sg;
         while (it.next(args, tp, tn, sg)) {
           const int arow = (2 * tp + (int)rank) * BM;
-          const int brow = tn * BN + (int)rank * (BN / 2);
+          const int brow = actual_col_tile(args, tn) * BN + (int)rank * (BN / 2);
           int c0, c1;
           seg_chunks(args, nchunks, sg, c0, c1);
           const int kb_last = min(nkb, c1 * kChunkKB);
@@ -175,6 +176,8 @@ gemm3xtf32_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
         while (it.next(args, tp, tn, sg)) {
           int c0, c1;
           seg_chunks(args, nchunks, sg, c0, c1);
+          // tile entirely left of the diagonal block: issue hi*lo before lo*hi (GemmArgs::orient)
+          const bool flip = args.orient && (actual_col_tile(args, tn) + 1) * BN <= args.diag_shift;
           for (int ch = c0; ch < c1; ++ch) {
             mbar_wait(tempty + acc, acc_phase ^ 1);
             tc_fence_after();
@@ -192,8 +195,14 @@ gemm3xtf32_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
 #pragma unroll
               for (int ks = 0; ks < BK / 8; ++ks) {
                 const uint64_t adv = (uint64_t)(ks * 32 >> 4);
-                mma_tf32_ss_pair(d_tmem, a_lo + adv, b_hi + adv, idesc, first | (uint32_t)(ks != 0));
-                mma_tf32_ss_pair(d_tmem, a_hi + adv, b_lo + adv, idesc, 1u);
+                const uint32_t acc0 = first | (uint32_t)(ks != 0);
+                if (!flip) {
+                  mma_tf32_ss_pair(d_tmem, a_lo + adv, b_hi + adv, idesc, acc0);
+                  mma_tf32_ss_pair(d_tmem, a_hi + adv, b_lo + adv, idesc, 1u);
+                } else {
+                  mma_tf32_ss_pair(d_tmem, a_hi + adv, b_lo + adv, idesc, acc0);
+                  mma_tf32_ss_pair(d_tmem, a_lo + adv, b_hi + adv, idesc, 1u);
+                }
                 mma_tf32_ss_pair(d_tmem, a_hi + adv, b_hi + adv, idesc, 1u);
               }
               mma_commit_pair(empty + stage);   // slot free in both CTAs once these MMAs retire
@@ -249,12 +258,13 @@ gemm3xtf32_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
           acc_phase ^= 1;
         }
       }
+      const int tna = actual_col_tile(args, tn);
       if (EPI == EPI_GRAM && args.ksplit > 1) {
         // raw partial tile of this K segment (part_ld % 4 == 0; columns past N are zero)
         const int row = tm * BM + q * 32 + lane;
         if (row < args.M) {
           float* prow = args.part + (long long)sg * args.part_stride + (long long)row * args.part_ld;
-          const int colbase = tn * BN + half * kEpiCols;
+          const int colbase = tna * BN + half * kEpiCols;
 #pragma unroll
           for (int j = 0; j < kEpiCols; j += 4) {
             const int col = colbase + j;
@@ -264,7 +274,7 @@ gemm3xtf32_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
         }
         continue;
       }
-      tile_epilogue<EPI>(args, tm, tn, q, half, lane, c, sum, sq);
+      tile_epilogue<EPI>(args, tm, tna, q, half, lane, c, sum, sq);
     }
     if (EPI == EPI_FORCE) {
       sq = warp_sum(sq);

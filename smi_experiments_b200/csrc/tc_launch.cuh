@@ -93,7 +93,7 @@ int launch_gemm_pair(const float* Ah, const float* Al, long long a_rows, const f
   if ((rc = make_map(&mb_l, Bl, b_rows, ldk, tc::BN / 2))) return rc;
   ga.K = (int)ldk;
   ga.tiles_m = (ga.M + tc::BM - 1) / tc::BM;
-  ga.tiles_n = (ga.N + tc::BN - 1) / tc::BN;
+  ga.tiles_n = ga.col_tiles > 0 ? ga.col_tiles : (ga.N + tc::BN - 1) / tc::BN;   // column window: enumerated tiles only
   const int npairtiles = ((ga.tiles_m + 1) / 2) * ga.tiles_n * (ga.ksplit > 1 ? ga.ksplit : 1);   // work units
   const int maxpairs = smi_num_sms() / 2;
   const int pairs = npairtiles < maxpairs ? npairtiles : maxpairs;

@@ -18,8 +18,10 @@ object (LibsmiRows: the CUDA kernels through the C ABI).  The CPU test-suite dri
 choreography over gloo with a NumPy stand-in backend (tests/test_dist_gloo.py).
 """
 
+import contextlib
 import ctypes as C
 import math
+import os
 
 import torch
 import torch.distributed as dist
@@ -89,13 +91,143 @@ class LibsmiRows:
                   ops._ptr(self.F), ops._ptr(self.sumsq), *self._w(), ops._stream())
         return self.F, self.sumsq
 
+    # ---- block-symmetric stages (smi_stein_sym_* in include/smi.h) ----
+    def sym_supported(self):
+        return bool(_lib.load().smi_stein_sym_supported(self.m, self.d, self.rows))
+
+    def sym_setup(self, nsend):
+        """Buffers of the block-symmetric choreography: the slab partials of the column mean (64 x d doubles, all-gathered
+        in place) and the packed transposed D2 blocks that travel to / from their other owner."""
+        if getattr(self, "part", None) is None:
+            self.nslabs = 64
+            per = self.m // 64
+            self.slab0, self.slab1 = self.row0 // per, (self.row0 + self.rows) // per
+            self.part = torch.zeros(64, self.d, dtype=torch.float64, device=self.device)
+            self.sendbuf = torch.empty(max(nsend, 1), self.rows, self.rows, dtype=torch.float32, device=self.device)
+            self.recvbuf = torch.empty_like(self.sendbuf)
+
+    def colsum(self, X):
+        _lib.call("smi_stein_sym_colsum", ops._ptr(X), self.m, self.d, self.row0, self.rows, ops._ptr(self.part),
+                  *self._w(), ops._stream())
+
+    def mean(self):
+        _lib.call("smi_stein_sym_mean", ops._ptr(self.part), self.m, self.d, self.row0, self.rows, *self._w(),
+                  ops._stream())
+
+    def split(self, X, r0, nr):
+        _lib.call("smi_stein_sym_split", ops._ptr(X), self.m, self.d, self.row0, self.rows, r0, nr, *self._w(),
+                  ops._stream())
+
+    def gram(self, right):
+        _lib.call("smi_stein_sym_gram", self.m, self.d, self.row0, self.rows, right, *self._w(), ops._stream())
+
+    def pack_t(self, col0, slot):
+        _lib.call("smi_stein_sym_pack_t", self.m, self.d, self.row0, self.rows, col0, ops._ptr(self.sendbuf[slot]),
+                  *self._w(), ops._stream())
+
+    def unpack(self, slot, col0):
+        _lib.call("smi_stein_sym_unpack", ops._ptr(self.recvbuf[slot]), self.m, self.d, self.row0, self.rows, col0,
+                  *self._w(), ops._stream())
+
+
+class _SideStream:
+    """A second CUDA stream for the collectives that travel under compute (no-op for CPU tensors: the gloo tests)."""
+
+    def __init__(self, device):
+        self.cuda = torch.device(device).type == "cuda"
+        self.stream = torch.cuda.Stream(device=device) if self.cuda else None
+
+    def fork(self):
+        if self.cuda:
+            self.stream.wait_stream(torch.cuda.current_stream())
+
+    def ctx(self):
+        return torch.cuda.stream(self.stream) if self.cuda else contextlib.nullcontext()
+
+    def event(self):
+        if not self.cuda:
+            return None
+        e = torch.cuda.Event()
+        e.record(self.stream)
+        return e
+
+    @staticmethod
+    def join(e):
+        if e is not None:
+            torch.cuda.current_stream().wait_event(e)
+
+
+def _all_gather_in_place(out, rows, group):
+    """all_gather_into_tensor whose input is this rank's slice of the output (NCCL takes the alias; gloo wants a copy)."""
+    dist.all_gather_into_tensor(out, rows if out.is_cuda else rows.clone(), group=group)
+
+
+def _exchange(pairs, group):
+    """pairs: [(send_tensor, dst, recv_tensor, src)]: one grouped ncclSend / ncclRecv batch; returns when the current
+    stream may use the received data."""
+    if not pairs:
+        return
+    p2p = []
+    for snd, dst, rcv, src in pairs:
+        p2p.append(dist.P2POp(dist.isend, snd, dst, group))
+        p2p.append(dist.P2POp(dist.irecv, rcv, src, group))
+    for w in dist.batch_isend_irecv(p2p):
+        w.wait()
+
+
+def stein_force_sym(backend, X, G, group=None, alpha=1.0, c_att=1.0, median_mode=_lib.MEDIAN_JAX_FP32_INDEX,
+                    h_fixed=0.0, side=None):
+    """Row-sharded Stein force with the exchange INSIDE: on entry only the local rows of X and G are valid.
+    Block-symmetric ring (include/smi.h, smi_stein_sym_*): the particle blocks to the right of this rank arrive
+    first (grouped ncclSend / ncclRecv on a side stream) and feed the Gram, which computes the own diagonal block and
+    world / 2 blocks to its right; the blocks to the left come back as packed transposes from the ranks that
+    computed them; the remaining particle blocks and the all-gather of the scores travel under the Gram and are
+    only awaited before the force.  Returns (F_rows, loss, h); X and G are complete afterwards."""
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    n, r0 = backend.rows, backend.row0
+    half = world // 2
+    right = list(range(1, half + 1))
+    sendt = [o for o in right if not (world % 2 == 0 and o == half)]     # the antipodal block is computed by both owners
+    backend.sym_setup(len(sendt))
+    side = side if side is not None else _SideStream(X.device)
+    blk = lambda t, j: t[(j % world) * n:(j % world) * n + n]
+    gr = lambda j: dist.get_global_rank(group, j % world) if group is not None else j % world
+    # ---- communication, all on the side stream ----
+    side.fork()
+    with side.ctx():
+        _exchange([(blk(X, rank), gr(rank - o), blk(X, rank + o), gr(rank + o)) for o in right], group)
+        ev_a = side.event()
+        _exchange([(blk(X, rank), gr(rank - o), blk(X, rank + o), gr(rank + o)) for o in range(half + 1, world)], group)
+        _all_gather_in_place(G, blk(G, rank), group)
+        ev_b = side.event()
+    # ---- column mean from slab partials (every rank adds the 64 slabs in the same order) ----
+    backend.colsum(X)
+    _all_gather_in_place(backend.part, backend.part[backend.slab0:backend.slab1], group)
+    backend.mean()
+    backend.split(X, r0, n)
+    side.join(ev_a)
+    for o in right:
+        backend.split(X, ((rank + o) % world) * n, n)
+    backend.gram(len(right))
+    # ---- every unordered block pair was computed once: hand the transposes to their other owner ----
+    for s, o in enumerate(sendt):
+        backend.pack_t(((rank + o) % world) * n, s)
+    _exchange([(backend.sendbuf[s], gr(rank + o), backend.recvbuf[s], gr(rank - o)) for s, o in enumerate(sendt)], group)
+    for s, o in enumerate(sendt):
+        backend.unpack(s, ((rank - o) % world) * n)
+    return _select_and_force(backend, X, G, group, alpha, c_att, median_mode, h_fixed, lambda: side.join(ev_b))
+
 
 def stein_force_rows(backend, X, G, group=None, alpha=1.0, c_att=1.0, median_mode=_lib.MEDIAN_JAX_FP32_INDEX,
                      h_fixed=0.0, wait_G=None):
     """Row-sharded Stein force.  X, G: ALL m particles / scores (already all-gathered; G may still
     be in flight -- `wait_G()` is called right before the force stage).  Returns (F_rows, loss, h)."""
-    m = backend.m
     backend.dist(X)
+    return _select_and_force(backend, X, G, group, alpha, c_att, median_mode, h_fixed, wait_G)
+
+
+def _select_and_force(backend, X, G, group, alpha, c_att, median_mode, h_fixed, wait_G):
+    m = backend.m
     cnt = mn = None
     if not (h_fixed > 0.0 or m == 1):
         for p in range(3):
@@ -217,6 +349,8 @@ def bench_sharded_force(m, d, reps, flush):
     keep = (X[r0:r0 + n].clone(), G[r0:r0 + n].clone())
     be = LibsmiRows(m, d, r0, n, dev)
     side = torch.cuda.Stream(device=dev)
+    sym = be.sym_supported() and os.environ.get("SMI_SHARD_SYM", "1") != "0"
+    side2 = _SideStream(dev)
 
     def scrub():
         # only the local rows are valid before the unit: the gathers must deliver the rest
@@ -224,6 +358,8 @@ def bench_sharded_force(m, d, reps, flush):
         X[r0:r0 + n], G[r0:r0 + n] = keep
 
     def unit():
+        if sym:       # block-symmetric ring: the exchange is part of the choreography
+            return stein_force_sym(be, X, G, side=side2)
         cur = torch.cuda.current_stream()
         dist.all_gather_into_tensor(X, X[r0:r0 + n])
         side.wait_stream(cur)
@@ -260,6 +396,10 @@ def bench_sharded_force(m, d, reps, flush):
     ms = torch.tensor([float(np.mean([a.elapsed_time(b) for a, b in evs]))], dtype=torch.float64, device=dev)
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     return dict(ms=float(ms), loss=float(loss), h=float(h), kernels=kern, X=X, G=G, F_rows=F, row0=r0,
-                collectives="ncclAllGather(X) blocking, ncclAllGather(G) on a side stream, 3 x ncclAllReduce(SUM, "
-                            "2048 x int32 histogram), ncclAllReduce(SUM count) + ncclAllReduce(MIN), ncclAllReduce(SUM, "
-                            "double sum F^2)")
+                path="block-symmetric ring" if sym else "row blocks, all columns",
+                collectives=("side stream: grouped ncclSend/ncclRecv of the particle blocks right of the rank (before the "
+                             "Gram), then of the other blocks, then ncclAllGather(G); main stream: ncclAllGather(64 x d "
+                             "column-sum slabs), grouped ncclSend/ncclRecv of the transposed D2 blocks, " if sym else
+                             "ncclAllGather(X) blocking, ncclAllGather(G) on a side stream, ") +
+                            "3 x ncclAllReduce(SUM, 2048 x int32 histogram), ncclAllReduce(SUM count) + ncclAllReduce(MIN), "
+                            "ncclAllReduce(SUM, double sum F^2)")

@@ -35,7 +35,49 @@ class NumpyRows:
         self.keys = d2.view(np.uint32).ravel()
         self.prefix, self.rank = 0, None
 
+    # ---- block-symmetric stages (stand-ins for smi_stein_sym_*) ----
+    def sym_setup(self, nsend):
+        m, d, n = self.m, self.d, self.rows
+        self.part = torch.zeros(m, d, dtype=torch.float64)          # one slab per row
+        self.slab0, self.slab1 = self.row0, self.row0 + n
+        self.sendbuf = torch.zeros(max(nsend, 1), n, n)
+        self.recvbuf = torch.zeros(max(nsend, 1), n, n)
+        self.xc = np.full((m, d), np.nan)
+        self.d2 = np.full((n, m), np.nan, np.float32)
+        self.prefix, self.rank = 0, None
+
+    def colsum(self, X):
+        r = slice(self.row0, self.row0 + self.rows)
+        self.part[r] = X[r].double()
+
+    def mean(self):
+        self.mu = self.part.numpy().sum(0) / self.m
+
+    def split(self, X, r0, nr):
+        self.xc[r0:r0 + nr] = X[r0:r0 + nr].numpy().astype(np.float64) - self.mu
+
+    def gram(self, right):
+        n, world = self.rows, self.m // self.rows
+        me = self.row0 // n
+        xa = self.xc[self.row0:self.row0 + n]
+        for o in range(right + 1):
+            c0 = ((me + o) % world) * n
+            xb = self.xc[c0:c0 + n]
+            assert not np.isnan(xb).any()                              # its particles must have arrived and been split
+            blk = np.maximum((xa * xa).sum(1)[:, None] + (xb * xb).sum(1)[None, :] - 2.0 * xa @ xb.T, 0.0)
+            self.d2[:, c0:c0 + n] = blk.astype(np.float32)
+        self.d2[np.arange(n), np.arange(n) + self.row0] = 0.0
+
+    def pack_t(self, col0, slot):
+        self.sendbuf[slot] = torch.from_numpy(np.ascontiguousarray(self.d2[:, col0:col0 + self.rows].T))
+
+    def unpack(self, slot, col0):
+        self.d2[:, col0:col0 + self.rows] = self.recvbuf[slot].numpy()
+
     def hist(self, p):
+        if p == 0:
+            assert not np.isnan(self.d2).any()                         # every block computed or received
+            self.keys = self.d2.view(np.uint32).ravel()
         sh, nb = self.SHIFT[p], self.BITS[p]
         k = self.keys
         if p > 0:
@@ -84,11 +126,11 @@ class NumpyRows:
         return torch.from_numpy(F.astype(np.float32)), torch.tensor([float((F * F).sum())], dtype=torch.float64)
 
 
-def _worker(rank, world, port, m, d, out):
+def _worker(rank, world, port, m, d, out, sym=False):
     sys.path.insert(0, ROOT)
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    from smi_experiments_b200.dist import partition, stein_force_rows
+    from smi_experiments_b200.dist import partition, stein_force_rows, stein_force_sym
     rng = np.random.default_rng(0)
     Xf = rng.standard_normal((m, d)).astype(np.float32) + np.float32(2.0)
     Gf = rng.standard_normal((m, d)).astype(np.float32)
@@ -97,10 +139,14 @@ def _worker(rank, world, port, m, d, out):
     X, G = torch.zeros(m, d), torch.zeros(m, d)
     X[r0:r0 + n] = torch.from_numpy(Xf[r0:r0 + n])
     G[r0:r0 + n] = torch.from_numpy(Gf[r0:r0 + n])
-    dist.all_gather_into_tensor(X, X[r0:r0 + n].clone())
-    dist.all_gather_into_tensor(G, G[r0:r0 + n].clone())
     be = NumpyRows(m, d, r0, n)
-    F, loss, h = stein_force_rows(be, X, G, alpha=2.0)
+    if sym:       # the exchange is inside: only the local rows are valid on entry
+        F, loss, h = stein_force_sym(be, X, G, alpha=2.0)
+        assert torch.equal(X, torch.from_numpy(Xf)) and torch.equal(G, torch.from_numpy(Gf))
+    else:
+        dist.all_gather_into_tensor(X, X[r0:r0 + n].clone())
+        dist.all_gather_into_tensor(G, G[r0:r0 + n].clone())
+        F, loss, h = stein_force_rows(be, X, G, alpha=2.0)
     torch.save(dict(F=F, loss=loss, h=h, sel=be.sel, r0=r0, n=n), os.path.join(out, "r%d.pt" % rank))
     dist.destroy_process_group()
 
@@ -113,11 +159,14 @@ def _free_port():
     return p
 
 
-@pytest.mark.parametrize("world,m", [(2, 24), (3, 24), (2, 90)])
-def test_row_sharded_force_matches_unsharded(tmp_path, world, m):
+@pytest.mark.parametrize("world,m,sym", [(2, 24, False), (3, 24, False), (2, 90, False),
+                                         # block-symmetric ring: even world (antipodal block computed by both owners),
+                                         # odd world, and a world of 4 with one transposed block per rank
+                                         (2, 24, True), (3, 24, True), (4, 24, True)])
+def test_row_sharded_force_matches_unsharded(tmp_path, world, m, sym):
     from oracle import stein
     d = 40
-    mp.spawn(_worker, args=(world, _free_port(), m, d, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), m, d, str(tmp_path), sym), nprocs=world, join=True)
     rng = np.random.default_rng(0)
     X = rng.standard_normal((m, d)).astype(np.float32) + np.float32(2.0)
     G = rng.standard_normal((m, d)).astype(np.float32)
