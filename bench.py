@@ -296,6 +296,8 @@ def sharded_point(torch, m, d, reps, flush, pk, world):
     out = stein_point(m, d, r["ms"], world, pk)
     out["kernels"] = r["kernels"]
     out["collectives"] = r["collectives"]
+    out["path"] = r["path"]
+    out["timeline_ms_rank0"] = r["timeline"]
     nv = 2.0 * (world - 1) / world * m * d * 4.0
     burst, _ = tf32_peaks(pk)
     out["roofline"].update(nvlink_bytes_per_rank=nv, t_comm_ms_at_770GBs=nv / 770e9 * 1e3,

@@ -202,7 +202,8 @@ int smi_stein_sym_colsum(const float* X, int m, int d, int row0, int rows, doubl
 int smi_stein_sym_mean(const double* part, int m, int d, int row0, int rows, void* ws, size_t ws_bytes, void* stream);
 int smi_stein_sym_split(const float* X, int m, int d, int row0, int rows, int r0, int nr, void* ws, size_t ws_bytes,
                         void* stream);
-int smi_stein_sym_gram(int m, int d, int row0, int rows, int right, void* ws, size_t ws_bytes, void* stream);
+int smi_stein_sym_gram(int m, int d, int row0, int rows, int first, int count, void* ws, size_t ws_bytes,
+                       void* stream);   /* column blocks [first, first + count) after the own one, ring order */
 int smi_stein_sym_pack_t(int m, int d, int row0, int rows, int col0, float* out, void* ws, size_t ws_bytes,
                          void* stream);
 int smi_stein_sym_unpack(const float* in, int m, int d, int row0, int rows, int col0, void* ws, size_t ws_bytes,

@@ -81,7 +81,7 @@ PROTOTYPES = {
     "smi_stein_sym_colsum": (_I, [_P, _I, _I, _I, _I, _P, _P, _Z, _P]),
     "smi_stein_sym_mean": (_I, [_P, _I, _I, _I, _I, _P, _Z, _P]),
     "smi_stein_sym_split": (_I, [_P, _I, _I, _I, _I, _I, _I, _P, _Z, _P]),
-    "smi_stein_sym_gram": (_I, [_I, _I, _I, _I, _I, _P, _Z, _P]),
+    "smi_stein_sym_gram": (_I, [_I, _I, _I, _I, _I, _I, _P, _Z, _P]),
     "smi_stein_sym_pack_t": (_I, [_I, _I, _I, _I, _I, _P, _P, _Z, _P]),
     "smi_stein_sym_unpack": (_I, [_P, _I, _I, _I, _I, _I, _P, _Z, _P]),
     "smi_adam_f32": (_I, [_P, _P, _P, _P, _F, _P, _I, _D, _D, _D, _D, _Z, _P]),

@@ -559,10 +559,13 @@ SMI_API int smi_stein_sym_split(const float* X, int m, int d, int row0, int rows
   return SMI_OK;
 }
 
-// D2 of the local rows against the own block and the `right` blocks after it (ring order, wrapping).
-SMI_API int smi_stein_sym_gram(int m, int d, int row0, int rows, int right, void* ws, size_t ws_bytes, void* stream) {
+// D2 of the local rows against `count` column blocks starting `first` blocks after the own one (ring order, wrapping;
+// first = 0 starts with the own diagonal block, computed symmetrically).  Several calls may cover the window piecewise
+// as the particle blocks arrive.
+SMI_API int smi_stein_sym_gram(int m, int d, int row0, int rows, int first, int count, void* ws, size_t ws_bytes,
+                               void* stream) {
   SYM_PROLOGUE();
-  if (right < 0 || (right + 1) * rows > m) SMI_FAIL(SMI_EINVAL, "stein_sym_gram: right=%d", right);
+  if (first < 0 || count < 1 || (first + count) * rows > m) SMI_FAIL(SMI_EINVAL, "stein_sym_gram: blocks [%d, %d)", first, first + count);
   const int ldk = pad32(d);
   tc::GemmArgs ga = {};
   ga.M = rows;
@@ -572,9 +575,9 @@ SMI_API int smi_stein_sym_gram(int m, int d, int row0, int rows, int right, void
   ga.na = w.norms + row0;
   ga.nb = w.norms;
   ga.diag_shift = row0;
-  ga.symmetric = 1;
-  ga.col_tile0 = row0 / tc::BN;
-  ga.col_tiles = (right + 1) * (rows / tc::BN);
+  ga.symmetric = first == 0 ? 1 : 0;
+  ga.col_tile0 = (int)(((long long)row0 + (long long)first * rows) % m) / tc::BN;
+  ga.col_tiles = count * (rows / tc::BN);
   ga.orient = 1;
   return launch_gemm_pair<tc::EPI_GRAM>(w.Xh + (size_t)row0 * ldk, w.Xl + (size_t)row0 * ldk, rows, w.Xh, w.Xl, m, ldk,
                                         ga, st);

@@ -95,16 +95,18 @@ class LibsmiRows:
     def sym_supported(self):
         return bool(_lib.load().smi_stein_sym_supported(self.m, self.d, self.rows))
 
-    def sym_setup(self, nsend):
+    def sym_setup(self, nsend, sendbuf=None):
         """Buffers of the block-symmetric choreography: the slab partials of the column mean (64 x d doubles, all-gathered
-        in place) and the packed transposed D2 blocks that travel to / from their other owner."""
+        in place) and the packed transposed D2 blocks that travel to / from their other owner (`sendbuf`: a
+        symmetric-memory buffer the peers pull from, PeerPull.ts)."""
         if getattr(self, "part", None) is None:
             self.nslabs = 64
             per = self.m // 64
             self.slab0, self.slab1 = self.row0 // per, (self.row0 + self.rows) // per
             self.part = torch.zeros(64, self.d, dtype=torch.float64, device=self.device)
-            self.sendbuf = torch.empty(max(nsend, 1), self.rows, self.rows, dtype=torch.float32, device=self.device)
-            self.recvbuf = torch.empty_like(self.sendbuf)
+            self.sendbuf = sendbuf if sendbuf is not None else torch.empty(max(nsend, 1), self.rows, self.rows,
+                                                                           dtype=torch.float32, device=self.device)
+            self.recvbuf = torch.empty(max(nsend, 1), self.rows, self.rows, dtype=torch.float32, device=self.device)
 
     def colsum(self, X):
         _lib.call("smi_stein_sym_colsum", ops._ptr(X), self.m, self.d, self.row0, self.rows, ops._ptr(self.part),
@@ -118,8 +120,8 @@ class LibsmiRows:
         _lib.call("smi_stein_sym_split", ops._ptr(X), self.m, self.d, self.row0, self.rows, r0, nr, *self._w(),
                   ops._stream())
 
-    def gram(self, right):
-        _lib.call("smi_stein_sym_gram", self.m, self.d, self.row0, self.rows, right, *self._w(), ops._stream())
+    def gram(self, first, count):
+        _lib.call("smi_stein_sym_gram", self.m, self.d, self.row0, self.rows, first, count, *self._w(), ops._stream())
 
     def pack_t(self, col0, slot):
         _lib.call("smi_stein_sym_pack_t", self.m, self.d, self.row0, self.rows, col0, ops._ptr(self.sendbuf[slot]),
@@ -157,6 +159,49 @@ class _SideStream:
             torch.cuda.current_stream().wait_event(e)
 
 
+class PeerPull:
+    """Bulk movement of the row-sharded Stein force over NVLink peer memory instead of NCCL: every rank publishes its
+    particle rows, score rows and packed transposed D2 blocks in torch symmetric-memory buffers (CUDA IPC mappings),
+    and the ranks that need them PULL them with cudaMemcpyAsync on side streams -- copy engines, zero SMs.  NCCL's
+    kernels need SMs, and the persistent Gram / force GEMMs hold every SM with one 198 KB CTA: measured on 8 B200s
+    (profiles/r02f_sym_n8.json) the grouped ncclSend / ncclRecv of the particle blocks slowed from 1.2 ms to 2.0 ms
+    under the Gram and the all-gather of the scores from 1.0 ms to 1.5 ms, while a pull of one 82 MB block runs at
+    645 GB/s whatever the SMs do (scripts/probe/symm_probe.py)."""
+
+    def __init__(self, rows, d, nsend, device, group=None, nstreams=1):
+        import torch.distributed._symmetric_memory as symm
+        g = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.xs = symm.empty(rows, d, dtype=torch.float32, device=device)
+        self.gs = symm.empty(rows, d, dtype=torch.float32, device=device)
+        self.ts = symm.empty(max(nsend, 1), rows, rows, dtype=torch.float32, device=device)
+        hx, hg, ht = symm.rendezvous(self.xs, g), symm.rendezvous(self.gs, g), symm.rendezvous(self.ts, g)
+        peers = [p for p in range(self.world) if p != self.rank]
+        self.peer_x = {p: hx.get_buffer(p, (rows, d), torch.float32) for p in peers}
+        self.peer_g = {p: hg.get_buffer(p, (rows, d), torch.float32) for p in peers}
+        self.peer_t = {p: ht.get_buffer(p, (max(nsend, 1), rows, rows), torch.float32) for p in peers}
+        self._h = (hx, hg, ht)
+        self.streams = [torch.cuda.Stream(device=device) for _ in range(nstreams)]
+        self.flag = torch.zeros(1, dtype=torch.int32, device=device)
+
+    def fork(self):
+        cur = torch.cuda.current_stream()
+        for s in self.streams:
+            s.wait_stream(cur)
+
+    def pull(self, jobs):
+        """jobs: [(dst, src)] copied round-robin over the side streams; returns one event per stream."""
+        for k, (dst, src) in enumerate(jobs):
+            with torch.cuda.stream(self.streams[k % len(self.streams)]):
+                dst.copy_(src, non_blocking=True)
+        evs = []
+        for s in self.streams:
+            e = torch.cuda.Event()
+            e.record(s)
+            evs.append(e)
+        return evs
+
+
 def _all_gather_in_place(out, rows, group):
     """all_gather_into_tensor whose input is this rank's slice of the output (NCCL takes the alias; gloo wants a copy)."""
     dist.all_gather_into_tensor(out, rows if out.is_cuda else rows.clone(), group=group)
@@ -176,7 +221,7 @@ def _exchange(pairs, group):
 
 
 def stein_force_sym(backend, X, G, group=None, alpha=1.0, c_att=1.0, median_mode=_lib.MEDIAN_JAX_FP32_INDEX,
-                    h_fixed=0.0, side=None):
+                    h_fixed=0.0, side=None, trace=None, pull=None):
     """Row-sharded Stein force with the exchange INSIDE: on entry only the local rows of X and G are valid.
     Block-symmetric ring (include/smi.h, smi_stein_sym_*): the particle blocks to the right of this rank arrive
     first (grouped ncclSend / ncclRecv on a side stream) and feed the Gram, which computes the own diagonal block and
@@ -190,32 +235,80 @@ def stein_force_sym(backend, X, G, group=None, alpha=1.0, c_att=1.0, median_mode
     sendt = [o for o in right if not (world % 2 == 0 and o == half)]     # the antipodal block is computed by both owners
     backend.sym_setup(len(sendt))
     side = side if side is not None else _SideStream(X.device)
+    def mark(name, stream=None):        # optional timeline (scripts/time_sharded.py): CUDA events at the stage boundaries
+        if trace is not None:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record(stream) if stream is not None else e.record()
+            trace.append((name, e))
+    mark("start")
     blk = lambda t, j: t[(j % world) * n:(j % world) * n + n]
     gr = lambda j: dist.get_global_rank(group, j % world) if group is not None else j % world
-    # ---- communication, all on the side stream ----
-    side.fork()
-    with side.ctx():
-        _exchange([(blk(X, rank), gr(rank - o), blk(X, rank + o), gr(rank + o)) for o in right], group)
-        ev_a = side.event()
-        _exchange([(blk(X, rank), gr(rank - o), blk(X, rank + o), gr(rank + o)) for o in range(half + 1, world)], group)
-        _all_gather_in_place(G, blk(G, rank), group)
-        ev_b = side.event()
-    # ---- column mean from slab partials (every rank adds the 64 slabs in the same order) ----
+    joins = lambda evs: [torch.cuda.current_stream().wait_event(e) for e in evs]
+    if pull is not None:      # publish the local rows for the peers' copy-engine pulls
+        pull.xs.copy_(blk(X, rank))
+        pull.gs.copy_(blk(G, rank))
+    # ---- column mean from slab partials (every rank adds the 64 slabs in the same order).  Issued BEFORE any bulk
+    # NCCL exchange: collectives of one communicator execute in issue order, whatever stream they are on.  Its
+    # completion also tells this rank that every peer has published its rows ----
     backend.colsum(X)
     _all_gather_in_place(backend.part, backend.part[backend.slab0:backend.slab1], group)
+    if pull is not None:
+        # ---- bulk movement.  Copies on different streams were measured to share ONE copy engine (no concurrency,
+        # 0.22 ms per 82 MB block when all 8 ranks pull), so the pulls go on one stream in priority order; the right
+        # blocks, which the Gram waits for while the SMs are idle anyway, are halved between a grouped ncclSend/ncclRecv
+        # and the copy engine so that both paths into the NVLink port are busy ----
+        nn = (len(right) + 1) // 2
+        pull.fork()
+        side.fork()
+        with side.ctx():
+            _exchange([(blk(X, rank), gr(rank - o), blk(X, rank + o), gr(rank + o)) for o in right[:nn]], group)
+            e_n = side.event()
+            mark("side: right blocks by NCCL arrived", side.stream)
+        ev_a = pull.pull([(blk(X, rank + o), pull.peer_x[(rank + o) % world]) for o in right[nn:]])
+        mark("side: right blocks by copy engine arrived", pull.streams[0])
+        ev_b = pull.pull([(blk(X, rank + o), pull.peer_x[(rank + o) % world]) for o in range(half + 1, world)] +
+                         [(blk(G, rank + o), pull.peer_g[(rank + o) % world]) for o in range(1, world)])
+        mark("side: left blocks + G pulled", pull.streams[0])
+        wait_a, wait_b = (lambda: (side.join(e_n), joins(ev_a))), (lambda: joins(ev_b))
+    else:
+        # ---- bulk communication over NCCL / gloo on the side stream: right blocks, the rest, G ----
+        side.fork()
+        with side.ctx():
+            ex = lambda offs: _exchange([(blk(X, rank), gr(rank - o), blk(X, rank + o), gr(rank + o)) for o in offs], group)
+            ex(right)
+            e_a = side.event()
+            mark("side: right blocks arrived", side.stream)
+            ex(range(half + 1, world))
+            _all_gather_in_place(G, blk(G, rank), group)
+            e_b = side.event()
+            mark("side: left blocks + G arrived", side.stream)
+        wait_a, wait_b = (lambda: side.join(e_a)), (lambda: side.join(e_b))
     backend.mean()
     backend.split(X, r0, n)
-    side.join(ev_a)
+    mark("mean + own split")
+    wait_a()
+    mark("waited for the right blocks")
     for o in right:
         backend.split(X, ((rank + o) % world) * n, n)
-    backend.gram(len(right))
+    backend.gram(0, len(right) + 1)
+    mark("split + gram")
     # ---- every unordered block pair was computed once: hand the transposes to their other owner ----
-    for s, o in enumerate(sendt):
-        backend.pack_t(((rank + o) % world) * n, s)
-    _exchange([(backend.sendbuf[s], gr(rank + o), backend.recvbuf[s], gr(rank - o)) for s, o in enumerate(sendt)], group)
-    for s, o in enumerate(sendt):
-        backend.unpack(s, ((rank - o) % world) * n)
-    return _select_and_force(backend, X, G, group, alpha, c_att, median_mode, h_fixed, lambda: side.join(ev_b))
+    for s_, o in enumerate(sendt):
+        backend.pack_t(((rank + o) % world) * n, s_)
+    # (NCCL, not the copy engine: its queue still holds the bulk pulls, and the SMs are free between Gram and select)
+    if True:
+        _exchange([(backend.sendbuf[s_], gr(rank + o), backend.recvbuf[s_], gr(rank - o)) for s_, o in enumerate(sendt)], group)
+    for s_, o in enumerate(sendt):
+        backend.unpack(s_, ((rank - o) % world) * n)
+    mark("D2 blocks exchanged")
+
+    def wait_rest():
+        mark("select + bandwidth")
+        wait_b()
+        mark("waited for left blocks + G")
+    out = _select_and_force(backend, X, G, group, alpha, c_att, median_mode, h_fixed, wait_rest)
+    mark("force + loss")
+    return out
 
 
 def stein_force_rows(backend, X, G, group=None, alpha=1.0, c_att=1.0, median_mode=_lib.MEDIAN_JAX_FP32_INDEX,
@@ -351,6 +444,15 @@ def bench_sharded_force(m, d, reps, flush):
     side = torch.cuda.Stream(device=dev)
     sym = be.sym_supported() and os.environ.get("SMI_SHARD_SYM", "1") != "0"
     side2 = _SideStream(dev)
+    pull = None
+    if sym and os.environ.get("SMI_SHARD_PULL", "1") != "0":
+        half = world // 2
+        nsend = len([o for o in range(1, half + 1) if not (world % 2 == 0 and o == half)])
+        try:
+            pull = PeerPull(n, d, nsend, dev)
+        except Exception as ex:      # no CUDA IPC on this box: the NCCL exchange remains
+            if rank == 0:
+                print("PeerPull unavailable (%s): NCCL exchange" % ex, flush=True)
 
     def scrub():
         # only the local rows are valid before the unit: the gathers must deliver the rest
@@ -359,7 +461,7 @@ def bench_sharded_force(m, d, reps, flush):
 
     def unit():
         if sym:       # block-symmetric ring: the exchange is part of the choreography
-            return stein_force_sym(be, X, G, side=side2)
+            return stein_force_sym(be, X, G, side=side2, pull=pull)
         cur = torch.cuda.current_stream()
         dist.all_gather_into_tensor(X, X[r0:r0 + n])
         side.wait_stream(cur)
@@ -393,10 +495,19 @@ def bench_sharded_force(m, d, reps, flush):
     for ln in buf.value.decode().splitlines():
         nm, cnt, tms = ln.split()
         kern[nm] = dict(launches=int(cnt), ms_per_step=float(tms))
+    timeline = None
+    if sym:       # stage timeline of one more unit on this rank (ms since the start of the unit)
+        tr = []
+        scrub()
+        dist.barrier()
+        stein_force_sym(be, X, G, side=side2, trace=tr, pull=pull)
+        torch.cuda.synchronize()
+        timeline = {nm: round(tr[0][1].elapsed_time(e), 3) for nm, e in tr[1:]}
     ms = torch.tensor([float(np.mean([a.elapsed_time(b) for a, b in evs]))], dtype=torch.float64, device=dev)
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    return dict(ms=float(ms), loss=float(loss), h=float(h), kernels=kern, X=X, G=G, F_rows=F, row0=r0,
-                path="block-symmetric ring" if sym else "row blocks, all columns",
+    return dict(ms=float(ms), loss=float(loss), h=float(h), kernels=kern, X=X, G=G, F_rows=F, row0=r0, timeline=timeline,
+                path=("block-symmetric ring, " + ("copy-engine pulls over symmetric memory" if pull is not None else "NCCL exchange"))
+                if sym else "row blocks, all columns",
                 collectives=("side stream: grouped ncclSend/ncclRecv of the particle blocks right of the rank (before the "
                              "Gram), then of the other blocks, then ncclAllGather(G); main stream: ncclAllGather(64 x d "
                              "column-sum slabs), grouped ncclSend/ncclRecv of the transposed D2 blocks, " if sym else

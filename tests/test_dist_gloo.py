@@ -36,7 +36,7 @@ class NumpyRows:
         self.prefix, self.rank = 0, None
 
     # ---- block-symmetric stages (stand-ins for smi_stein_sym_*) ----
-    def sym_setup(self, nsend):
+    def sym_setup(self, nsend, sendbuf=None):
         m, d, n = self.m, self.d, self.rows
         self.part = torch.zeros(m, d, dtype=torch.float64)          # one slab per row
         self.slab0, self.slab1 = self.row0, self.row0 + n
@@ -56,11 +56,11 @@ class NumpyRows:
     def split(self, X, r0, nr):
         self.xc[r0:r0 + nr] = X[r0:r0 + nr].numpy().astype(np.float64) - self.mu
 
-    def gram(self, right):
+    def gram(self, first, count):
         n, world = self.rows, self.m // self.rows
         me = self.row0 // n
         xa = self.xc[self.row0:self.row0 + n]
-        for o in range(right + 1):
+        for o in range(first, first + count):
             c0 = ((me + o) % world) * n
             xb = self.xc[c0:c0 + n]
             assert not np.isnan(xb).any()                              # its particles must have arrived and been split
