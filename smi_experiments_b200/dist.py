@@ -257,13 +257,13 @@ def stein_force_sym(backend, X, G, group=None, alpha=1.0, c_att=1.0, median_mode
         # 0.22 ms per 82 MB block when all 8 ranks pull), so the pulls go on one stream in priority order; the right
         # blocks, which the Gram waits for while the SMs are idle anyway, are halved between a grouped ncclSend/ncclRecv
         # and the copy engine so that both paths into the NVLink port are busy ----
-        nn = (len(right) + 1) // 2
+        nn = len(right) // 2      # a single right block (worlds of 2, 3) goes by copy engine: one ncclSend/Recv pair runs at ~250 GB/s
         pull.fork()
         side.fork()
         with side.ctx():
             _exchange([(blk(X, rank), gr(rank - o), blk(X, rank + o), gr(rank + o)) for o in right[:nn]], group)
             e_n = side.event()
-            mark("side: right blocks by NCCL arrived", side.stream)
+            mark("side: right blocks by NCCL arrived", side.stream if side.cuda else None)
         ev_a = pull.pull([(blk(X, rank + o), pull.peer_x[(rank + o) % world]) for o in right[nn:]])
         mark("side: right blocks by copy engine arrived", pull.streams[0])
         ev_b = pull.pull([(blk(X, rank + o), pull.peer_x[(rank + o) % world]) for o in range(half + 1, world)] +
