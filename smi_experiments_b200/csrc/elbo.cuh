@@ -40,6 +40,9 @@ struct ElboWs {
   float* DZ;       // [nrows x S x L] d log p / d u
   float* QP;       // [nrows x nkq x S x m] partial quadratic forms
   float* W;        // [nrows x S x m]
+  int* NNZ;        // [nrows x S] components with a non-zero responsibility (exact zeros: expf underflow)
+  unsigned char* NZI;   // [nrows x S x m] their indices, ascending
+  int* nnz_total;  // [1] sum of NNZ over the rows of this call (zeroed by guide_prep)
   float* LOGQ;     // [nrows x S]
   float* LOGP;     // [nrows x S]
   int nkt;         // tiles of 64 latents (guide_grad grid)

@@ -36,8 +36,10 @@ __device__ __forceinline__ int find_site(const SmiModelDesc& md, int k) {
 __global__ void __launch_bounds__(256)
 guide_prep_kernel(const SmiModelDesc md, const float* __restrict__ psi, int m, int* __restrict__ loc_of,
                   int* __restrict__ rho_of, int* __restrict__ tr_of, float* __restrict__ MU,
-                  float* __restrict__ SIG, float* __restrict__ ISIG, double* __restrict__ logdet_part) {
+                  float* __restrict__ SIG, float* __restrict__ ISIG, double* __restrict__ logdet_part,
+                  int* __restrict__ nnz_total) {
   __shared__ double red[32];
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) *nnz_total = 0;
   const int L = md.latent_dim, d = md.particle_dim;
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = blockIdx.y;
@@ -72,7 +74,12 @@ guide_prep_kernel(const SmiModelDesc md, const float* __restrict__ psi, int m, i
 // KSUB > 1 (fewer, fatter partials for guide_weights) is used only when one pass covers all draws
 // and components (S <= 128, m <= 32).
 // smem: zt[64][128] (eps), mt[64][32] (A), it[64][32] (B), columns XOR-swizzled by ((k & 7) << 2); out[128][32].
-__global__ void __launch_bounds__(256, 3)
+// DA x DB = register block of a thread (draws x components).  4 x 4 costs 3 LDS.128 per 32 FMAs per latent: with four
+// warps issuing FMAs the shared-memory pipe (128 B / clock) is 1.5x oversubscribed -- harmless while the kernel is
+// latency-bound at m = 20, but at m = 160 (five component chunks per z tile, 255 us of a 0.9 ms step) it is the
+// limit; 8 x 8 needs 6 LDS.128 per 128 FMAs (0.75x).  Measured slower all the same (see smi_guide_sample): opt-in.
+template <int DA, int DB>
+__global__ void __launch_bounds__(256, DA * DB > 16 ? 2 : 3)
 guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU, const float* __restrict__ SIG,
                     const float* __restrict__ ISIG, int m, int S, int L, int row0, float* __restrict__ Z,
                     float* __restrict__ QP, int nkq, int ksub) {
@@ -81,11 +88,11 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
   float* mt = zt + kGuideKT * 128;      // [64][32]
   float* it = mt + kGuideKT * 32;       // [64][32]
   const int kq = blockIdx.x, r = blockIdx.y, i = row0 + r;
-  // component chunks of JCH = 4 * njg <= 32 columns chosen to divide m evenly (m = 20 -> one chunk
+  // component chunks of JCH = DB * njg <= 32 columns chosen to divide m evenly (m = 20 -> one chunk
   // of 20, not a padded 32)
   const int nch = (m + 31) / 32;
-  const int njg = (((m + nch - 1) / nch) + 3) >> 2, JCH = njg << 2;
-  const int nsg = (min(S, 128) + 3) >> 2;
+  const int njg = (((m + nch - 1) / nch) + DB - 1) / DB, JCH = njg * DB;
+  const int nsg = (min(S, 128) + DA - 1) / DA;
   const int nsj = njg * nsg;
   int KS = 1;
   while (KS < 8 && 2 * KS * nsj <= (int)blockDim.x) KS <<= 1;
@@ -95,11 +102,11 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
   for (int sb = 0; sb < S; sb += 128) {
     const int Sc = min(128, S - sb);
     for (int jb = 0; jb < m; jb += JCH) {
-      float acc[4][4];
+      float acc[DA][DB];
 #pragma unroll
-      for (int a = 0; a < 4; ++a)
+      for (int a = 0; a < DA; ++a)
 #pragma unroll
-        for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+        for (int b = 0; b < DB; ++b) acc[a][b] = 0.f;
       for (int sub = 0; sub < ksub; ++sub) {
         const int k0 = (kq * ksub + sub) * kGuideKT;
         if (k0 >= L) break;
@@ -135,21 +142,28 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
               zt[(kk + 1) * 128 + (s2 ^ (((kk + 1) & 7) << 2))] = ev[u].y;
             }
           }
+          if (DA > 4) {   // draws past Sc inside the last group of DA are read by the register blocks: keep them finite
+            for (int t = threadIdx.x; t < kGuideKT * (128 - Sc); t += blockDim.x) {
+              const int kk2 = t / (128 - Sc), s2 = Sc + t % (128 - Sc);
+              if (s2 < nsg * DA) zt[kk2 * 128 + (s2 ^ ((kk2 & 7) << 2))] = 0.f;
+            }
+          }
         } else {
-          for (int t = threadIdx.x; t < Sc * kGuideKT; t += blockDim.x) {
+          for (int t = threadIdx.x; t < 128 * kGuideKT; t += blockDim.x) {
             const int sl = t / kGuideKT, kk = t - sl * kGuideKT;
             const int s = sb + sl, k = k0 + kk;
             float ep = 0.f;
-            if (k < L) {
+            if (k < L && sl < Sc) {
               const size_t e = ((size_t)r * S + s) * L + k;
               ep = eps[e];
               if (jb == 0) Z[e] = fmaf(SIG[(size_t)i * L + k], ep, MU[(size_t)i * L + k]);
             }
-            zt[kk * 128 + (sl ^ ((kk & 7) << 2))] = ep;
+            if (sl < Sc || sl < nsg * DA) zt[kk * 128 + (sl ^ ((kk & 7) << 2))] = ep;
           }
         }
-        for (int t = threadIdx.x; t < JCH * kGuideKT; t += blockDim.x) {
+        for (int t = threadIdx.x; t < 32 * kGuideKT; t += blockDim.x) {
           const int jl = t / kGuideKT, kk = t - jl * kGuideKT;
+          if (jl >= JCH) break;
           const int j = jb + jl, k = k0 + kk;
           // (z - mu_j) / sigma_j with z = mu_i + sigma_i eps, as A + B eps: A = (mu_i - mu_j) / sigma_j,
           // B = sigma_i / sigma_j (one FMA per pair in the inner loop, and no cancellation against z);
@@ -166,19 +180,26 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
         }
         __syncthreads();
         if (lane_on) {
-#pragma unroll 4
+#pragma unroll 2
           for (int kk = ks * kper; kk < (ks + 1) * kper; ++kk) {
             const int sw = (kk & 7) << 2;
-            const float4 z4 = *reinterpret_cast<const float4*>(zt + kk * 128 + ((ts * 4) ^ sw));
-            const float4 m4 = *reinterpret_cast<const float4*>(mt + kk * 32 + ((tj * 4) ^ sw));
-            const float4 i4 = *reinterpret_cast<const float4*>(it + kk * 32 + ((tj * 4) ^ sw));
-            const float zz[4] = {z4.x, z4.y, z4.z, z4.w};
-            const float mm[4] = {m4.x, m4.y, m4.z, m4.w};
-            const float ii[4] = {i4.x, i4.y, i4.z, i4.w};
+            float zz[DA], mm[DB], ii[DB];
 #pragma unroll
-            for (int a = 0; a < 4; ++a)
+            for (int e = 0; e < DA; e += 4) {
+              const float4 z4 = *reinterpret_cast<const float4*>(zt + kk * 128 + ((ts * DA + e) ^ sw));
+              zz[e] = z4.x, zz[e + 1] = z4.y, zz[e + 2] = z4.z, zz[e + 3] = z4.w;
+            }
 #pragma unroll
-              for (int b = 0; b < 4; ++b) {
+            for (int e = 0; e < DB; e += 4) {
+              const float4 m4 = *reinterpret_cast<const float4*>(mt + kk * 32 + ((tj * DB + e) ^ sw));
+              const float4 i4 = *reinterpret_cast<const float4*>(it + kk * 32 + ((tj * DB + e) ^ sw));
+              mm[e] = m4.x, mm[e + 1] = m4.y, mm[e + 2] = m4.z, mm[e + 3] = m4.w;
+              ii[e] = i4.x, ii[e + 1] = i4.y, ii[e + 2] = i4.z, ii[e + 3] = i4.w;
+            }
+#pragma unroll
+            for (int a = 0; a < DA; ++a)
+#pragma unroll
+              for (int b = 0; b < DB; ++b) {
                 const float df = fmaf(ii[b], zz[a], mm[b]);
                 acc[a][b] = fmaf(df, df, acc[a][b]);
               }
@@ -186,31 +207,28 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
         }
       }
       // ---- sum the latent slices in a fixed order, write the partial ----
-      __syncthreads();
-      float* red = mt;   // [16][KS][nsj] over mt + it (4096 words): consecutive threads -> consecutive words
-      const int tlin = ts * njg + tj;
-      if (lane_on) {
-#pragma unroll
-        for (int a = 0; a < 4; ++a)
-#pragma unroll
-          for (int b = 0; b < 4; ++b) red[((a * 4 + b) * KS + ks) * nsj + tlin] = acc[a][b];
-      }
-      __syncthreads();
       // the slice sums go to shared memory as the [Sc][mc] block they form in QP, then out as whole
-      // rows (the per-thread 4 x 4 patches written directly cost 32 sectors per store instruction)
+      // rows (the per-thread patches written directly cost 32 sectors per store instruction)
       const int mc = min(JCH, m - jb);
+      float* red = mt;   // [16][KS][nsj] over mt + it (4096 words): consecutive threads -> consecutive words
       float* outb = it + kGuideKT * 32;    // [Sc][mc], its own 4096 words (zt must survive the chunk loop)
-      if (ks == 0) {
+      const int tlin = ts * njg + tj;
 #pragma unroll
-        for (int a = 0; a < 4; ++a) {
-          const int sl = ts * 4 + a;
-          if (sl >= Sc) continue;
+      for (int g = 0; g < DA * DB / 16; ++g) {   // 16 accumulators per round through the 4096-word buffer
+        __syncthreads();
+        if (lane_on) {
 #pragma unroll
-          for (int b = 0; b < 4; ++b) {
-            const int jl = tj * 4 + b;
-            if (jl >= mc) continue;
+          for (int e = 0; e < 16; ++e) red[(e * KS + ks) * nsj + tlin] = acc[(16 * g + e) / DB][(16 * g + e) % DB];
+        }
+        __syncthreads();
+        if (ks == 0) {
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {
+            const int a = (16 * g + e) / DB, b = (16 * g + e) % DB;
+            const int sl = ts * DA + a, jl = tj * DB + b;
+            if (sl >= Sc || jl >= mc) continue;
             float v = 0.f;
-            for (int q = 0; q < KS; ++q) v += red[((a * 4 + b) * KS + q) * nsj + tlin];
+            for (int q = 0; q < KS; ++q) v += red[(e * KS + q) * nsj + tlin];
             outb[sl * mc + jl] = v;
           }
         }
@@ -235,7 +253,8 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
 __global__ void __launch_bounds__(256)
 guide_weights_kernel(const SmiModelDesc md, const float* __restrict__ QP, const double* __restrict__ logdet_part,
                      int nlb, const float* __restrict__ Z, int m, int S, int nrows, int nkt,
-                     float* __restrict__ W, float* __restrict__ LOGQ) {
+                     float* __restrict__ W, float* __restrict__ LOGQ, int* __restrict__ NNZ,
+                     unsigned char* __restrict__ NZI, int* __restrict__ nnz_total) {
   const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (wid >= nrows * S) return;
   const int r = wid / S, s = wid - r * S;
@@ -266,6 +285,22 @@ guide_weights_kernel(const SmiModelDesc md, const float* __restrict__ QP, const 
 #pragma unroll
   for (int c = 0; c < kMaxCompPerLane; ++c)
     if (lane + 32 * c < m) W[((size_t)r * S + s) * m + lane + 32 * c] = e[c] / sum;
+  // compact list of the components whose responsibility is not EXACTLY zero (far components underflow in expf):
+  // the sparse gradient kernel visits only these and gets the same sums as a pass over all m
+  {
+    int base = 0;
+#pragma unroll
+    for (int c = 0; c < kMaxCompPerLane; ++c) {
+      const bool nz = e[c] != 0.f;
+      const unsigned mask = __ballot_sync(0xffffffffu, nz);
+      if (nz) NZI[((size_t)r * S + s) * m + base + __popc(mask & ((1u << lane) - 1u))] = (unsigned char)(lane + 32 * c);
+      base += __popc(mask);
+    }
+    if (lane == 0) {
+      NNZ[(size_t)r * S + s] = base;
+      atomicAdd(nnz_total, base);
+    }
+  }
   if (lane == 0) {
     float logjac = 0.f;  // log |d theta / d u| = u on exp sites
     for (int t = 0; t < md.n_sites; ++t)
@@ -372,6 +407,114 @@ guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, 
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// Sparse variant for many components (m > 48; the weak-scaling mixtures of 20 N particles).  With thousands of latent
+// dimensions the responsibilities of all but a few components underflow to exactly 0.f, and a term with w_j = 0 adds
+// exactly nothing to T = sum_j w_j (...): the kernel visits only the components guide_weights listed (NZI, ascending j)
+// and costs O(S nnz) per latent instead of O(S m) -- at m = 160 the dense split kernel is 210 us of a 0.9 ms step.
+// The data decides which kernel does the work, on the device: both are launched, this one runs when the lists are
+// short on average (*nnz_total <= thresh) and the dense one returns at once, and the other way round.
+__global__ void __launch_bounds__(256, 3)
+guide_grad_sparse_kernel(const float* __restrict__ psi, const float* __restrict__ eps, const float* __restrict__ MU,
+                         const float* __restrict__ SIG, const float* __restrict__ ISIG, const float* __restrict__ W,
+                         const float* __restrict__ DZ, const float* __restrict__ LOGP, const float* __restrict__ LOGQ,
+                         const int* __restrict__ NNZ, const unsigned char* __restrict__ NZI,
+                         const int* __restrict__ nnz_total, int thresh,
+                         const int* __restrict__ loc_of, const int* __restrict__ rho_of, const int* __restrict__ tr_of,
+                         int m, int S, int L, int d, float tau_host, const float* __restrict__ tau_dev, int row0,
+                         float* __restrict__ G, float* __restrict__ elbo) {
+  if (*nnz_total > thresh) return;
+  const float tau = tau_dev ? *tau_dev : tau_host;
+  __shared__ float part[kGradSG * kGradKT * 2];
+  const int kt = blockIdx.x, r = blockIdx.y, i = row0 + r;
+  const int kk = threadIdx.x & (kGradKT - 1), sg = threadIdx.x / kGradKT;
+  const int k = kt * kGradKT + kk;
+  float gl = 0.f, gs = 0.f;
+  if (k < L) {
+    const float mu_i = MU[(size_t)i * L + k], sg_i = SIG[(size_t)i * L + k], is_i = ISIG[(size_t)i * L + k];
+    const float q_i = is_i * is_i;
+    const float jac = tr_of[k] == SMI_T_EXP ? 1.f : 0.f;
+    constexpr int kBatch = 8;
+    for (int s0 = sg; s0 < S; s0 += kGradSG * kBatch) {
+      float epv[kBatch], dzv[kBatch];
+#pragma unroll
+      for (int u = 0; u < kBatch; ++u) {
+        const int s = s0 + u * kGradSG;
+        const size_t e = ((size_t)r * S + min(s, S - 1)) * L + k;
+        epv[u] = __ldcs(eps + e);
+        dzv[u] = __ldcs(DZ + e);
+      }
+      // the list heads of the 8 draws are fetched together (warp-uniform addresses): a chain of three dependent
+      // loads per draw -- count, first index, its weight -- would otherwise be paid 25 times in sequence
+      int nv[kBatch], j0v[kBatch];
+      float wiv[kBatch];
+#pragma unroll
+      for (int u = 0; u < kBatch; ++u) {
+        const size_t rs = (size_t)r * S + min(s0 + u * kGradSG, S - 1);
+        nv[u] = __ldg(NNZ + rs);
+        j0v[u] = __ldg(NZI + rs * m);
+        wiv[u] = __ldg(W + rs * m + i);
+      }
+      float w0v[kBatch];
+#pragma unroll
+      for (int u = 0; u < kBatch; ++u) {
+        const size_t rs = (size_t)r * S + min(s0 + u * kGradSG, S - 1);
+        w0v[u] = __ldg(W + rs * m + j0v[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < kBatch; ++u) {
+        const int s = s0 + u * kGradSG;
+        if (s < S) {
+          const size_t rs = (size_t)r * S + s;
+          const int n = nv[u];                              // warp-uniform
+          const float* wrow = W + rs * m;
+          const unsigned char* list = NZI + rs * m;
+          float T1 = 0.f, T2 = 0.f;
+          for (int t = 0; t < n; ++t) {
+            const int j = t == 0 ? j0v[u] : (int)__ldg(list + t);
+            const float wj = t == 0 ? w0v[u] : __ldg(wrow + j);
+            float q = q_i, cqv = 0.f;
+            if (j != i) {
+              const float is = __ldg(ISIG + (size_t)j * L + k);
+              q = is * is;
+              cqv = (mu_i - __ldg(MU + (size_t)j * L + k)) * q;
+            }
+            T1 = fmaf(wj, q, T1);
+            T2 = fmaf(wj, cqv, T2);
+          }
+          const float ep = epv[u];
+          const float T = fmaf(sg_i * ep, T1, T2);
+          const float du = fmaf(tau, dzv[u], T) + jac;
+          const float wi = wiv[u];
+          gl += du - wi * ep * is_i;
+          gs += du * ep - wi * (ep * ep - 1.f) * is_i;
+        }
+      }
+    }
+  }
+  part[(sg * kGradKT + kk) * 2] = gl;
+  part[(sg * kGradKT + kk) * 2 + 1] = gs;
+  __syncthreads();
+  if (sg == 0 && k < L) {
+    float a = 0.f, b = 0.f;
+#pragma unroll
+    for (int g = 0; g < kGradSG; ++g) {
+      a += part[(g * kGradKT + kk) * 2];
+      b += part[(g * kGradKT + kk) * 2 + 1];
+    }
+    const float inv = 1.f / (float)S;
+    G[(size_t)r * d + loc_of[k]] = a * inv;
+    G[(size_t)r * d + rho_of[k]] = b * inv * sigmoid_f(psi[(size_t)i * d + rho_of[k]]);
+  }
+  if (kt == 0 && elbo && threadIdx.x < 32) {
+    double v = 0.0;
+    for (int s = threadIdx.x; s < S; s += 32)
+      v += (double)tau * (double)LOGP[(size_t)r * S + s] - (double)LOGQ[(size_t)r * S + s];
+    v = warp_sum(v);
+    if (threadIdx.x == 0) elbo[r] = (float)(v / (double)S);
+  }
+}
+
 // 48 < m <= 192: the components are split over four thread groups (thread = latent column x component
 // group), each with its MPC-component tables in registers.  Per batch of 8 draws every thread writes its
 // partial (sum_j w q_j, sum_j w c_j) for the 8 draws to shared memory; after one barrier each thread
@@ -386,7 +529,8 @@ guide_grad_split_kernel(const float* __restrict__ psi, const float* __restrict__
                         const float* __restrict__ DZ, const float* __restrict__ LOGP, const float* __restrict__ LOGQ,
                         const int* __restrict__ loc_of, const int* __restrict__ rho_of, const int* __restrict__ tr_of,
                         int m, int S, int L, int d, float tau_host, const float* __restrict__ tau_dev, int row0,
-                        float* __restrict__ G, float* __restrict__ elbo) {
+                        float* __restrict__ G, float* __restrict__ elbo, const int* __restrict__ nnz_total, int thresh) {
+  if (*nnz_total <= thresh) return;   // short component lists: guide_grad_sparse_kernel does this call
   constexpr int MW = kSplitCG * MPC, KT = kGradKT, NB = kSplitNB;
   const float tau = tau_dev ? *tau_dev : tau_host;
   extern __shared__ __align__(16) float sm[];
@@ -514,7 +658,8 @@ guide_grad_big_kernel(const float* __restrict__ psi, const float* __restrict__ e
                       const float* __restrict__ DZ, const float* __restrict__ LOGP, const float* __restrict__ LOGQ,
                       const int* __restrict__ loc_of, const int* __restrict__ rho_of, const int* __restrict__ tr_of,
                       int m, int S, int L, int d, float tau_host, const float* __restrict__ tau_dev, int row0,
-                      float* __restrict__ G, float* __restrict__ elbo) {
+                      float* __restrict__ G, float* __restrict__ elbo, const int* __restrict__ nnz_total, int thresh) {
+  if (*nnz_total <= thresh) return;   // short component lists: guide_grad_sparse_kernel does this call
   const float tau = tau_dev ? *tau_dev : tau_host;
   extern __shared__ float sm[];
   const int mw = (m + 3) & ~3;                      // row pitch of the weights: float4 reads
@@ -689,6 +834,9 @@ size_t smi_elbo_carve(SmiArena& ar, ElboWs& w, const SmiModelDesc& md, int m, in
   w.DZ = ar.take<float>((size_t)nrows * S * L);
   w.QP = ar.take<float>(normal ? (size_t)nrows * w.nkq * S * m : 0);
   w.W = ar.take<float>(normal ? (size_t)nrows * S * m : 0);
+  w.NNZ = ar.take<int>(normal ? (size_t)nrows * S : 0);
+  w.NZI = ar.take<unsigned char>(normal ? (size_t)nrows * S * m : 0);
+  w.nnz_total = ar.take<int>(1);
   w.LOGQ = ar.take<float>((size_t)nrows * S);
   w.LOGP = ar.take<float>((size_t)nrows * S);
   ClsTcWs& c = w.cls;
@@ -714,7 +862,7 @@ int smi_guide_prep(const SmiModelDesc& md, const float* psi, int m, ElboWs& w, c
   dim3 grid(nlb_of(md.latent_dim), m);
   SMI_PROF_BEGIN(st);
   guide_prep_kernel<<<grid, 256, 0, st>>>(md, psi, m, w.loc_of, w.rho_of, w.tr_of, w.MU, w.SIG, w.ISIG,
-                                          w.logdet_part);
+                                          w.logdet_part, w.nnz_total);
   SMI_LAUNCH_OK_N("guide_prep_kernel", st);
   return SMI_OK;
 }
@@ -724,13 +872,22 @@ int smi_guide_sample(const SmiModelDesc& md, const float* eps, int m, int S, int
   const size_t smem = ((size_t)kGuideKT * (128 + 64) + 128 * 32) * sizeof(float);
   static bool set = false;
   if (!set) {
-    SMI_CUDA_OK(cudaFuncSetAttribute(guide_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    SMI_CUDA_OK(cudaFuncSetAttribute(guide_sample_kernel<4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    SMI_CUDA_OK(cudaFuncSetAttribute(guide_sample_kernel<8, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     set = true;
   }
   dim3 grid(w.nkq, nrows);
   SMI_PROF_BEGIN(st);
-  guide_sample_kernel<<<grid, 256, smem, st>>>(eps, w.MU, w.SIG, w.ISIG, m, S, md.latent_dim, row0, w.Z, w.QP,
-                                               w.nkq, w.ksub);
+  // measured on B200 (scripts/time_mixture.py, m = 160 / 80 / 40): 8 x 8 blocks 428 / 272 / 186 us against 264 / 154 / 87 us
+  // for 4 x 4 -- two CTAs of 208 active threads per SM hide the staging and reduction phases worse than three CTAs of
+  // 200-250; the variant stays for comparison runs (SMI_SAMPLE_8X8=1)
+  static const bool big_blocks = getenv("SMI_SAMPLE_8X8") != nullptr;
+  if (m > 32 && big_blocks)
+    guide_sample_kernel<8, 8><<<grid, 256, smem, st>>>(eps, w.MU, w.SIG, w.ISIG, m, S, md.latent_dim, row0, w.Z, w.QP,
+                                                       w.nkq, w.ksub);
+  else
+    guide_sample_kernel<4, 4><<<grid, 256, smem, st>>>(eps, w.MU, w.SIG, w.ISIG, m, S, md.latent_dim, row0, w.Z, w.QP,
+                                                       w.nkq, w.ksub);
   SMI_LAUNCH_OK_N("guide_sample_kernel", st);
   return SMI_OK;
 }
@@ -739,7 +896,7 @@ int smi_guide_weights(const SmiModelDesc& md, int m, int S, int nrows, ElboWs& w
   const int warps = nrows * S;
   SMI_PROF_BEGIN(st);
   guide_weights_kernel<<<(warps + 7) / 8, 256, 0, st>>>(md, w.QP, w.logdet_part, nlb_of(md.latent_dim), w.Z, m, S,
-                                                        nrows, w.nkq, w.W, w.LOGQ);
+                                                        nrows, w.nkq, w.W, w.LOGQ, w.NNZ, w.NZI, w.nnz_total);
   SMI_LAUNCH_OK_N("guide_weights_kernel", st);
   return SMI_OK;
 }
@@ -760,6 +917,26 @@ static int launch_grad(const SmiModelDesc& md, const float* psi, const float* ep
   return SMI_OK;
 }
 
+// The sparse kernel takes the call when the lists hold at most kSparseAvg components per draw on average
+// (SMI_GRAD_SPARSE=0 disables it: the threshold becomes -1 and the dense kernels always run).
+constexpr int kSparseAvg = 8;
+static int sparse_thresh(int nrows, int S) {
+  const char* e = getenv("SMI_GRAD_SPARSE");
+  if (e && e[0] == '0') return -1;
+  return kSparseAvg * nrows * S;
+}
+
+static int launch_grad_sparse(const SmiModelDesc& md, const float* psi, const float* eps, int m, int S, float tau,
+                              const float* tau_dev, int row0, int nrows, ElboWs& w, float* G, float* elbo, cudaStream_t st) {
+  dim3 grid((md.latent_dim + kGradKT - 1) / kGradKT, nrows);
+  SMI_PROF_BEGIN(st);
+  guide_grad_sparse_kernel<<<grid, 256, 0, st>>>(psi, eps, w.MU, w.SIG, w.ISIG, w.W, w.DZ, w.LOGP, w.LOGQ, w.NNZ, w.NZI,
+                                                 w.nnz_total, sparse_thresh(nrows, S), w.loc_of, w.rho_of, w.tr_of, m, S,
+                                                 md.latent_dim, md.particle_dim, tau, tau_dev, row0, G, elbo);
+  SMI_LAUNCH_OK_N("guide_grad_sparse_kernel", st);
+  return SMI_OK;
+}
+
 template <int MPC>
 static int launch_grad_split(const SmiModelDesc& md, const float* psi, const float* eps, int m, int S, float tau,
                              const float* tau_dev, int row0, int nrows, ElboWs& w, float* G, float* elbo,
@@ -772,7 +949,8 @@ static int launch_grad_split(const SmiModelDesc& md, const float* psi, const flo
   SMI_PROF_BEGIN(st);
   guide_grad_split_kernel<MPC><<<grid, 256, smem, st>>>(psi, eps, w.MU, w.SIG, w.ISIG, w.W, w.DZ, w.LOGP, w.LOGQ,
                                                         w.loc_of, w.rho_of, w.tr_of, m, S, md.latent_dim,
-                                                        md.particle_dim, tau, tau_dev, row0, G, elbo);
+                                                        md.particle_dim, tau, tau_dev, row0, G, elbo, w.nnz_total,
+                                                        sparse_thresh(nrows, S));
   SMI_LAUNCH_OK_N("guide_grad_split_kernel", st);
   return SMI_OK;
 }
@@ -788,6 +966,12 @@ int smi_guide_grad(const SmiModelDesc& md, const float* psi, const float* eps, i
   if (m <= 32) return launch_grad<32>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
   if (m <= 40) return launch_grad<40>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
   if (m <= 48) return launch_grad<48>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+  // m > 48: sparse kernel first (runs or returns at once, decided on the device), then the dense kernel for the
+  // opposite case
+  {
+    int rc = launch_grad_sparse(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+    if (rc) return rc;
+  }
   if (m <= 4 * 48 && !getenv("SMI_GRAD_STREAM")) {
     const int mpc = (m + 3) / 4;
     int rc;
@@ -806,7 +990,8 @@ int smi_guide_grad(const SmiModelDesc& md, const float* psi, const float* eps, i
   dim3 grid((md.latent_dim + kBigKT - 1) / kBigKT, nrows);
   SMI_PROF_BEGIN(st);
   kern<<<grid, 256, smem, st>>>(psi, eps, w.MU, w.SIG, w.ISIG, w.W, w.DZ, w.LOGP, w.LOGQ, w.loc_of, w.rho_of, w.tr_of, m, S,
-                                md.latent_dim, md.particle_dim, tau, tau_dev, row0, G, elbo);
+                                md.latent_dim, md.particle_dim, tau, tau_dev, row0, G, elbo, w.nnz_total,
+                                sparse_thresh(nrows, S));
   SMI_LAUNCH_OK_N("guide_grad_big_kernel", st);
   return SMI_OK;
 }

@@ -114,10 +114,28 @@ def test_gaussian_target_streaming_gradient_kernel(cuda, monkeypatch):
     _gaussian_target_case(cuda, "normal", 60, 100, 30)
 
 
-def _gaussian_target_case(cuda, guide, m, S, dim):
+@pytest.mark.parametrize("m,S,dim,radius", [(160, 100, 40, 0.02), (100, 13, 30, 0.05), (200, 20, 24, 0.02), (70, 33, 50, 0.3)])
+def test_gaussian_target_overlapping_particles_dense_weights(cuda, m, S, dim, radius):
+    """m > 48 with nearly coincident particles: every component keeps a non-zero responsibility, so the device
+    hands the gradient to the dense kernels (split / streaming) instead of the sparse one; radius 0.3 is mixed."""
+    _gaussian_target_case(cuda, "normal", m, S, dim, radius=radius)
+
+
+def test_sparse_and_dense_gradient_kernels_agree(cuda, monkeypatch):
+    """The same far-apart mixture through the sparse kernel (default) and with SMI_GRAD_SPARSE=0 (dense kernels)."""
+    from smi_experiments_b200 import models
+    pm, om = models.GaussianTarget(60), omodels.gaussian(60)
+    md, psi, eps, rng, L, d = _setup(pm, om, "normal", 96, 40, seed=5, radius=2.0)
+    G1, E1 = _run(cuda, md, psi, eps, None, None, None, 40, 0, 1.0, 1.0)
+    monkeypatch.setenv("SMI_GRAD_SPARSE", "0")
+    G0, E0 = _run(cuda, md, psi, eps, None, None, None, 40, 0, 1.0, 1.0)
+    assert _rel(G1, G0) <= 1e-6 and np.array_equal(E1, E0)
+
+
+def _gaussian_target_case(cuda, guide, m, S, dim, radius=2.0):
     from smi_experiments_b200 import models
     pm, om = models.GaussianTarget(dim), omodels.gaussian(dim)
-    md, psi, eps, rng, L, d = _setup(pm, om, guide, m, S, seed=dim + m, radius=2.0)
+    md, psi, eps, rng, L, d = _setup(pm, om, guide, m, S, seed=dim + m, radius=radius)
     tau = 1.0 if guide == "normal" else 1.0 / m
     G, E = _run(cuda, md, psi, eps, None, None, None, S, 0, 1.0, tau)
     G64, E64 = oelbo.elbo_grads(om, psi.astype(np.float64), eps, None, None, None, None, tau, guide, torch.float64)
