@@ -380,7 +380,7 @@ def force_rows_check(torch, X, G, F_rows, row0, h, nsample=16, alpha=1.0, c_att=
                 force_rows_rel_err_vs_float64=err, ok=bool(err <= 1e-5))
 
 
-def bench_other_configs(torch, smi, dev, flush):
+def bench_other_configs(torch, smi, dev, flush, pk=None):
     """The other BASELINE.json configs (parity-test cases) timed the same
     way as `value` (graph replay, L2 flushed between steps, CUDA events): context, not bench lines."""
     out = {}
@@ -419,8 +419,20 @@ def bench_other_configs(torch, smi, dev, flush):
     xb = torch.from_numpy(rng.integers(0, 256, (128, 784)).astype(np.float32) / 255.0).to(dev)
     yb = torch.from_numpy(rng.integers(0, 10, 128).astype(np.int32)).to(dev)
     st = eng.init(smi.PRNGKey(4), xb, yb, n=60000, batch_size=128)
-    timed("C4 MNIST-shape MLP 784-100-100-10, SMI 10 particles, 55 draws, batch 128", eng, st, (xb, yb),
-          dict(n=60000, batch_size=128), 10)
+    c4 = "C4 MNIST-shape MLP 784-100-100-10, SMI 10 particles, 55 draws, batch 128"
+    timed(c4, eng, st, (xb, yb), dict(n=60000, batch_size=128), 10)
+    if pk is not None:
+        # HBM roofline of the C4 step: algorithmic bytes = 4 (m S L + 2 m d) for the ELBO gradients with
+        # eps as an input + 28 m d for the optimizer; the design's own traffic (eps written + read twice, Z / DZ each
+        # way, W1^T operand planes written + read) is about ten times that
+        m_, S_, L_, d_ = 10, 55, eng.layout.latent_dim, eng.layout.particle_dim
+        ms = out[c4]["ms_per_step"]
+        alg = 4.0 * (m_ * S_ * L_ + 2 * m_ * d_) + 28.0 * m_ * d_
+        design = 7.0 * 4.0 * m_ * S_ * L_ + 2.0 * 2.0 * 4.0 * m_ * S_ * 100 * 800 + 2.0 * 4.0 * m_ * S_ * 128 * 100 * 3 + 40.0 * m_ * d_
+        out[c4]["roofline"] = dict(bound="hbm", achieved=alg / ms / 1e6, peak=pk["hbm"], unit="GB/s",
+                                   frac=(alg / ms / 1e6) / pk["hbm"], algorithmic_bytes=alg,
+                                   design_traffic_bytes=design, frac_of_design_traffic=(design / ms / 1e6) / pk["hbm"],
+                                   peak_source=pk["src"], traffic=None)
     return out
 
 
@@ -576,7 +588,7 @@ def run_gpu(args):
         if rank == 0:
             line["stein_force"] = sw
     if rank == 0 and world == 1 and not args.no_configs:
-        line["other_configs"] = bench_other_configs(torch, smi, dev, flush)
+        line["other_configs"] = bench_other_configs(torch, smi, dev, flush, pk)
     # ---- CPU baseline (rank 0, N = 1 only): bounded sample of the same workload ----
     if rank == 0 and world == 1 and not args.no_cpu:
         step, cores = cpu_step_runner(os.cpu_count())

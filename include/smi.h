@@ -121,6 +121,11 @@ int smi_stage_h2d(void* handle, const void* src, size_t nbytes, void* dst, void*
  * off_{i+1} = off_i + nbytes[i] rounded up to 256 (sum <= the handle's capacity).             */
 int smi_stage_h2dv(void* handle, const void* const* srcs, const size_t* nbytes, int count, void* dst, void* stream);
 int smi_stage_destroy(void* handle);
+/* Widening of staged raw arguments on the device: the reference hands its classifier uint8 pixels and int64 labels
+ * (datasets/ood_detection/load_ood_detect.py:39-46, experiments/img_classifier.py:66-73), which jnp converts inside
+ * the jitted update; here the raw bytes travel H2D and these kernels widen them (no torch op on the step's path). */
+int smi_convert_u8_f32(const unsigned char* in, size_t n, float* out, void* stream);
+int smi_convert_i64_i32(const long long* in, size_t n, int* out, void* stream);
 
 /* ---- Stein force: replaces RBFKernel.compute + _apply_kernel + _kernel_grad + force sum
  *      + ||F|| (NumPyro steinvi.py::_svgd_loss_and_grads).

@@ -62,6 +62,8 @@ PROTOTYPES = {
     "smi_stage_h2d": (_I, [_P, _P, _Z, _P, _P]),
     "smi_stage_h2dv": (_I, [_P, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), _I, _P, _P]),
     "smi_stage_destroy": (_I, [_P]),
+    "smi_convert_u8_f32": (_I, [_P, _Z, _P, _P]),
+    "smi_convert_i64_i32": (_I, [_P, _Z, _P, _P]),
     "smi_stein_force_workspace_bytes": (_Z, [_I, _I, _I]),
     "smi_stein_force_f32": (_I, [_P, _P, _I, _I, _F, _F, _I, _F, _I, _P, _P, _P, _P, _Z, _P]),
     "smi_sqdist_workspace_bytes": (_Z, [_I, _I, _I]),

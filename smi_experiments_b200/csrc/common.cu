@@ -202,3 +202,42 @@ SMI_API int smi_stage_destroy(void* handle) {
   delete s;
   return SMI_OK;
 }
+
+
+// ---- staged-argument conversion: the reference feeds its classifier un-normalised uint8 pixels and int64 labels
+// (datasets/ood_detection/load_ood_detect.py:39-46; experiments/img_classifier.py:66-73): the raw bytes are staged
+// H2D as they are and widened on the device by these kernels (one launch each, no torch op on the path) ----
+__global__ void __launch_bounds__(256) cvt_u8_f32_kernel(const unsigned char* __restrict__ in, size_t n, float* __restrict__ out) {
+  const size_t n4 = n >> 2;
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < n4; t += (size_t)gridDim.x * blockDim.x) {
+    const uchar4 v = reinterpret_cast<const uchar4*>(in)[t];
+    reinterpret_cast<float4*>(out)[t] = make_float4((float)v.x, (float)v.y, (float)v.z, (float)v.w);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) out[(n4 << 2) + threadIdx.x] = (float)in[(n4 << 2) + threadIdx.x];
+}
+__global__ void __launch_bounds__(256) cvt_i64_i32_kernel(const long long* __restrict__ in, size_t n, int* __restrict__ out) {
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (size_t)gridDim.x * blockDim.x) out[t] = (int)in[t];
+}
+
+SMI_API int smi_convert_u8_f32(const unsigned char* in, size_t n, float* out, void* stream) {
+  if (!in || !out) SMI_FAIL(SMI_EINVAL, "smi_convert_u8_f32: null pointer");
+  if ((((uintptr_t)in) & 3) || (((uintptr_t)out) & 15)) SMI_FAIL(SMI_EINVAL, "smi_convert_u8_f32: unaligned buffer");
+  if (!n) return SMI_OK;
+  const size_t blocks = (n / 4 + 255) / 256;
+  const int grid = (int)(blocks < (size_t)smi_num_sms() * 8 ? (blocks ? blocks : 1) : (size_t)smi_num_sms() * 8);
+  SMI_PROF_BEGIN((cudaStream_t)stream);
+  cvt_u8_f32_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(in, n, out);
+  SMI_LAUNCH_OK_N("cvt_u8_f32_kernel", (cudaStream_t)stream);
+  return SMI_OK;
+}
+
+SMI_API int smi_convert_i64_i32(const long long* in, size_t n, int* out, void* stream) {
+  if (!in || !out) SMI_FAIL(SMI_EINVAL, "smi_convert_i64_i32: null pointer");
+  if (!n) return SMI_OK;
+  const size_t blocks = (n + 255) / 256;
+  const int grid = (int)(blocks < (size_t)smi_num_sms() * 8 ? blocks : (size_t)smi_num_sms() * 8);
+  SMI_PROF_BEGIN((cudaStream_t)stream);
+  cvt_i64_i32_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(in, n, out);
+  SMI_LAUNCH_OK_N("cvt_i64_i32_kernel", (cudaStream_t)stream);
+  return SMI_OK;
+}

@@ -160,8 +160,14 @@ class SteinVI:
                 slot.srcs[j] = a.ctypes.data
             _lib.call("smi_stage_h2dv", slot.handle, slot.srcs, slot.sizes, slot.n, slot.buf_ptr, ops._stream())
             for j, i in enumerate(host):
-                if slot.raw[j] is not slot.dev[j]:
-                    slot.dev[j].copy_(slot.raw[j])  # dtype conversion (e.g. uint8 pixels -> fp32), on the device
+                if slot.raw[j] is not slot.dev[j]:      # dtype conversion on the device (uint8 pixels -> fp32, int64 labels -> int32)
+                    r, dv = slot.raw[j], slot.dev[j]
+                    if r.dtype == torch.uint8 and dv.dtype == torch.float32:
+                        _lib.call("smi_convert_u8_f32", ops._ptr(r), r.numel(), ops._ptr(dv), ops._stream())
+                    elif r.dtype == torch.int64 and dv.dtype == torch.int32:
+                        _lib.call("smi_convert_i64_i32", ops._ptr(r), r.numel(), ops._ptr(dv), ops._stream())
+                    else:
+                        dv.copy_(r)
                 out[i] = slot.dev[j]
             self.h2d_bytes += slot.nbytes
         return out
