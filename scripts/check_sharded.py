@@ -40,13 +40,14 @@ for m, d in [(4096 * world if world <= 2 else 2048 * world, 1000), (8192, 2500)]
     F1, l1, h1 = smi.ops.stein_force(Xf, Gf, alpha=2.0, path=smi.ops.PATH_TC)
     D1 = smi.ops.sqdist(Xf, path=smi.ops.PATH_TC)
     half = world // 2
+    bulk = dist.new_group() if world > 3 else None
     pull = PeerPull(n, d, len([o for o in range(1, half + 1) if not (world % 2 == 0 and o == half)]), dev)
     for rep in range(3):      # rep 0, 1: copy-engine pulls over symmetric memory; rep 2: NCCL exchange (needs its own backend buffers)
         if rep == 2:
             be = LibsmiRows(m, d, r0, n, dev)
         X, G = torch.zeros_like(Xf), torch.zeros_like(Gf)
         X[r0:r0 + n], G[r0:r0 + n] = Xf[r0:r0 + n], Gf[r0:r0 + n]
-        F, loss, h = stein_force_sym(be, X, G, alpha=2.0, pull=pull if rep < 2 else None)
+        F, loss, h = stein_force_sym(be, X, G, alpha=2.0, pull=pull if rep < 2 else None, bulk_group=bulk if rep == 1 else None)
         torch.cuda.synchronize()
         D2 = be.ws[:0]  # (the workspace layout is private; the distances are checked through h and the force)
         e = (rel(F, F1[r0:r0 + n]), abs(float(loss) - float(l1)) / float(l1), float(h) == float(h1),

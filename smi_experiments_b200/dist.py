@@ -221,13 +221,16 @@ def _exchange(pairs, group):
 
 
 def stein_force_sym(backend, X, G, group=None, alpha=1.0, c_att=1.0, median_mode=_lib.MEDIAN_JAX_FP32_INDEX,
-                    h_fixed=0.0, side=None, trace=None, pull=None):
+                    h_fixed=0.0, side=None, trace=None, pull=None, bulk_group=None):
     """Row-sharded Stein force with the exchange INSIDE: on entry only the local rows of X and G are valid.
     Block-symmetric ring (include/smi.h, smi_stein_sym_*): the particle blocks to the right of this rank arrive
     first (grouped ncclSend / ncclRecv on a side stream) and feed the Gram, which computes the own diagonal block and
     world / 2 blocks to its right; the blocks to the left come back as packed transposes from the ranks that
     computed them; the remaining particle blocks and the all-gather of the scores travel under the Gram and are
-    only awaited before the force.  Returns (F_rows, loss, h); X and G are complete afterwards."""
+    only awaited before the force.  Returns (F_rows, loss, h); X and G are complete afterwards.
+    bulk_group: a second process group over the same ranks (its own NCCL communicator) for the grouped ncclSend /
+    ncclRecv of the right blocks, so that it starts at once instead of queueing behind the small collectives of
+    `group` -- the collectives of ONE communicator execute in issue order, whatever stream they are on."""
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     n, r0 = backend.rows, backend.row0
     half = world // 2
@@ -244,32 +247,46 @@ def stein_force_sym(backend, X, G, group=None, alpha=1.0, c_att=1.0, median_mode
     blk = lambda t, j: t[(j % world) * n:(j % world) * n + n]
     gr = lambda j: dist.get_global_rank(group, j % world) if group is not None else j % world
     joins = lambda evs: [torch.cuda.current_stream().wait_event(e) for e in evs]
-    if pull is not None:      # publish the local rows for the peers' copy-engine pulls
+    nn = 0
+    if pull is not None:
+        # ---- the right blocks the Gram waits for: with a communicator of their own all of them go by grouped
+        # ncclSend / ncclRecv at once (every rank sends its own rows: nothing to wait for, and the SMs are idle);
+        # otherwise half of them, after the small all-gather below, the other half by copy engine ----
+        nn = len(right) if bulk_group is not None else len(right) // 2
+        if world <= 3:
+            nn = 0      # a single right block: one ncclSend / ncclRecv pair runs at ~250 GB/s, the copy engine at 645
+        bg = bulk_group if bulk_group is not None else group
+        bgr = lambda j: dist.get_global_rank(bg, j % world) if bg is not None else j % world
+
+        def nccl_right():
+            side.fork()
+            with side.ctx():
+                _exchange([(blk(X, rank), bgr(rank - o), blk(X, rank + o), bgr(rank + o)) for o in right[:nn]], bg)
+                e = side.event()
+                mark("side: right blocks by NCCL arrived", side.stream if side.cuda else None)
+            return e
+        e_n = nccl_right() if (bulk_group is not None and nn) else None
+        # publish the local rows for the peers' copy-engine pulls
         pull.xs.copy_(blk(X, rank))
         pull.gs.copy_(blk(G, rank))
     # ---- column mean from slab partials (every rank adds the 64 slabs in the same order).  Issued BEFORE any bulk
-    # NCCL exchange: collectives of one communicator execute in issue order, whatever stream they are on.  Its
-    # completion also tells this rank that every peer has published its rows ----
+    # NCCL exchange on the same communicator.  Its completion also tells this rank that every peer has published
+    # its rows ----
     backend.colsum(X)
     _all_gather_in_place(backend.part, backend.part[backend.slab0:backend.slab1], group)
     if pull is not None:
-        # ---- bulk movement.  Copies on different streams were measured to share ONE copy engine (no concurrency,
-        # 0.22 ms per 82 MB block when all 8 ranks pull), so the pulls go on one stream in priority order; the right
-        # blocks, which the Gram waits for while the SMs are idle anyway, are halved between a grouped ncclSend/ncclRecv
-        # and the copy engine so that both paths into the NVLink port are busy ----
-        nn = len(right) // 2      # a single right block (worlds of 2, 3) goes by copy engine: one ncclSend/Recv pair runs at ~250 GB/s
+        # ---- bulk movement under the GEMMs by copy engine.  Copies on different streams were measured to share ONE
+        # copy engine (no concurrency, 0.22 ms per 82 MB block when all 8 ranks pull), so the pulls go on one stream
+        # in priority order ----
         pull.fork()
-        side.fork()
-        with side.ctx():
-            _exchange([(blk(X, rank), gr(rank - o), blk(X, rank + o), gr(rank + o)) for o in right[:nn]], group)
-            e_n = side.event()
-            mark("side: right blocks by NCCL arrived", side.stream if side.cuda else None)
+        if e_n is None and nn:
+            e_n = nccl_right()
         ev_a = pull.pull([(blk(X, rank + o), pull.peer_x[(rank + o) % world]) for o in right[nn:]])
         mark("side: right blocks by copy engine arrived", pull.streams[0])
         ev_b = pull.pull([(blk(X, rank + o), pull.peer_x[(rank + o) % world]) for o in range(half + 1, world)] +
                          [(blk(G, rank + o), pull.peer_g[(rank + o) % world]) for o in range(1, world)])
         mark("side: left blocks + G pulled", pull.streams[0])
-        wait_a, wait_b = (lambda: (side.join(e_n), joins(ev_a))), (lambda: joins(ev_b))
+        wait_a, wait_b = (lambda: (side.join(e_n), joins(ev_a))), (lambda: joins(ev_b))     # join(None) is a no-op
     else:
         # ---- bulk communication over NCCL / gloo on the side stream: right blocks, the rest, G ----
         side.fork()
@@ -444,7 +461,9 @@ def bench_sharded_force(m, d, reps, flush):
     side = torch.cuda.Stream(device=dev)
     sym = be.sym_supported() and os.environ.get("SMI_SHARD_SYM", "1") != "0"
     side2 = _SideStream(dev)
-    pull = None
+    pull = bulk = None
+    if sym and world > 3 and os.environ.get("SMI_SHARD_BULK_COMM", "1") != "0":
+        bulk = dist.new_group()      # its own NCCL communicator for the right-block exchange
     if sym and os.environ.get("SMI_SHARD_PULL", "1") != "0":
         half = world // 2
         nsend = len([o for o in range(1, half + 1) if not (world % 2 == 0 and o == half)])
@@ -461,7 +480,7 @@ def bench_sharded_force(m, d, reps, flush):
 
     def unit():
         if sym:       # block-symmetric ring: the exchange is part of the choreography
-            return stein_force_sym(be, X, G, side=side2, pull=pull)
+            return stein_force_sym(be, X, G, side=side2, pull=pull, bulk_group=bulk)
         cur = torch.cuda.current_stream()
         dist.all_gather_into_tensor(X, X[r0:r0 + n])
         side.wait_stream(cur)
@@ -500,7 +519,7 @@ def bench_sharded_force(m, d, reps, flush):
         tr = []
         scrub()
         dist.barrier()
-        stein_force_sym(be, X, G, side=side2, trace=tr, pull=pull)
+        stein_force_sym(be, X, G, side=side2, trace=tr, pull=pull, bulk_group=bulk)
         torch.cuda.synchronize()
         timeline = {nm: round(tr[0][1].elapsed_time(e), 3) for nm, e in tr[1:]}
     ms = torch.tensor([float(np.mean([a.elapsed_time(b) for a, b in evs]))], dtype=torch.float64, device=dev)
