@@ -51,7 +51,11 @@ def bench_config(world):
                          "minibatch 100, 100 ELBO draws, Adam",
                 particles_per_gpu=C2["m"], particles_total=C2["m"] * world, elbo_draws=C2["S"], minibatch=C2["B"],
                 unit_note="one unit = one SMI step on 20 particles; under weak scaling (--gpus N) a step updates "
-                          "20 N particles of one mixture and counts N units")
+                          "20 N particles of one mixture and counts N units",
+                # how the GPU arm is timed (the same dict is printed by --impl reference so that both arms carry an
+                # identical `config`; the CPU arm times whole steps with perf_counter)
+                l2="GPU arm: flushed between steps (256 MiB memset, untimed)",
+                timing="GPU arm: cuda events per step, max over ranks; graph replay at N = 1, eager launches at N > 1")
 
 
 def peaks():
@@ -555,8 +559,6 @@ def run_gpu(args):
         step_flop = 3.0 * 2.0 * (B * I * H + B * H * H + B * H) * m_local * S
         roof["step_frac"] = (step_flop / (dev_ms / steps) / 1e9) / (burst / 3.0)
         cfg = bench_config(world)
-        cfg.update(l2="flushed between steps (256 MiB memset, untimed)", timing="cuda events per step, max over ranks",
-                   cuda_graph=bool(eng.use_cuda_graph))
         line = dict(metric=METRIC, value=value, unit=UNIT,
                     n_gpus=world, steps=steps, warmup=max(args.warmup, 3), ms_per_step=dev_ms / steps,
                     higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
