@@ -16,7 +16,7 @@ OUT = os.path.join(PKG, "libsmi.so")
 OBJ = os.path.join(HERE, "build")
 
 SOURCES = ["common.cu", "stein_small.cu", "stein_mid.cu", "select.cu", "stein_tc.cu", "stein_api.cu", "optim.cu",
-           "elbo_guide.cu", "elbo_mlp.cu", "elbo_bnn_mma.cu", "elbo_bnn_tc.cu", "elbo_mlp_cls.cu", "elbo_cls_tc.cu", "elbo_api.cu", "prng.cu", "predictive.cu"]
+           "elbo_guide.cu", "elbo_mlp.cu", "elbo_bnn_mma.cu", "elbo_bnn_tc.cu", "elbo_mlp_cls.cu", "elbo_cls_tc.cu", "elbo_mix_tc.cu", "elbo_api.cu", "prng.cu", "predictive.cu"]
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

@@ -27,8 +27,28 @@ struct ClsTcWs {
   double* w1sq;     // [ndraws x nit]     partial sums of W1^2 (prior)
 };
 
+// Buffers of the tensor-core mixture filter (elbo_mix_tc.cu): the quadratic forms a_sj of every (draw, component)
+// as ONE split-K tcgen05 GEMM, used to certify which responsibilities vanish; the survivors are re-evaluated exactly.
+constexpr int kMixCandMax = 32;   // candidates per draw the exact path handles
+struct MixTcWs {
+  bool on;
+  int Lp, ld, ksplit;   // pad32(L), 3 Lp, K segments
+  float *Ah, *Al;       // [nrows S x 3 Lp]   [u^2, u mu'_i, u]
+  float *Bh, *Bl;       // [m x 3 Lp]         [q_j, 2 q_j, -2 mu'_j q_j]
+  float* cent;          // [L] centroid of the component means
+  float* part;          // [ksplit x nrows S x 256] raw partial tiles
+  double* C;            // [nrows x m] sum_k q_j (mu_i - mu_j)^2
+  float* bnd;           // [nrows x m x 3]  bmax^2, D_ij, D_jj (error bound of the GEMM form)
+  float* epart;         // [nrows S x nkc] partial sums of eps^2
+  int* cand_n;          // [nrows S]
+  unsigned char* cand_i;  // [nrows S x kMixCandMax]
+  double* aex;          // [nrows S x kMixCandMax] exact quadratic forms of the candidates
+  int* gate;            // [2] total candidates, max per draw  (zeroed by guide_prep)
+};
+
 struct ElboWs {
   ClsTcWs cls;
+  MixTcWs mix;
   int* loc_of;     // [L] latent index -> offset of loc in psi
   int* rho_of;     // [L]
   int* tr_of;      // [L] transform code
@@ -52,6 +72,12 @@ struct ElboWs {
 size_t smi_elbo_carve(SmiArena& ar, ElboWs& w, const SmiModelDesc& md, int m, int S, int nrows, int B);
 bool smi_cls_tc_eligible(const SmiModelDesc& md, int B);
 
+bool smi_mix_tc_eligible(const SmiModelDesc& md, int m, int S, int nrows);
+size_t smi_mix_tc_carve(SmiArena& ar, MixTcWs& x, const SmiModelDesc& md, int m, int S, int nrows);
+// Replaces guide_sample + guide_weights when w.mix.on: returns after launching the filter GEMM, the exact evaluation of
+// the surviving components and the weights; `fallback` gates (device-side) the CUDA-core kernels the caller launches next.
+int smi_guide_mix_tc(const SmiModelDesc& md, const float* eps, int m, int S, int row0, int nrows, ElboWs& w,
+                     cudaStream_t st);
 int smi_guide_prep(const SmiModelDesc& md, const float* psi, int m, ElboWs& w, cudaStream_t st);
 int smi_guide_sample(const SmiModelDesc& md, const float* eps, int m, int S, int row0, int nrows, ElboWs& w,
                      cudaStream_t st);

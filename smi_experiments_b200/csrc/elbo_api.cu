@@ -47,6 +47,9 @@ static int elbo_grad_impl(const SmiModelDesc* md, const float* psi, const float*
   if (!eps) SMI_FAIL(SMI_EINVAL, "AutoNormal guides need eps");
   if (m > kGuideMaxM) SMI_FAIL(SMI_ELIMIT, "AutoNormal mixture path supports m <= %d particles (m=%d)", kGuideMaxM, m);
   if ((rc = smi_guide_prep(*md, psi, m, w, st))) return rc;
+  // many components over many latent dimensions: tensor-core filter + exact survivors (elbo_mix_tc.cu); the two
+  // CUDA-core kernels below then return at once unless the device found the mixture dense
+  if (w.mix.on && (rc = smi_guide_mix_tc(*md, eps, m, S, row0, nrows, w, st))) return rc;
   if ((rc = smi_guide_sample(*md, eps, m, S, row0, nrows, w, st))) return rc;
   if ((rc = smi_guide_weights(*md, m, S, nrows, w, st))) return rc;
   if ((rc = smi_model_logp_grad(*md, w.Z, idx, x, y, nrows * S, B, lik_scale, w.DZ, w.LOGP, w, st))) return rc;

@@ -37,9 +37,12 @@ __global__ void __launch_bounds__(256)
 guide_prep_kernel(const SmiModelDesc md, const float* __restrict__ psi, int m, int* __restrict__ loc_of,
                   int* __restrict__ rho_of, int* __restrict__ tr_of, float* __restrict__ MU,
                   float* __restrict__ SIG, float* __restrict__ ISIG, double* __restrict__ logdet_part,
-                  int* __restrict__ nnz_total) {
+                  int* __restrict__ nnz_total, int* __restrict__ mix_gate) {
   __shared__ double red[32];
-  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) *nnz_total = 0;
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
+    *nnz_total = 0;
+    if (mix_gate) mix_gate[0] = mix_gate[1] = 0;
+  }
   const int L = md.latent_dim, d = md.particle_dim;
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = blockIdx.y;
@@ -78,11 +81,18 @@ guide_prep_kernel(const SmiModelDesc md, const float* __restrict__ psi, int m, i
 // warps issuing FMAs the shared-memory pipe (128 B / clock) is 1.5x oversubscribed -- harmless while the kernel is
 // latency-bound at m = 20, but at m = 160 (five component chunks per z tile, 255 us of a 0.9 ms step) it is the
 // limit; 8 x 8 needs 6 LDS.128 per 128 FMAs (0.75x).  Measured slower all the same (see smi_guide_sample): opt-in.
+// mix_gate (elbo_mix_tc.cu): {total, max per draw} of the components the tensor-core filter could not rule out; when
+// the lists are short the exact path there has produced W / LOGQ and the CUDA-core kernels of this file return at once.
+__device__ __forceinline__ bool mix_handled(const int* gate, int Rtot) {
+  return gate && gate[0] <= 4 * Rtot && gate[1] <= kMixCandMax;
+}
+
 template <int DA, int DB>
 __global__ void __launch_bounds__(256, DA * DB > 16 ? 2 : 3)
 guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU, const float* __restrict__ SIG,
                     const float* __restrict__ ISIG, int m, int S, int L, int row0, float* __restrict__ Z,
-                    float* __restrict__ QP, int nkq, int ksub) {
+                    float* __restrict__ QP, int nkq, int ksub, const int* __restrict__ mix_gate) {
+  if (mix_handled(mix_gate, (int)gridDim.y * S)) return;
   extern __shared__ float sm[];
   float* zt = sm;                       // [64][128]
   float* mt = zt + kGuideKT * 128;      // [64][32]
@@ -254,7 +264,8 @@ __global__ void __launch_bounds__(256)
 guide_weights_kernel(const SmiModelDesc md, const float* __restrict__ QP, const double* __restrict__ logdet_part,
                      int nlb, const float* __restrict__ Z, int m, int S, int nrows, int nkt,
                      float* __restrict__ W, float* __restrict__ LOGQ, int* __restrict__ NNZ,
-                     unsigned char* __restrict__ NZI, int* __restrict__ nnz_total) {
+                     unsigned char* __restrict__ NZI, int* __restrict__ nnz_total, const int* __restrict__ mix_gate) {
+  if (mix_handled(mix_gate, nrows * S)) return;
   const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (wid >= nrows * S) return;
   const int r = wid / S, s = wid - r * S;
@@ -839,6 +850,8 @@ size_t smi_elbo_carve(SmiArena& ar, ElboWs& w, const SmiModelDesc& md, int m, in
   w.nnz_total = ar.take<int>(1);
   w.LOGQ = ar.take<float>((size_t)nrows * S);
   w.LOGP = ar.take<float>((size_t)nrows * S);
+  w.mix.on = normal && smi_mix_tc_eligible(md, m, S, nrows);
+  if (w.mix.on) smi_mix_tc_carve(ar, w.mix, md, m, S, nrows);
   ClsTcWs& c = w.cls;
   c.on = smi_cls_tc_eligible(md, B);
   if (c.on) {
@@ -862,7 +875,7 @@ int smi_guide_prep(const SmiModelDesc& md, const float* psi, int m, ElboWs& w, c
   dim3 grid(nlb_of(md.latent_dim), m);
   SMI_PROF_BEGIN(st);
   guide_prep_kernel<<<grid, 256, 0, st>>>(md, psi, m, w.loc_of, w.rho_of, w.tr_of, w.MU, w.SIG, w.ISIG,
-                                          w.logdet_part, w.nnz_total);
+                                          w.logdet_part, w.nnz_total, w.mix.on ? w.mix.gate : nullptr);
   SMI_LAUNCH_OK_N("guide_prep_kernel", st);
   return SMI_OK;
 }
@@ -884,10 +897,10 @@ int smi_guide_sample(const SmiModelDesc& md, const float* eps, int m, int S, int
   static const bool big_blocks = getenv("SMI_SAMPLE_8X8") != nullptr;
   if (m > 32 && big_blocks)
     guide_sample_kernel<8, 8><<<grid, 256, smem, st>>>(eps, w.MU, w.SIG, w.ISIG, m, S, md.latent_dim, row0, w.Z, w.QP,
-                                                       w.nkq, w.ksub);
+                                                       w.nkq, w.ksub, w.mix.on ? w.mix.gate : nullptr);
   else
     guide_sample_kernel<4, 4><<<grid, 256, smem, st>>>(eps, w.MU, w.SIG, w.ISIG, m, S, md.latent_dim, row0, w.Z, w.QP,
-                                                       w.nkq, w.ksub);
+                                                       w.nkq, w.ksub, w.mix.on ? w.mix.gate : nullptr);
   SMI_LAUNCH_OK_N("guide_sample_kernel", st);
   return SMI_OK;
 }
@@ -896,7 +909,8 @@ int smi_guide_weights(const SmiModelDesc& md, int m, int S, int nrows, ElboWs& w
   const int warps = nrows * S;
   SMI_PROF_BEGIN(st);
   guide_weights_kernel<<<(warps + 7) / 8, 256, 0, st>>>(md, w.QP, w.logdet_part, nlb_of(md.latent_dim), w.Z, m, S,
-                                                        nrows, w.nkq, w.W, w.LOGQ, w.NNZ, w.NZI, w.nnz_total);
+                                                        nrows, w.nkq, w.W, w.LOGQ, w.NNZ, w.NZI, w.nnz_total,
+                                                        w.mix.on ? w.mix.gate : nullptr);
   SMI_LAUNCH_OK_N("guide_weights_kernel", st);
   return SMI_OK;
 }

@@ -30,7 +30,7 @@ constexpr uint32_t kStageBytes = 2 * kABytes + 2 * kBBytes;  // 96 KB
 constexpr uint32_t kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
 constexpr int kGroupM = 16;  // tile rasterisation: 16 row-tiles share a B panel sweep
 
-enum { EPI_GRAM = 0, EPI_FORCE = 1, EPI_CLS_H1 = 2, EPI_CLS_DW1 = 3 };
+enum { EPI_GRAM = 0, EPI_FORCE = 1, EPI_CLS_H1 = 2, EPI_CLS_DW1 = 3, EPI_PART = 4 };   // EPI_PART: raw (split-K) partial tiles only
 
 struct GemmArgs {
   int M, N, K;          // K already padded to a multiple of BK in the planes

@@ -59,7 +59,7 @@ int launch_gemm(const float* Ah, const float* Al, long long a_rows, const float*
   ga.tiles_n = (ga.N + tc::BN - 1) / tc::BN;
   const int ntiles = ga.tiles_m * ga.tiles_n;
   const int grid = ntiles < smi_num_sms() ? ntiles : smi_num_sms();
-  static bool attr_set[4] = {false, false, false, false};
+  static bool attr_set[5] = {false, false, false, false, false};
   if (!attr_set[EPI]) {
     SMI_CUDA_OK(cudaFuncSetAttribute(tc::gemm3xtf32_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)tc::kSmemBytes));
@@ -97,7 +97,7 @@ int launch_gemm_pair(const float* Ah, const float* Al, long long a_rows, const f
   const int npairtiles = ((ga.tiles_m + 1) / 2) * ga.tiles_n * (ga.ksplit > 1 ? ga.ksplit : 1);   // work units
   const int maxpairs = smi_num_sms() / 2;
   const int pairs = npairtiles < maxpairs ? npairtiles : maxpairs;
-  static bool attr_set[4] = {false, false, false, false};
+  static bool attr_set[5] = {false, false, false, false, false};
   if (!attr_set[EPI]) {
     SMI_CUDA_OK(cudaFuncSetAttribute(tc::gemm3xtf32_pair_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)tc::kPairSmemBytes));
@@ -117,7 +117,7 @@ int launch_gemm_pair(const float* Ah, const float* Al, long long a_rows, const f
   cfg.numAttrs = 1;
   SMI_PROF_BEGIN(st);
   SMI_CUDA_OK(cudaLaunchKernelEx(&cfg, tc::gemm3xtf32_pair_kernel<EPI>, ma_h, ma_l, mb_h, mb_l, ga));
-  SMI_LAUNCH_OK_N(EPI == tc::EPI_GRAM ? "gemm3xtf32_pair_gram" : "gemm3xtf32_pair_force", st);
+  SMI_LAUNCH_OK_N(EPI == tc::EPI_GRAM ? "gemm3xtf32_pair_gram" : (EPI == tc::EPI_PART ? "gemm3xtf32_pair_part" : "gemm3xtf32_pair_force"), st);
   return SMI_OK;
 }
 

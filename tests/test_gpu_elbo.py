@@ -226,3 +226,31 @@ def test_bnn_reg_tcgen05_kernel(cuda, monkeypatch, m, S, N, B, I, act, noise):
         tol = max(RTOL, 4.0 * _rel(G32, G64))
     assert _rel(G, G64) <= tol
     assert np.max(np.abs(E - E64) / np.abs(E64)) <= RTOL
+
+
+@pytest.mark.parametrize("m,S,dim,radius", [(160, 100, 40, 2.0), (160, 100, 40, 0.02), (70, 33, 50, 0.3), (40, 130, 70, 2.0),
+                                            (200, 20, 24, 1.0), (5, 7, 300, 0.5)])
+def test_mixture_tensor_core_filter_forced(cuda, monkeypatch, m, S, dim, radius):
+    """The tcgen05 mixture filter (csrc/elbo_mix_tc.cu) forced onto shapes below its default rule (SMI_MIX_TC=2):
+    far-apart particles (every foreign component certified zero, exact path), nearly coincident ones (the device hands
+    the call back to the CUDA-core kernels) and mixed cases; all against the float64 oracle at 1e-5."""
+    monkeypatch.setenv("SMI_MIX_TC", "2")
+    _gaussian_target_case(cuda, "normal", m, S, dim, radius=radius)
+
+
+def test_mixture_filter_agrees_with_cuda_core_path(cuda, monkeypatch):
+    """UCI-shape BNN (L = 3302), 96 components, 4 local rows: filter path (default rule) against SMI_MIX_TC=0."""
+    from smi_experiments_b200 import models
+    pm, om = models.uci_bnn(13), omodels.uci_bnn(13)
+    m, S, N, B = 96, 20, 60, 30
+    md, psi, eps, rng, L, d = _setup(pm, om, "normal", m, S, seed=3)
+    x = rng.standard_normal((N, 13)).astype(np.float32)
+    y = rng.standard_normal(N).astype(np.float32)
+    idx = np.stack([rng.permutation(N)[:B] for _ in range(4 * S)]).reshape(4, S, B).astype(np.int32)
+    G1, E1 = _run(cuda, md, psi, eps[8:12], idx, x, y, S, B, 2.0, 1.0, row0=8, nrows=4)
+    monkeypatch.setenv("SMI_MIX_TC", "0")
+    G0, E0 = _run(cuda, md, psi, eps[8:12], idx, x, y, S, B, 2.0, 1.0, row0=8, nrows=4)
+    assert _rel(G1, G0) <= 2e-6
+    assert np.max(np.abs(E1 - E0) / np.abs(E0)) <= 2e-6
+    G64, E64 = oelbo.elbo_grads(om, psi.astype(np.float64), eps[8:12], idx, x, y, N, 1.0, "normal", torch.float64, rows=(8, 4))
+    assert _rel(G1, G64) <= RTOL and np.max(np.abs(E1 - E64) / np.abs(E64)) <= RTOL
