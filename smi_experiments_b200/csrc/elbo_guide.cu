@@ -109,6 +109,14 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
   const int tj = threadIdx.x % njg, ts = (threadIdx.x / njg) % nsg, ks = threadIdx.x / nsj;
   const bool lane_on = ks < KS;
   const int kper = kGuideKT / KS;        // latents of a tile per slice
+  int zoff[8][DA / 4], moff[8][DB / 4];  // swizzled column offsets of this thread's operands for latent u mod 8
+#pragma unroll
+  for (int u = 0; u < 8; ++u) {
+#pragma unroll
+    for (int e = 0; e < DA; e += 4) zoff[u][e >> 2] = (ts * DA + e) ^ (u << 2);
+#pragma unroll
+    for (int e = 0; e < DB; e += 4) moff[u][e >> 2] = (tj * DB + e) ^ (u << 2);
+  }
   for (int sb = 0; sb < S; sb += 128) {
     const int Sc = min(128, S - sb);
     for (int jb = 0; jb < m; jb += JCH) {
@@ -190,29 +198,36 @@ guide_sample_kernel(const float* __restrict__ eps, const float* __restrict__ MU,
         }
         __syncthreads();
         if (lane_on) {
-#pragma unroll 2
-          for (int kk = ks * kper; kk < (ks + 1) * kper; ++kk) {
-            const int sw = (kk & 7) << 2;
-            float zz[DA], mm[DB], ii[DB];
+          // kper is a multiple of 8 and so is every slice start: the swizzle (kk & 7) << 2 of latent kb + u is the
+          // constant u << 2, and the eight (row, column) offsets of a thread are loop invariants -- one add per
+          // LDS instead of six integer instructions (ncu: 38 % of the issued instructions were the FMAs)
+          for (int kb = ks * kper; kb < (ks + 1) * kper; kb += 8) {
+            const float* zb = zt + kb * 128;
+            const float* mb = mt + kb * 32;
+            const float* ib = it + kb * 32;
 #pragma unroll
-            for (int e = 0; e < DA; e += 4) {
-              const float4 z4 = *reinterpret_cast<const float4*>(zt + kk * 128 + ((ts * DA + e) ^ sw));
-              zz[e] = z4.x, zz[e + 1] = z4.y, zz[e + 2] = z4.z, zz[e + 3] = z4.w;
-            }
+            for (int u = 0; u < 8; ++u) {
+              float zz[DA], mm[DB], ii[DB];
 #pragma unroll
-            for (int e = 0; e < DB; e += 4) {
-              const float4 m4 = *reinterpret_cast<const float4*>(mt + kk * 32 + ((tj * DB + e) ^ sw));
-              const float4 i4 = *reinterpret_cast<const float4*>(it + kk * 32 + ((tj * DB + e) ^ sw));
-              mm[e] = m4.x, mm[e + 1] = m4.y, mm[e + 2] = m4.z, mm[e + 3] = m4.w;
-              ii[e] = i4.x, ii[e + 1] = i4.y, ii[e + 2] = i4.z, ii[e + 3] = i4.w;
-            }
-#pragma unroll
-            for (int a = 0; a < DA; ++a)
-#pragma unroll
-              for (int b = 0; b < DB; ++b) {
-                const float df = fmaf(ii[b], zz[a], mm[b]);
-                acc[a][b] = fmaf(df, df, acc[a][b]);
+              for (int e = 0; e < DA; e += 4) {
+                const float4 z4 = *reinterpret_cast<const float4*>(zb + u * 128 + zoff[u][e >> 2]);
+                zz[e] = z4.x, zz[e + 1] = z4.y, zz[e + 2] = z4.z, zz[e + 3] = z4.w;
               }
+#pragma unroll
+              for (int e = 0; e < DB; e += 4) {
+                const float4 m4 = *reinterpret_cast<const float4*>(mb + u * 32 + moff[u][e >> 2]);
+                const float4 i4 = *reinterpret_cast<const float4*>(ib + u * 32 + moff[u][e >> 2]);
+                mm[e] = m4.x, mm[e + 1] = m4.y, mm[e + 2] = m4.z, mm[e + 3] = m4.w;
+                ii[e] = i4.x, ii[e + 1] = i4.y, ii[e + 2] = i4.z, ii[e + 3] = i4.w;
+              }
+#pragma unroll
+              for (int a = 0; a < DA; ++a)
+#pragma unroll
+                for (int b = 0; b < DB; ++b) {
+                  const float df = fmaf(ii[b], zz[a], mm[b]);
+                  acc[a][b] = fmaf(df, df, acc[a][b]);
+                }
+            }
           }
         }
       }
@@ -332,7 +347,8 @@ guide_grad_kernel(const float* __restrict__ psi, const float* __restrict__ eps, 
                   const float* __restrict__ DZ, const float* __restrict__ LOGP, const float* __restrict__ LOGQ,
                   const int* __restrict__ loc_of, const int* __restrict__ rho_of, const int* __restrict__ tr_of,
                   int m, int S, int L, int d, float tau_host, const float* __restrict__ tau_dev, int row0,
-                  float* __restrict__ G, float* __restrict__ elbo) {
+                  float* __restrict__ G, float* __restrict__ elbo, const int* __restrict__ nnz_total, int thresh) {
+  if (nnz_total && *nnz_total <= thresh) return;   // short component lists: guide_grad_sparse_kernel does this call
   const float tau = tau_dev ? *tau_dev : tau_host;   // device-side schedule (ASVGD) when given
   extern __shared__ float sm[];
   float* wt = sm;                        // [S][MP]
@@ -915,22 +931,6 @@ int smi_guide_weights(const SmiModelDesc& md, int m, int S, int nrows, ElboWs& w
   return SMI_OK;
 }
 
-template <int MP>
-static int launch_grad(const SmiModelDesc& md, const float* psi, const float* eps, int m, int S, float tau,
-                       const float* tau_dev, int row0, int nrows, ElboWs& w, float* G, float* elbo, cudaStream_t st) {
-  const size_t smem = ((size_t)S * MP + kGradSG * kGradKT * 2) * sizeof(float);
-  if (smem > 200 * 1024) SMI_FAIL(SMI_ELIMIT, "guide_grad: S * m too large for shared memory");
-  if (smem > 48 * 1024)
-    SMI_CUDA_OK(cudaFuncSetAttribute(guide_grad_kernel<MP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dim3 grid((md.latent_dim + kGradKT - 1) / kGradKT, nrows);
-  SMI_PROF_BEGIN(st);
-  guide_grad_kernel<MP><<<grid, 256, smem, st>>>(psi, eps, w.MU, w.SIG, w.ISIG, w.W, w.DZ, w.LOGP, w.LOGQ,
-                                                 w.loc_of, w.rho_of, w.tr_of, m, S, md.latent_dim,
-                                                 md.particle_dim, tau, tau_dev, row0, G, elbo);
-  SMI_LAUNCH_OK_N("guide_grad_kernel", st);
-  return SMI_OK;
-}
-
 // The sparse kernel takes the call when the lists hold at most kSparseAvg components per draw on average
 // (SMI_GRAD_SPARSE=0 disables it: the threshold becomes -1 and the dense kernels always run).
 constexpr int kSparseAvg = 8;
@@ -948,6 +948,24 @@ static int launch_grad_sparse(const SmiModelDesc& md, const float* psi, const fl
                                                  w.nnz_total, sparse_thresh(nrows, S), w.loc_of, w.rho_of, w.tr_of, m, S,
                                                  md.latent_dim, md.particle_dim, tau, tau_dev, row0, G, elbo);
   SMI_LAUNCH_OK_N("guide_grad_sparse_kernel", st);
+  return SMI_OK;
+}
+
+template <int MP>
+static int launch_grad(const SmiModelDesc& md, const float* psi, const float* eps, int m, int S, float tau,
+                       const float* tau_dev, int row0, int nrows, ElboWs& w, float* G, float* elbo, cudaStream_t st) {
+  const size_t smem = ((size_t)S * MP + kGradSG * kGradKT * 2) * sizeof(float);
+  if (smem > 200 * 1024) SMI_FAIL(SMI_ELIMIT, "guide_grad: S * m too large for shared memory");
+  if (smem > 48 * 1024)
+    SMI_CUDA_OK(cudaFuncSetAttribute(guide_grad_kernel<MP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid((md.latent_dim + kGradKT - 1) / kGradKT, nrows);
+  SMI_PROF_BEGIN(st);
+  const bool gated = m > 32;      // 32 < m <= 48: the sparse kernel was launched first (smi_guide_grad)
+  guide_grad_kernel<MP><<<grid, 256, smem, st>>>(psi, eps, w.MU, w.SIG, w.ISIG, w.W, w.DZ, w.LOGP, w.LOGQ,
+                                                 w.loc_of, w.rho_of, w.tr_of, m, S, md.latent_dim,
+                                                 md.particle_dim, tau, tau_dev, row0, G, elbo,
+                                                 gated ? w.nnz_total : nullptr, gated ? sparse_thresh(nrows, S) : 0);
+  SMI_LAUNCH_OK_N("guide_grad_kernel", st);
   return SMI_OK;
 }
 
@@ -978,14 +996,14 @@ int smi_guide_grad(const SmiModelDesc& md, const float* psi, const float* eps, i
   if (m <= 20) return launch_grad<20>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
   if (m <= 24) return launch_grad<24>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
   if (m <= 32) return launch_grad<32>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
-  if (m <= 40) return launch_grad<40>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
-  if (m <= 48) return launch_grad<48>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
-  // m > 48: sparse kernel first (runs or returns at once, decided on the device), then the dense kernel for the
-  // opposite case
+  // m > 32: sparse kernel first (runs or returns at once, decided on the device), then the dense kernel for the
+  // opposite case (at m = 40 the dense register-table kernel takes 74 us, the sparse one 48)
   {
     int rc = launch_grad_sparse(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
     if (rc) return rc;
   }
+  if (m <= 40) return launch_grad<40>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+  if (m <= 48) return launch_grad<48>(md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
   if (m <= 4 * 48 && !getenv("SMI_GRAD_STREAM")) {
     const int mpc = (m + 3) / 4;
     int rc;

@@ -300,6 +300,50 @@ gram_finish_kernel(const float* __restrict__ part, int ks, long long stride, int
   D2[(long long)i * m + j] = v;
 }
 
+// Split-K of the force product where the tile count quantises badly on the 74 CTA pairs: 2048 rows x d = 1e4 are
+// 320 pair tiles = 4.3 -> 5 waves (2.74 ms where 2.4 would do; 8 GPUs x 2048 rows, or m = 2048 on one GPU).  Cost model in
+// waves of whole tiles: ceil(tiles ks / pairs) x (chunks per segment / chunks) + 0.03 ks for the partial tiles' traffic.
+int force_ksplit(int rows, int m, int d) {
+  if (!tc_pair_enabled()) return 1;
+  if (const char* e = getenv("SMI_FORCE_KSPLIT")) return atoi(e) > 0 ? atoi(e) : 1;   // experiments only
+  const int nchunks = (pad32(m) / tc::BK + tc::kChunkKB - 1) / tc::kChunkKB;
+  const int tiles = ((rows + 255) / 256) * ((d + 255) / 256), pairs = smi_num_sms() / 2;
+  int best = 1;
+  double best_cost = (double)((tiles + pairs - 1) / pairs);
+  // the partial tiles live in the X plane region (2 m pad32(d) floats): ks rows d must fit
+  const long long fit = (2LL * m * pad32(d)) / ((long long)rows * ((d + 3) / 4 * 4));
+  // measured: with short K loops the split LOSES (m = 1024 / 2048 on one GPU: 0.56 -> 0.71 / 1.08 -> 1.42 ms -- a unit of
+  // 16 K blocks is too short to amortise its epilogue and the finishing pass), so segments keep >= 16 chunks (K >= 4096)
+  for (int s = 2; s <= 4 && s <= fit && nchunks / s >= 16; ++s) {
+    const double cost = (double)(((long long)tiles * s + pairs - 1) / pairs) * (double)((nchunks + s - 1) / s) / nchunks + 0.03 * s;
+    if (cost < 0.93 * best_cost && cost < (best == 1 ? 0.93 * best_cost : best_cost)) best = s, best_cost = cost;
+  }
+  return best;
+}
+
+// F[i][k] = sum_s part[s][i][k] + c rowsum_i (x_ik - mean_k), segments added in order; sum F^2 in double per CTA.
+__global__ void __launch_bounds__(256)
+force_finish_kernel(const float* __restrict__ part, int ks, long long stride, int ldp, int rows, int d,
+                    const float* __restrict__ X, const float* __restrict__ mean, const float* __restrict__ rowsum,
+                    const float* __restrict__ scal, float* __restrict__ F, double* __restrict__ lpart) {
+  __shared__ double red[32];
+  const float c = scal[1];
+  double sq = 0.0;
+  for (int i = blockIdx.x; i < rows; i += gridDim.x) {
+    const float ra = c * rowsum[i];
+    for (int k = threadIdx.x; k < d; k += blockDim.x) {
+      const float* p = part + (long long)i * ldp + k;
+      float acc = 0.f;
+      for (int s = 0; s < ks; ++s) acc += p[s * stride];
+      const float v = fmaf(ra, __ldg(X + (size_t)i * d + k) - __ldg(mean + k), acc);
+      F[(size_t)i * d + k] = v;
+      sq += (double)v * (double)v;
+    }
+  }
+  sq = block_sum(sq, red);
+  if (threadIdx.x == 0) lpart[blockIdx.x] = sq;
+}
+
 // ---- orchestration ------------------------------------------------------------------------
 size_t smi_stein_tc_workspace_bytes(int rows, int m, int d) {
   SmiArena ar(nullptr, 0);
@@ -384,6 +428,24 @@ static int tc_force_rows(const float* X, const float* G, int m, int d, int row0,
   ga.scal = w.scal;
   ga.lpart = w.lpart;
   SMI_CUDA_OK(cudaMemsetAsync(w.lpart, 0, 256 * sizeof(double), st));
+  const int ks = force_ksplit(rows, m, d);
+  if (ks > 1) {
+    // raw partial tiles go into the X plane region of the workspace (dead once the Gram has run)
+    const int ldp = (d + 3) / 4 * 4;
+    const size_t span = (size_t)2 * m * pad32(d);
+    if ((size_t)ks * rows * ldp > span) SMI_FAIL(SMI_ENOSPC, "force split-K partials do not fit the plane region");
+    ga.ksplit = ks;
+    ga.part = w.Xh;
+    ga.part_stride = (long long)rows * ldp;
+    ga.part_ld = ldp;
+    int rc = launch_gemm_stein<tc::EPI_FORCE>(w.Kh, w.Kl, rows, w.Yh, w.Yl, d, ldm, ga, st);
+    if (rc) return rc;
+    SMI_PROF_BEGIN(st);
+    force_finish_kernel<<<256, 256, 0, st>>>(w.Xh, ks, (long long)rows * ldp, ldp, rows, d, X + (size_t)row0 * d, w.mean,
+                                             w.rowsum, w.scal, F, w.lpart);
+    SMI_LAUNCH_OK_N("force_finish_kernel", st);
+    return SMI_OK;
+  }
   return launch_gemm_stein<tc::EPI_FORCE>(w.Kh, w.Kl, rows, w.Yh, w.Yl, d, ldm, ga, st);
 }
 

@@ -259,7 +259,7 @@ gemm3xtf32_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
         }
       }
       const int tna = actual_col_tile(args, tn);
-      if ((EPI == EPI_GRAM && args.ksplit > 1) || EPI == EPI_PART) {
+      if (((EPI == EPI_GRAM || EPI == EPI_FORCE) && args.ksplit > 1) || EPI == EPI_PART) {
         // raw partial tile of this K segment (part_ld % 4 == 0; columns past N are zero)
         const int row = tm * BM + q * 32 + lane;
         if (row < args.M) {
