@@ -305,7 +305,12 @@ gram_finish_kernel(const float* __restrict__ part, int ks, long long stride, int
 // waves of whole tiles: ceil(tiles ks / pairs) x (chunks per segment / chunks) + 0.03 ks for the partial tiles' traffic.
 int force_ksplit(int rows, int m, int d) {
   if (!tc_pair_enabled()) return 1;
-  if (const char* e = getenv("SMI_FORCE_KSPLIT")) return atoi(e) > 0 ? atoi(e) : 1;   // experiments only
+  // Measured at N = 8 (2048 rows, K = 16384, ks = 2; profiles/r02n_sharded_c5_n8_force_splitk.json): the GEMM goes
+  // 2.74 -> 2.52 ms as the model says, but the finishing pass over the 164 MB of partials costs 0.47 ms -- a net loss, so
+  // the split is OFF unless SMI_FORCE_KSPLIT asks for it (= a segment count, or "auto" for the cost model below).
+  const char* e = getenv("SMI_FORCE_KSPLIT");
+  if (!e) return 1;
+  if (atoi(e) > 0) return atoi(e);
   const int nchunks = (pad32(m) / tc::BK + tc::kChunkKB - 1) / tc::kChunkKB;
   const int tiles = ((rows + 255) / 256) * ((d + 255) / 256), pairs = smi_num_sms() / 2;
   int best = 1;
