@@ -55,7 +55,7 @@ def bench_config(world):
                 # how the GPU arm is timed (the same dict is printed by --impl reference so that both arms carry an
                 # identical `config`; the CPU arm times whole steps with perf_counter)
                 l2="GPU arm: flushed between steps (256 MiB memset, untimed)",
-                timing="GPU arm: cuda events per step, max over ranks; graph replay at N = 1, eager launches at N > 1")
+                timing="GPU arm: cuda events per step, max over ranks; CUDA-graph replay of the whole step (NCCL all-gathers included at N > 1)")
 
 
 def peaks():

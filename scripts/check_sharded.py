@@ -63,12 +63,12 @@ xd, yd = torch.from_numpy(x).to(dev), torch.from_numpy(y).to(dev)
 for per in (4, 20):
     m = per * world
     model = smi.uci_bnn(13)
-    mk = lambda cls: cls(model, smi.AutoNormal(model, init_loc_fn=smi.init_to_uniform(radius=0.1)), smi.Adam(5e-3),
-                         smi.RBFKernel(), num_stein_particles=m, num_elbo_particles=10, use_cuda_graph=False)
-    e1, eN = mk(smi.SteinVI), mk(ShardedSteinVI)
+    mk = lambda cls, graph=False: cls(model, smi.AutoNormal(model, init_loc_fn=smi.init_to_uniform(radius=0.1)), smi.Adam(5e-3),
+                                      smi.RBFKernel(), num_stein_particles=m, num_elbo_particles=10, use_cuda_graph=graph)
+    e1, eN = mk(smi.SteinVI), mk(ShardedSteinVI, graph=(per == 20))     # per = 20: the sharded step replays a CUDA graph (NCCL inside) from its third call
     s1 = e1.init(smi.PRNGKey(3), x=xd, y=yd, subsample=100)
     sN = eN.init(smi.PRNGKey(3), x=xd, y=yd, subsample=100)
-    for it in range(3):
+    for it in range(5):
         s1, l1 = e1.update(s1, x=xd, y=yd, subsample=100)
         sN, lN = eN.update(sN, x=xd, y=yd, subsample=100)
         ex, el = rel(sN.optim_state.x, s1.optim_state.x), abs(float(lN) - float(l1)) / float(l1)

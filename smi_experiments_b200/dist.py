@@ -362,7 +362,11 @@ class ShardedSteinVI(SteinVI):
     all-gathered every step), the optimizer slots cover the local rows only."""
 
     def __init__(self, *args, group=None, **kwargs):
-        kwargs.setdefault("use_cuda_graph", False)
+        # m <= 256 (every rank evaluates the small / mid Stein path after one all-gather of the scores): the step --
+        # two ncclAllGather included -- is captured into a CUDA graph like the single-GPU step; at ~25 launches and
+        # ~0.5 ms per step the eager Python / ctypes issue rate was the limit at N = 4 (kernels 542 us, step 623 us).
+        # SMI_SHARD_GRAPH=0 keeps eager launches.
+        kwargs.setdefault("use_cuda_graph", os.environ.get("SMI_SHARD_GRAPH", "1") != "0")
         super().__init__(*args, **kwargs)
         self.group = group
         self.world = dist.get_world_size(group)
@@ -372,7 +376,7 @@ class ShardedSteinVI(SteinVI):
         self._side = None
 
     def _graphable(self):
-        return False
+        return self.num_stein_particles <= 256
 
     def init(self, rng_key, *args, **kwargs):
         st = super().init(rng_key, *args, **kwargs)         # every rank draws the same full init
