@@ -623,6 +623,9 @@ def run_gpu(args):
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
+        eng._graph = None            # the captured step holds NCCL kernels: drop it before the communicator goes
+        torch.cuda.synchronize()
+        dist.barrier()
         dist.destroy_process_group()
 
 
