@@ -31,6 +31,14 @@ def step():
 for _ in range(3):
     step()
 torch.cuda.synchronize()
+evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+for a, b in evs:       # wall time of the launch sequence (kernels on libsmi's internal side stream overlap)
+    flush.zero_()
+    a.record()
+    step()
+    b.record()
+torch.cuda.synchronize()
+wall = sum(a.elapsed_time(b) for a, b in evs) / reps * 1e3
 lib.smi_profile(1)
 for _ in range(reps):
     flush.zero_()
@@ -45,3 +53,4 @@ for ln in buf.value.decode().splitlines():
     print("%-28s %7.1f us" % (nm, float(ms) / reps * 1e3))
     tot += float(ms) / reps * 1e3
 print("%-28s %7.1f us   (m=%d, rows=%d)" % ("sum", tot, m, nrows))
+print("%-28s %7.1f us   (CUDA events around the eager launch sequence)" % ("wall", wall))

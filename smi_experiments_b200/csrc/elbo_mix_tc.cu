@@ -64,35 +64,45 @@ mix_centroid_kernel(const float* __restrict__ MU, int m, int L, float* __restric
   if (g == 0 && k < L) cent[k] = (float)(((part[0][kk] + part[1][kk]) + (part[2][kk] + part[3][kk])) / (double)m);
 }
 
-// A planes + Z + partial sums of eps^2.  grid (ceil(Lp / 256), nrows * S)
+// A planes + Z + partial sums of eps^2.  grid (ceil(Lp / 1024), nrows * S): four latents per thread, 16-byte plane
+// stores (Lp is a multiple of 32, so every plane row segment is 16-byte aligned; eps / Z rows are not -- L = 3302 --
+// and move as scalars).
 __global__ void __launch_bounds__(256)
 mix_a_planes_kernel(const float* __restrict__ eps, const float* __restrict__ MU, const float* __restrict__ SIG,
                     const float* __restrict__ cent, int S, int L, int Lp, int row0, float* __restrict__ Z,
                     float* __restrict__ Ah, float* __restrict__ Al, float* __restrict__ epart) {
   __shared__ float red[8];
   const int R = blockIdx.y, r = R / S, i = row0 + r;
-  const int k = blockIdx.x * 256 + threadIdx.x;
+  const int k0 = (blockIdx.x * 256 + threadIdx.x) * 4;
   float e2 = 0.f;
-  if (k < Lp) {
-    float v0 = 0.f, v1 = 0.f, v2 = 0.f;
-    if (k < L) {
-      const float ep = __ldcs(eps + (size_t)R * L + k);
-      const float mu = MU[(size_t)i * L + k], sg = SIG[(size_t)i * L + k];
-      const float u = sg * ep;
-      Z[(size_t)R * L + k] = fmaf(sg, ep, mu);
-      v0 = u * u;
-      v1 = u * (mu - cent[k]);
-      v2 = u;
-      e2 = ep * ep;
+  if (k0 < Lp) {
+    float ep[4], mu[4], sg[4], ce[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int k = k0 + e;
+      const bool ok = k < L;
+      ep[e] = ok ? __ldcs(eps + (size_t)R * L + k) : 0.f;
+      mu[e] = ok ? __ldg(MU + (size_t)i * L + k) : 0.f;
+      sg[e] = ok ? __ldg(SIG + (size_t)i * L + k) : 0.f;
+      ce[e] = ok ? __ldg(cent + k) : 0.f;
     }
-    const size_t base = (size_t)R * (3 * (size_t)Lp) + k;
-    float h, l;
-    split32(v0, h, l);
-    Ah[base] = h, Al[base] = l;
-    split32(v1, h, l);
-    Ah[base + Lp] = h, Al[base + Lp] = l;
-    split32(v2, h, l);
-    Ah[base + 2 * (size_t)Lp] = h, Al[base + 2 * (size_t)Lp] = l;
+    float h0[4], l0[4], h1[4], l1[4], h2[4], l2[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float u = sg[e] * ep[e];
+      if (k0 + e < L) Z[(size_t)R * L + k0 + e] = fmaf(sg[e], ep[e], mu[e]);
+      split32(u * u, h0[e], l0[e]);
+      split32(u * (mu[e] - ce[e]), h1[e], l1[e]);
+      split32(u, h2[e], l2[e]);
+      e2 = fmaf(ep[e], ep[e], e2);
+    }
+    const size_t base = (size_t)R * (3 * (size_t)Lp) + k0;
+    *reinterpret_cast<float4*>(Ah + base) = make_float4(h0[0], h0[1], h0[2], h0[3]);
+    *reinterpret_cast<float4*>(Al + base) = make_float4(l0[0], l0[1], l0[2], l0[3]);
+    *reinterpret_cast<float4*>(Ah + base + Lp) = make_float4(h1[0], h1[1], h1[2], h1[3]);
+    *reinterpret_cast<float4*>(Al + base + Lp) = make_float4(l1[0], l1[1], l1[2], l1[3]);
+    *reinterpret_cast<float4*>(Ah + base + 2 * (size_t)Lp) = make_float4(h2[0], h2[1], h2[2], h2[3]);
+    *reinterpret_cast<float4*>(Al + base + 2 * (size_t)Lp) = make_float4(l2[0], l2[1], l2[2], l2[3]);
   }
   e2 = warp_sum(e2);
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = e2;
@@ -336,7 +346,7 @@ size_t smi_mix_tc_carve(SmiArena& ar, MixTcWs& x, const SmiModelDesc& md, int m,
   x.part = ar.take<float>((size_t)x.ksplit * Rtot * 256);
   x.C = ar.take<double>((size_t)nrows * m);
   x.bnd = ar.take<float>((size_t)nrows * m * 3);
-  x.epart = ar.take<float>(Rtot * ((x.Lp + 255) / 256));
+  x.epart = ar.take<float>(Rtot * ((x.Lp + 1023) / 1024));
   x.cand_n = ar.take<int>(Rtot);
   x.cand_i = ar.take<unsigned char>(Rtot * kMixCandMax);
   x.aex = ar.take<double>(Rtot * kMixCandMax);
@@ -344,22 +354,57 @@ size_t smi_mix_tc_carve(SmiArena& ar, MixTcWs& x, const SmiModelDesc& md, int m,
   return ar.off;
 }
 
+// A second stream inside libsmi (created once per host thread) so that the B planes and the per-pair constants, which
+// depend only on the centroid, run beside the HBM-bound A-plane kernel instead of after it.  Fork / join by events:
+// legal under stream capture (the sharded step replays a CUDA graph), and every fork is joined before the call returns.
+struct MixAux {
+  cudaStream_t st = nullptr;
+  cudaEvent_t fork = nullptr, b_done = nullptr, c_done = nullptr;
+  int dev = -1;
+};
+static int mix_aux(MixAux*& out) {
+  static thread_local MixAux aux;
+  int dev = -1;
+  SMI_CUDA_OK(cudaGetDevice(&dev));
+  if (aux.st == nullptr || aux.dev != dev) {
+    SMI_CUDA_OK(cudaStreamCreateWithFlags(&aux.st, cudaStreamNonBlocking));
+    SMI_CUDA_OK(cudaEventCreateWithFlags(&aux.fork, cudaEventDisableTiming));
+    SMI_CUDA_OK(cudaEventCreateWithFlags(&aux.b_done, cudaEventDisableTiming));
+    SMI_CUDA_OK(cudaEventCreateWithFlags(&aux.c_done, cudaEventDisableTiming));
+    aux.dev = dev;
+  }
+  out = &aux;
+  return SMI_OK;
+}
+
 int smi_guide_mix_tc(const SmiModelDesc& md, const float* eps, int m, int S, int row0, int nrows, ElboWs& w,
                      cudaStream_t st) {
   MixTcWs& x = w.mix;
-  const int L = md.latent_dim, Lp = x.Lp, Rtot = nrows * S, nkc = (Lp + 255) / 256, nlb = (L + 255) / 256;
+  const int L = md.latent_dim, Lp = x.Lp, Rtot = nrows * S, nkc = (Lp + 1023) / 1024, nlb = (L + 255) / 256;
+  MixAux* aux = nullptr;
+  int rc = mix_aux(aux);
+  if (rc) return rc;
+  cudaStream_t as = aux->st;
   SMI_PROF_BEGIN(st);
   mix_centroid_kernel<<<(L + 63) / 64, 256, 0, st>>>(w.MU, m, L, x.cent);
   SMI_LAUNCH_OK_N("mix_centroid_kernel", st);
+  // fork: B planes and pair constants beside the A planes
+  SMI_CUDA_OK(cudaEventRecord(aux->fork, st));
+  SMI_CUDA_OK(cudaStreamWaitEvent(as, aux->fork, 0));
+  SMI_PROF_BEGIN(as);
+  mix_b_planes_kernel<<<dim3((3 * Lp + 255) / 256, m), 256, 0, as>>>(w.MU, w.ISIG, x.cent, L, Lp, x.Bh, x.Bl);
+  SMI_LAUNCH_OK_N("mix_b_planes_kernel", as);
+  SMI_CUDA_OK(cudaEventRecord(aux->b_done, as));
+  SMI_PROF_BEGIN(as);
+  mix_pair_consts_kernel<<<nrows * m, 128, 0, as>>>(w.MU, w.SIG, w.ISIG, x.cent, m, L, row0, nrows, x.C, x.bnd);
+  SMI_LAUNCH_OK_N("mix_pair_consts_kernel", as);
+  SMI_CUDA_OK(cudaEventRecord(aux->c_done, as));
   SMI_PROF_BEGIN(st);
   mix_a_planes_kernel<<<dim3(nkc, Rtot), 256, 0, st>>>(eps, w.MU, w.SIG, x.cent, S, L, Lp, row0, w.Z, x.Ah, x.Al, x.epart);
   SMI_LAUNCH_OK_N("mix_a_planes_kernel", st);
-  SMI_PROF_BEGIN(st);
-  mix_b_planes_kernel<<<dim3((3 * Lp + 255) / 256, m), 256, 0, st>>>(w.MU, w.ISIG, x.cent, L, Lp, x.Bh, x.Bl);
-  SMI_LAUNCH_OK_N("mix_b_planes_kernel", st);
-  SMI_PROF_BEGIN(st);
-  mix_pair_consts_kernel<<<nrows * m, 128, 0, st>>>(w.MU, w.SIG, w.ISIG, x.cent, m, L, row0, nrows, x.C, x.bnd);
-  SMI_LAUNCH_OK_N("mix_pair_consts_kernel", st);
+  // the GEMM needs the B planes; the constants may still run beside it (measured, wall time of the launch sequence at
+  // m = 160: 453 us with the join after the GEMM, 461 us with it before -- the GEMM itself 75 vs 60 us)
+  SMI_CUDA_OK(cudaStreamWaitEvent(st, aux->b_done, 0));
   tc::GemmArgs ga = {};
   ga.M = Rtot;
   ga.N = m;
@@ -367,8 +412,9 @@ int smi_guide_mix_tc(const SmiModelDesc& md, const float* eps, int m, int S, int
   ga.part = x.part;
   ga.part_stride = (long long)Rtot * 256;
   ga.part_ld = 256;
-  int rc = launch_gemm_pair<tc::EPI_PART>(x.Ah, x.Al, Rtot, x.Bh, x.Bl, m, 3 * Lp, ga, st);
+  rc = launch_gemm_pair<tc::EPI_PART>(x.Ah, x.Al, Rtot, x.Bh, x.Bl, m, 3 * Lp, ga, st);
   if (rc) return rc;
+  SMI_CUDA_OK(cudaStreamWaitEvent(st, aux->c_done, 0));      // join: nothing of this call is left on the aux stream
   SMI_PROF_BEGIN(st);
   mix_filter_kernel<<<(Rtot + 7) / 8, 256, 0, st>>>(x.part, x.ksplit, Rtot, x.C, x.bnd, x.epart, nkc, w.logdet_part, nlb, m,
                                                     S, x.cand_n, x.cand_i, x.gate);
