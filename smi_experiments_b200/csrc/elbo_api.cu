@@ -1,4 +1,6 @@
 // C-ABI entry point of the per-particle mixture-ELBO gradient.
+#include <stdlib.h>
+
 #include "elbo.cuh"
 
 static int check_desc(const SmiModelDesc* md) {
@@ -20,6 +22,29 @@ SMI_API size_t smi_elbo_grad_workspace_bytes(const SmiModelDesc* md, int m, int 
   SmiArena ar(nullptr, 0);
   ElboWs w;
   return smi_elbo_carve(ar, w, *md, m, S, nrows, B) + 512;
+}
+
+// A side stream inside libsmi (one per host thread): guide_weights depends on guide_sample only, the model kernel
+// on Z only, so the weights run beside the model kernel -- in the shadow of its last, half-empty wave of CTAs (C2:
+// 2000 draws on 444 slots = 4.5 waves) -- instead of before it.  Fork / join by events (legal under stream capture,
+// joined before guide_grad).  SMI_ELBO_FORK=0 keeps one stream.
+struct ElboAux {
+  cudaStream_t st = nullptr;
+  cudaEvent_t fork = nullptr, done = nullptr;
+  int dev = -1;
+};
+static int elbo_aux(ElboAux*& out) {
+  static thread_local ElboAux aux;
+  int dev = -1;
+  SMI_CUDA_OK(cudaGetDevice(&dev));
+  if (aux.st == nullptr || aux.dev != dev) {
+    SMI_CUDA_OK(cudaStreamCreateWithFlags(&aux.st, cudaStreamNonBlocking));
+    SMI_CUDA_OK(cudaEventCreateWithFlags(&aux.fork, cudaEventDisableTiming));
+    SMI_CUDA_OK(cudaEventCreateWithFlags(&aux.done, cudaEventDisableTiming));
+    aux.dev = dev;
+  }
+  out = &aux;
+  return SMI_OK;
 }
 
 static int elbo_grad_impl(const SmiModelDesc* md, const float* psi, const float* eps, const int32_t* idx,
@@ -51,6 +76,19 @@ static int elbo_grad_impl(const SmiModelDesc* md, const float* psi, const float*
   // CUDA-core kernels below then return at once unless the device found the mixture dense
   if (w.mix.on && (rc = smi_guide_mix_tc(*md, eps, m, S, row0, nrows, w, st))) return rc;
   if ((rc = smi_guide_sample(*md, eps, m, S, row0, nrows, w, st))) return rc;
+  static const bool fork = !(getenv("SMI_ELBO_FORK") && getenv("SMI_ELBO_FORK")[0] == '0');
+  if (fork && md->kind != SMI_MODEL_GAUSS) {
+    ElboAux* aux = nullptr;
+    if ((rc = elbo_aux(aux))) return rc;
+    SMI_CUDA_OK(cudaEventRecord(aux->fork, st));
+    SMI_CUDA_OK(cudaStreamWaitEvent(aux->st, aux->fork, 0));
+    // model kernel first (it should own the machine), weights on the side stream
+    if ((rc = smi_model_logp_grad(*md, w.Z, idx, x, y, nrows * S, B, lik_scale, w.DZ, w.LOGP, w, st))) return rc;
+    if ((rc = smi_guide_weights(*md, m, S, nrows, w, aux->st))) return rc;
+    SMI_CUDA_OK(cudaEventRecord(aux->done, aux->st));
+    SMI_CUDA_OK(cudaStreamWaitEvent(st, aux->done, 0));
+    return smi_guide_grad(*md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
+  }
   if ((rc = smi_guide_weights(*md, m, S, nrows, w, st))) return rc;
   if ((rc = smi_model_logp_grad(*md, w.Z, idx, x, y, nrows * S, B, lik_scale, w.DZ, w.LOGP, w, st))) return rc;
   return smi_guide_grad(*md, psi, eps, m, S, tau, tau_dev, row0, nrows, w, G, elbo, st);
