@@ -10,6 +10,7 @@
 // with an integer all-reduce between `hist` and `scan` (see smi_experiments_b200/dist.py).
 // HBM traffic: 4 reads of D2 = 16 bytes per matrix element.
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "select.cuh"
@@ -90,6 +91,107 @@ select_hist(const unsigned* __restrict__ keys, size_t n, int pass, const unsigne
 #pragma unroll
     for (int w = 0; w < kThreads / 32; ++w) c += sh_all[w * kBins + t];
     if (c) atomicAdd(hist + t, c);
+  }
+}
+
+// Exactly symmetric matrix (the single-GPU Gram: lower triangle = mirror of the upper): read only the columns
+// j >= i of every row and count the off-diagonal elements twice -- half the bytes of a pass (1.07 GB at m = 16384).
+// One warp per row (rows dealt round-robin to the warps of the grid, so the shrinking rows balance), 16-byte loads from
+// the aligned column at or below the diagonal; weights 0 / 1 / 2 for j < i, j = i, j > i.  Integer counts: same result.
+__device__ __forceinline__ void run_add_w(unsigned* sh, unsigned& cur, unsigned& cnt, unsigned key, unsigned w, int shift,
+                                          unsigned mask) {
+  if (w) {
+    const unsigned digit = (key >> shift) & mask;
+    if (digit == cur) {
+      cnt += w;
+    } else {
+      if (cnt) atomicAdd(sh + cur, cnt);
+      cur = digit;
+      cnt = w;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+select_hist_sym(const unsigned* __restrict__ keys, int m, int pass, const unsigned* __restrict__ state,
+                unsigned* __restrict__ hist) {
+  extern __shared__ unsigned sh_all[];  // [kThreads / 32][kBins]
+  for (int t = threadIdx.x; t < kBins * (kThreads / 32); t += blockDim.x) sh_all[t] = 0u;
+  __syncthreads();
+  unsigned* sh = sh_all + (threadIdx.x >> 5) * kBins;
+  const int shift = pass_shift(pass), bits = pass_bits(pass);
+  const unsigned mask = (1u << bits) - 1u;
+  const unsigned prefix = pass == 0 ? 0u : state[0];
+  const int hs = shift + bits;
+  const int lane = threadIdx.x & 31;
+  const int wg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+  const int m4 = m >> 2;
+  unsigned cur = 0u, cnt = 0u;
+  constexpr int kInFlight = 4;
+  for (int i = wg; i < m; i += nw) {
+    const uint4* row = reinterpret_cast<const uint4*>(keys + (size_t)i * m);
+    for (int c0 = (i >> 2) + lane; c0 < m4; c0 += 32 * kInFlight) {
+      uint4 v[kInFlight];
+#pragma unroll
+      for (int e = 0; e < kInFlight; ++e) {
+        const int c = c0 + 32 * e;
+        v[e] = c < m4 ? __ldcs(row + c) : make_uint4(0u, 0u, 0u, 0u);
+      }
+#pragma unroll
+      for (int e = 0; e < kInFlight; ++e) {
+        const int c = c0 + 32 * e;
+        if (c >= m4) continue;
+        const int j = c << 2;
+        const unsigned ks[4] = {v[e].x, v[e].y, v[e].z, v[e].w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const unsigned w = j + q < i ? 0u : (j + q == i ? 1u : 2u);
+          run_add_w(sh, cur, cnt, ks[q], (pass == 0 || (ks[q] >> hs) == prefix) ? w : 0u, shift, mask);
+        }
+      }
+    }
+  }
+  if (cnt) atomicAdd(sh + cur, cnt);
+  __syncthreads();
+  for (int t = threadIdx.x; t < kBins; t += blockDim.x) {
+    unsigned c = 0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) c += sh_all[w * kBins + t];
+    if (c) atomicAdd(hist + t, c);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+select_tail_sym(const unsigned* __restrict__ keys, int m, unsigned* __restrict__ state) {
+  const unsigned a = state[2];
+  unsigned cnt = 0, mn = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int wg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+  const int m4 = m >> 2;
+  for (int i = wg; i < m; i += nw) {
+    const uint4* row = reinterpret_cast<const uint4*>(keys + (size_t)i * m);
+    for (int c = (i >> 2) + lane; c < m4; c += 32) {
+      const uint4 v = __ldcs(row + c);
+      const int j = c << 2;
+      const unsigned ks[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const unsigned w = j + q < i ? 0u : (j + q == i ? 1u : 2u);
+        if (w) {
+          if (ks[q] <= a) cnt += w;
+          else mn = min(mn, ks[q]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  }
+  if (lane == 0) {
+    if (cnt) atomicAdd(state + 3, cnt);
+    if (mn != 0xffffffffu) atomicMin(state + 4, mn);
   }
 }
 
@@ -207,6 +309,19 @@ int smi_select_hist(const float* D2, size_t n, int pass, unsigned* state, unsign
   return SMI_OK;
 }
 
+static int select_hist_sym_launch(const float* D2, int m, int pass, unsigned* state, unsigned* hist, cudaStream_t st) {
+  SMI_PROF_BEGIN(st);
+  constexpr size_t kHistSmem = (size_t)kBins * (kThreads / 32) * sizeof(unsigned);
+  static bool attr = false;
+  if (!attr) {
+    SMI_CUDA_OK(cudaFuncSetAttribute(select_hist_sym, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kHistSmem));
+    attr = true;
+  }
+  select_hist_sym<<<hist_grid(), kThreads, kHistSmem, st>>>((const unsigned*)D2, m, pass, state, hist);
+  SMI_LAUNCH_OK_N("select_hist", st);
+  return SMI_OK;
+}
+
 int smi_select_scan(unsigned* hist, int pass, unsigned long long rank_lo, unsigned* state, cudaStream_t st) {
   SMI_PROF_BEGIN(st);
   select_scan<<<1, 32, 0, st>>>(hist, pass, (unsigned)rank_lo, state);
@@ -240,7 +355,7 @@ int smi_select_fixed(float h, int m, float alpha, float* h_out, float* scal, cud
 
 // Whole single-GPU select: D2 is the full (m x m) matrix.
 int smi_select_bandwidth(const float* D2, int m, int median_mode, float alpha, float* h_out, float* scal,
-                         unsigned* rank_out, void* ws, size_t ws_bytes, cudaStream_t st) {
+                         unsigned* rank_out, void* ws, size_t ws_bytes, cudaStream_t st, int symmetric) {
   if (ws_bytes < smi_select_workspace_bytes()) SMI_FAIL(SMI_ENOSPC, "select workspace too small");
   if (m == 1) return smi_select_fixed(1.0f, m, alpha, h_out, scal, st);
   SmiArena ar(ws, ws_bytes);
@@ -251,13 +366,24 @@ int smi_select_bandwidth(const float* D2, int m, int median_mode, float alpha, f
   long long lo, hi;
   smi_median_ranks((long long)n, median_mode, &lo, &hi);
   SMI_CUDA_OK(cudaMemsetAsync(hist, 0, kBins * sizeof(unsigned), st));
+  // exactly symmetric D2 with 16-byte aligned rows: the passes read the upper triangle only (SMI_SELECT_SYM=0: full)
+  static const bool sym_off = getenv("SMI_SELECT_SYM") && getenv("SMI_SELECT_SYM")[0] == '0';
+  const bool sym = symmetric && !sym_off && (m & 3) == 0 && m >= 64 && (((uintptr_t)D2) & 15) == 0;
   for (int p = 0; p < 3; ++p) {
-    int rc = smi_select_hist(D2, n, p, state, hist, st);
+    int rc = sym ? select_hist_sym_launch(D2, m, p, state, hist, st) : smi_select_hist(D2, n, p, state, hist, st);
     if (rc) return rc;
     rc = smi_select_scan(hist, p, (unsigned long long)lo, state, st);
     if (rc) return rc;
   }
-  int rc = smi_select_tail(D2, n, state, st);
+  int rc;
+  if (sym) {
+    SMI_PROF_BEGIN(st);
+    select_tail_sym<<<hist_grid(), kThreads, 0, st>>>((const unsigned*)D2, m, state);
+    SMI_LAUNCH_OK_N("select_tail", st);
+    rc = SMI_OK;
+  } else {
+    rc = smi_select_tail(D2, n, state, st);
+  }
   if (rc) return rc;
   return smi_select_finish(state, nullptr, nullptr, (unsigned long long)hi, m, alpha, h_out, scal, rank_out, st);
 }

@@ -13,5 +13,6 @@ int smi_select_finish(const unsigned* state, const unsigned* cnt_le, const unsig
                       unsigned long long rank_hi, int m, float alpha, float* h_out, float* scal,
                       unsigned* rank_out, cudaStream_t st);
 int smi_select_fixed(float h, int m, float alpha, float* h_out, float* scal, cudaStream_t st);
+// symmetric != 0: D2 is EXACTLY symmetric (the single-GPU Gram): the passes read the upper triangle only.
 int smi_select_bandwidth(const float* D2, int m, int median_mode, float alpha, float* h_out, float* scal,
-                         unsigned* rank_out, void* ws, size_t ws_bytes, cudaStream_t st);
+                         unsigned* rank_out, void* ws, size_t ws_bytes, cudaStream_t st, int symmetric = 0);

@@ -472,7 +472,7 @@ int smi_stein_tc_run(const float* X, const float* G, int m, int d, int row0, int
   } else {
     if ((rc = tc_dist_rows(X, m, d, row0, rows, w, w.D2, st))) return rc;
     if ((rc = smi_select_bandwidth(w.D2, m, median_mode, alpha, h, w.scal, nullptr, w.sel,
-                                   smi_select_workspace_bytes(), st)))
+                                   smi_select_workspace_bytes(), st, /*symmetric=*/1)))
       return rc;
   }
   if ((rc = tc_force_rows(X, G, m, d, row0, rows, c_att, w, F, st))) return rc;
