@@ -554,7 +554,7 @@ def run_gpu(args):
             # layer products, forward + backward: 3 x 2 x (B I H + B H H + B H) per draw
             flop = 3.0 * 2.0 * (B * I * H + B * H * H + B * H) * m_local * S
             tc = dom_name.startswith("bnn_reg_tc")
-            src = "profiles/r02_ncu_bnn_reg_tc_kernel_C2.txt" if tc else "profiles/r01g_ncu_bnn_reg_mma3_ct_kernel_C2.txt"
+            src = "profiles/r02c_ncu_bnn_reg_tc_v1_C2.txt" if tc else "profiles/r01g_ncu_bnn_reg_mma3_ct_kernel_C2.txt"
             roof = dict(kernel=dom_name, bound="tensor", achieved=flop / dom_avg_ms / 1e9, peak=burst / 3.0,
                         unit="TFLOP/s", frac=(flop / dom_avg_ms / 1e9) / (burst / 3.0),
                         peak_sustained=sus / 3.0, frac_sustained_peak=(flop / dom_avg_ms / 1e9) / (sus / 3.0),
