@@ -258,3 +258,18 @@ def test_full_size_sweep_point_properties(cuda):
     Kr[torch.arange(len(rows), device=cuda), rows] = 1.0
     Fref = Kr @ (G.double() - c * X64) + c * Kr.sum(1, keepdim=True) * X64[rows]
     assert float((F1[rows].double() - Fref).norm() / Fref.norm()) <= RTOL
+
+
+@pytest.mark.parametrize("m,d", [(64, 40), (200, 100), (1000, 333), (1028, 64), (2052, 32)])
+def test_triangle_select_matches_full_select(cuda, m, d):
+    """The single-GPU force selects its bandwidth from the upper triangle of the symmetric D2 (off-diagonal elements
+    counted twice); the staged entry point reads the whole matrix.  Same integer counts, so the same bits of h --
+    also for particle counts that are not multiples of the 256-wide tiles."""
+    from smi_experiments_b200 import ops
+    x, g = _mk(m, d, seed=3 * m + d)
+    xt, gt = torch.from_numpy(x).to(cuda), torch.from_numpy(g).to(cuda)
+    _, _, h_tri = ops.stein_force(xt, gt, path=ops.PATH_TC)
+    D2 = ops.sqdist(xt, path=ops.PATH_TC)
+    assert torch.equal(D2, D2.T)
+    h_full, _ = ops.median_bandwidth(D2, 1)
+    assert h_tri.view(torch.int32).item() == h_full.view(torch.int32).item()
